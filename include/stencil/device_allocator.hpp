@@ -1,0 +1,36 @@
+#pragma once
+/* DeviceAllocator<T>: std-allocator-shaped wrapper over cudaMalloc on a chosen GPU.
+   Parity: reference include/stencil/device_allocator.hpp:7-64. */
+#include <cstddef>
+#include <new>
+
+#include "stencil/cuda_runtime.hpp"
+
+template <class T> class DeviceAllocator {
+  int dev_;
+
+public:
+  typedef T value_type;
+  explicit DeviceAllocator(int dev = 0) noexcept : dev_(dev) {}
+  template <class U> DeviceAllocator(const DeviceAllocator<U> &o) noexcept : dev_(o.device()) {}
+  int device() const noexcept { return dev_; }
+
+  T *allocate(std::size_t n) {
+    int prev = 0;
+    CUDA_RUNTIME(cudaGetDevice(&prev));
+    CUDA_RUNTIME(cudaSetDevice(dev_));
+    void *p = nullptr;
+    const cudaError_t e = cudaMalloc(&p, n * sizeof(T));
+    CUDA_RUNTIME(cudaSetDevice(prev));
+    if (e != cudaSuccess) {
+      (void)cudaGetLastError();
+      throw std::bad_alloc();
+    }
+    return static_cast<T *>(p);
+  }
+  void deallocate(T *p, std::size_t) noexcept {
+    if (p) cudaFree(p);
+  }
+  template <class U> bool operator==(const DeviceAllocator<U> &o) const noexcept { return dev_ == o.device(); }
+  template <class U> bool operator!=(const DeviceAllocator<U> &o) const noexcept { return dev_ != o.device(); }
+};

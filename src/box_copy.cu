@@ -1,0 +1,323 @@
+/* box_copy_kernel: the sm_100a data mover behind pack / unpack / translate / halo push (kernels N1, N6, N7 of
+   SURVEY section 8; replaces reference kernels K1-K7: pack_kernel.cuh:5-46, copy.cuh:13-146, packer.cuh:52-69,194-250).
+
+   Differences from the reference kernels that matter on B200:
+   * one launch for ANY number of boxes/quantities/messages (the reference launches one kernel per message and loops
+     over quantities serially inside each thread);
+   * access width chosen per segment from the actual alignment (16 B vectors for y/z faces whose rows start on the
+     128 B-aligned interior; scalar for the 1-3 element rows of x faces), not a per-element switch on elemSize;
+   * flat (row, unit) index space per chunk, so thin rows keep all 32 lanes busy (the reference maps a 3-wide face
+     onto a 4-wide block and idles 25 % of the lanes; a 1-wide face gets one sector per thread either way);
+   * loads are streaming (ld.global.nc.L1::no_allocate) and 4 deep per thread before the stores, so one thread has
+     up to 64 B in flight towards NVLink/HBM;
+   * 64-bit byte offsets (the reference's pack indices overflow past 4 Gi elements);
+   * optional release-signal epilogue so the same launch that stores into a peer's halo also tells it "done". */
+#include "stencil/copy_plan.hpp"
+
+#include <algorithm>
+#include <cstdio>
+
+#include "stencil/cuda_runtime.hpp"
+
+namespace stencil {
+
+namespace {
+
+template <int BYTES> struct VecT;
+template <> struct VecT<16> { typedef uint4 type; };
+template <> struct VecT<8> { typedef uint2 type; };
+template <> struct VecT<4> { typedef unsigned type; };
+template <> struct VecT<2> { typedef unsigned short type; };
+template <> struct VecT<1> { typedef unsigned char type; };
+
+__device__ __forceinline__ uint4 ld_stream(const uint4 *p) {
+  uint4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ uint2 ld_stream(const uint2 *p) {
+  uint2 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ unsigned ld_stream(const unsigned *p) {
+  unsigned v;
+  asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ unsigned short ld_stream(const unsigned short *p) { return __ldg(p); }
+__device__ __forceinline__ unsigned char ld_stream(const unsigned char *p) { return __ldg(p); }
+
+__device__ __forceinline__ void st_release_sys(unsigned *p, unsigned v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned *p) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+constexpr int kThreads = 256;
+constexpr int kUnroll = 4;
+
+/* copy rows [row0, row0+nrows) of one segment with BYTES-wide accesses */
+template <int BYTES>
+__device__ __forceinline__ void copy_chunk(const CopySeg &s, const char *__restrict__ src, char *__restrict__ dst,
+                                           unsigned row0, unsigned nrows) {
+  typedef typename VecT<BYTES>::type V;
+  const unsigned upr = s.rowBytes / BYTES; // units per row
+  const unsigned total = nrows * upr;
+  const unsigned ny = s.ny;
+  for (unsigned base = threadIdx.x; base < total; base += kThreads * kUnroll) {
+    V v[kUnroll];
+    long long doff[kUnroll];
+#pragma unroll
+    for (int k = 0; k < kUnroll; ++k) {
+      const unsigned i = base + k * kThreads;
+      if (i < total) {
+        const unsigned r = i / upr;
+        const unsigned u = i - r * upr;
+        const unsigned row = row0 + r;
+        const unsigned z = row / ny;
+        const unsigned y = row - z * ny;
+        const long long soff = (long long)z * s.srcPitchZ + (long long)y * s.srcPitchY + (long long)u * BYTES;
+        doff[k] = (long long)z * s.dstPitchZ + (long long)y * s.dstPitchY + (long long)u * BYTES;
+        v[k] = ld_stream(reinterpret_cast<const V *>(src + soff));
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < kUnroll; ++k) {
+      const unsigned i = base + k * kThreads;
+      if (i < total) *reinterpret_cast<V *>(dst + doff[k]) = v[k];
+    }
+  }
+}
+
+template <bool SIGNAL>
+__global__ void __launch_bounds__(kThreads)
+    box_copy_kernel(const CopySeg *__restrict__ segs, const CopyChunk *__restrict__ chunks, unsigned nchunks, int parity,
+                    unsigned *done, SignalSet sig, unsigned epoch) {
+  __shared__ CopySeg s;
+  unsigned cached = 0xffffffffu;
+  for (unsigned c = blockIdx.x; c < nchunks; c += gridDim.x) {
+    const CopyChunk ch = chunks[c];
+    if (ch.seg != cached) { // uniform per CTA
+      __syncthreads();
+      if (threadIdx.x < sizeof(CopySeg) / sizeof(unsigned))
+        reinterpret_cast<unsigned *>(&s)[threadIdx.x] = reinterpret_cast<const unsigned *>(&segs[ch.seg])[threadIdx.x];
+      __syncthreads();
+      cached = ch.seg;
+    }
+    const char *src = s.src[parity];
+    char *dst = s.dst[parity];
+    switch (s.vecLog2) {
+    case 4: copy_chunk<16>(s, src, dst, ch.row0, ch.nrows); break;
+    case 3: copy_chunk<8>(s, src, dst, ch.row0, ch.nrows); break;
+    case 2: copy_chunk<4>(s, src, dst, ch.row0, ch.nrows); break;
+    case 1: copy_chunk<2>(s, src, dst, ch.row0, ch.nrows); break;
+    default: copy_chunk<1>(s, src, dst, ch.row0, ch.nrows); break;
+    }
+  }
+  if (SIGNAL) {
+    /* every thread's stores -> CTA barrier -> one system-scope fence -> count this CTA as done.
+       The CTA that observes the full count owns the release stores to the (peer) flags. */
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence_system();
+      const unsigned prev = atomicAdd(done, 1u);
+      if (prev == gridDim.x - 1) {
+        *done = 0; // ready for the next launch on this stream
+        __threadfence_system();
+        for (unsigned k = 0; k < sig.n; ++k) st_release_sys(sig.flag[k], epoch);
+      }
+    }
+  }
+}
+
+__global__ void wait_flags_kernel(WaitSet ws, unsigned epoch, unsigned *errWord, unsigned long long timeoutNs) {
+  const unsigned k = threadIdx.x;
+  if (k >= ws.n) return;
+  const unsigned long long t0 = globaltimer_ns();
+  unsigned backoff = 32;
+  while (int(ld_acquire_sys(ws.flag[k]) - epoch) < 0) {
+    __nanosleep(backoff);
+    if (backoff < 1024) backoff <<= 1;
+    if (globaltimer_ns() - t0 > timeoutNs) {
+      atomicCAS(errWord, 0u, 1u + k);
+      __threadfence_system();
+      return;
+    }
+  }
+}
+
+/* a few boxes whose descriptors arrive as kernel parameters: blockIdx.y = box, blockIdx.x strides over row groups */
+__global__ void __launch_bounds__(kThreads) box_copy_batch_kernel(const __grid_constant__ SegBatch batch, int parity, unsigned rowsPerCta) {
+  const CopySeg &s = batch.seg[blockIdx.y];
+  const unsigned rows = s.ny * s.nz;
+  const char *src = s.src[parity];
+  char *dst = s.dst[parity];
+  for (unsigned row0 = blockIdx.x * rowsPerCta; row0 < rows; row0 += gridDim.x * rowsPerCta) {
+    const unsigned n = min(rowsPerCta, rows - row0);
+    switch (s.vecLog2) {
+    case 4: copy_chunk<16>(s, src, dst, row0, n); break;
+    case 3: copy_chunk<8>(s, src, dst, row0, n); break;
+    case 2: copy_chunk<4>(s, src, dst, row0, n); break;
+    case 1: copy_chunk<2>(s, src, dst, row0, n); break;
+    default: copy_chunk<1>(s, src, dst, row0, n); break;
+    }
+  }
+}
+
+__global__ void signal_flags_kernel(SignalSet sig, unsigned epoch) {
+  if (threadIdx.x < sig.n) {
+    __threadfence_system();
+    st_release_sys(sig.flag[threadIdx.x], epoch);
+  }
+}
+
+unsigned log2_floor_pow2(unsigned long long x) {
+  unsigned l = 0;
+  while (l < 4 && (x % (2ull << l)) == 0) ++l;
+  return l;
+}
+
+} // namespace
+
+CopyPlan::~CopyPlan() {
+  if (dSegs_ || dChunks_ || dDone_) {
+    int prev = 0;
+    if (cudaGetDevice(&prev) == cudaSuccess) {
+      cudaSetDevice(dev_);
+      cudaFree(dSegs_);
+      cudaFree(dChunks_);
+      cudaFree(dDone_);
+      cudaSetDevice(prev);
+    }
+  }
+}
+
+void CopyPlan::swap(CopyPlan &o) noexcept {
+  segs_.swap(o.segs_);
+  chunks_.swap(o.chunks_);
+  std::swap(bytes_, o.bytes_);
+  std::swap(dSegs_, o.dSegs_);
+  std::swap(dChunks_, o.dChunks_);
+  std::swap(dDone_, o.dDone_);
+  std::swap(dev_, o.dev_);
+}
+
+void CopyPlan::clear() {
+  CopyPlan empty;
+  swap(empty);
+}
+
+CopySeg make_seg(const BoxView &src, const Dim3 &srcPos, const BoxView &dst, const Dim3 &dstPos, const Dim3 &ext) {
+  const long long es = (long long)src.elemSize;
+  CopySeg s;
+  for (int p = 0; p < 2; ++p) {
+    s.src[p] = src.base[p] + srcPos.z * src.pitchZ + srcPos.y * src.pitchY + srcPos.x * es;
+    s.dst[p] = dst.base[p] + dstPos.z * dst.pitchZ + dstPos.y * dst.pitchY + dstPos.x * es;
+  }
+  s.srcPitchY = src.pitchY;
+  s.srcPitchZ = src.pitchZ;
+  s.dstPitchY = dst.pitchY;
+  s.dstPitchZ = dst.pitchZ;
+  s.rowBytes = unsigned(ext.x * es);
+  s.ny = unsigned(ext.y);
+  s.nz = unsigned(ext.z);
+  /* widest power-of-two (<= 16 B) dividing every address any row can start at, and the row length */
+  unsigned long long a = s.rowBytes;
+  for (int p = 0; p < 2; ++p) a |= (unsigned long long)(uintptr_t)s.src[p] | (unsigned long long)(uintptr_t)s.dst[p];
+  if (s.ny > 1) a |= (unsigned long long)src.pitchY | (unsigned long long)dst.pitchY;
+  if (s.nz > 1) a |= (unsigned long long)src.pitchZ | (unsigned long long)dst.pitchZ;
+  s.vecLog2 = log2_floor_pow2(a);
+  return s;
+}
+
+void CopyPlan::add(const BoxView &src, const Dim3 &srcPos, const BoxView &dst, const Dim3 &dstPos, const Dim3 &ext) {
+  if (ext.x <= 0 || ext.y <= 0 || ext.z <= 0) return;
+  const CopySeg s = make_seg(src, srcPos, dst, dstPos, ext);
+  segs_.push_back(s);
+  bytes_ += size_t(s.rowBytes) * s.ny * s.nz;
+}
+
+void CopyPlan::finalize(int dev, size_t chunkBytes) {
+  dev_ = dev;
+  chunks_.clear();
+  for (size_t si = 0; si < segs_.size(); ++si) {
+    const CopySeg &s = segs_[si];
+    const unsigned rows = s.ny * s.nz;
+    unsigned per = unsigned(std::max<size_t>(1, chunkBytes / std::max(1u, s.rowBytes)));
+    for (unsigned r = 0; r < rows; r += per) chunks_.push_back(CopyChunk{unsigned(si), r, std::min(per, rows - r), 0});
+  }
+  if (segs_.empty()) return;
+  int prev = 0;
+  CUDA_RUNTIME(cudaGetDevice(&prev));
+  CUDA_RUNTIME(cudaSetDevice(dev_));
+  if (dSegs_) CUDA_RUNTIME(cudaFree(dSegs_));
+  if (dChunks_) CUDA_RUNTIME(cudaFree(dChunks_));
+  if (!dDone_) {
+    CUDA_RUNTIME(cudaMalloc(&dDone_, sizeof(unsigned)));
+    CUDA_RUNTIME(cudaMemset(dDone_, 0, sizeof(unsigned)));
+  }
+  CUDA_RUNTIME(cudaMalloc(&dSegs_, segs_.size() * sizeof(CopySeg)));
+  CUDA_RUNTIME(cudaMalloc(&dChunks_, chunks_.size() * sizeof(CopyChunk)));
+  CUDA_RUNTIME(cudaMemcpy(dSegs_, segs_.data(), segs_.size() * sizeof(CopySeg), cudaMemcpyHostToDevice));
+  CUDA_RUNTIME(cudaMemcpy(dChunks_, chunks_.data(), chunks_.size() * sizeof(CopyChunk), cudaMemcpyHostToDevice));
+  CUDA_RUNTIME(cudaSetDevice(prev));
+}
+
+unsigned CopyPlan::grid_size() const {
+  /* 148 SMs x 8 resident 256-thread CTAs is a full wave on B200; small plans use one CTA per chunk */
+  return unsigned(std::min<size_t>(chunks_.size(), 148 * 8));
+}
+
+void CopyPlan::launch(int parity, cudaStream_t stream) const {
+  if (chunks_.empty()) return;
+  SignalSet none;
+  none.n = 0;
+  box_copy_kernel<false><<<grid_size(), kThreads, 0, stream>>>(dSegs_, dChunks_, unsigned(chunks_.size()), parity, dDone_, none, 0u);
+  CUDA_RUNTIME(cudaGetLastError());
+}
+
+void CopyPlan::launch_and_signal(int parity, const SignalSet &sig, unsigned epoch, cudaStream_t stream) const {
+  if (chunks_.empty()) {
+    /* nothing to move, but neighbours still wait for the flag */
+    launch_signal_flags(sig, epoch, stream);
+    return;
+  }
+  box_copy_kernel<true><<<grid_size(), kThreads, 0, stream>>>(dSegs_, dChunks_, unsigned(chunks_.size()), parity, dDone_, sig, epoch);
+  CUDA_RUNTIME(cudaGetLastError());
+}
+
+void launch_box_copy(const SegBatch &batch, int parity, cudaStream_t stream) {
+  if (batch.n == 0) return;
+  unsigned maxRows = 1, minRowBytes = 0xffffffffu;
+  for (unsigned i = 0; i < batch.n; ++i) {
+    maxRows = std::max(maxRows, batch.seg[i].ny * batch.seg[i].nz);
+    minRowBytes = std::min(minRowBytes, std::max(1u, batch.seg[i].rowBytes));
+  }
+  const unsigned rowsPerCta = std::max(1u, (32u * 1024u) / minRowBytes);
+  const unsigned gx = std::min((maxRows + rowsPerCta - 1) / rowsPerCta, 148u * 8u);
+  box_copy_batch_kernel<<<dim3(gx, batch.n, 1), kThreads, 0, stream>>>(batch, parity, rowsPerCta);
+  CUDA_RUNTIME(cudaGetLastError());
+}
+
+void launch_signal_flags(const SignalSet &sig, unsigned epoch, cudaStream_t stream) {
+  if (sig.n == 0) return;
+  signal_flags_kernel<<<1, 32, 0, stream>>>(sig, epoch);
+  CUDA_RUNTIME(cudaGetLastError());
+}
+
+void launch_wait_flags(const WaitSet &ws, unsigned epoch, unsigned *errWord, unsigned long long timeoutNs, cudaStream_t stream) {
+  if (ws.n == 0) return;
+  wait_flags_kernel<<<1, 32, 0, stream>>>(ws, epoch, errWord, timeoutNs);
+  CUDA_RUNTIME(cudaGetLastError());
+}
+
+} // namespace stencil

@@ -1,0 +1,90 @@
+/* RankPartition / NodePartition. RankPartition expectations are those of the reference's
+   test/test_cpu_partition.cpp; the NodePartition cases (untested there) use the values obtained by running the
+   reference's code on the BASELINE configs. */
+#include "harness.hpp"
+#include "stencil/partition.hpp"
+
+TEST_CASE("rank partition even", "[partition]") {
+  RankPartition p(Dim3(10, 5, 5), 2);
+  REQUIRE(p.dim() == Dim3(2, 1, 1));
+  REQUIRE(p.subdomain_size(Dim3(0, 0, 0)) == Dim3(5, 5, 5));
+  REQUIRE(p.subdomain_size(Dim3(1, 0, 0)) == Dim3(5, 5, 5));
+}
+
+TEST_CASE("rank partition remainders", "[partition]") {
+  RankPartition p(Dim3(10, 3, 1), 4);
+  const int64_t sizes[4] = {3, 3, 2, 2}, origins[4] = {0, 3, 6, 8};
+  for (int i = 0; i < 4; ++i) {
+    REQUIRE(p.subdomain_size(Dim3(i, 0, 0)) == Dim3(sizes[i], 3, 1));
+    REQUIRE(p.subdomain_origin(Dim3(i, 0, 0)) == Dim3(origins[i], 0, 0));
+  }
+  RankPartition q(Dim3(10, 5, 5), 3);
+  REQUIRE(q.subdomain_size(Dim3(0, 0, 0)) == Dim3(4, 5, 5));
+  REQUIRE(q.subdomain_size(Dim3(1, 0, 0)) == Dim3(3, 5, 5));
+  REQUIRE(q.subdomain_size(Dim3(2, 0, 0)) == Dim3(3, 5, 5));
+  RankPartition r(Dim3(13, 7, 7), 4);
+  REQUIRE(r.subdomain_size(Dim3(0, 0, 0)) == Dim3(4, 7, 7));
+  for (int i = 1; i < 4; ++i) REQUIRE(r.subdomain_size(Dim3(i, 0, 0)) == Dim3(3, 7, 7));
+}
+
+TEST_CASE("rank partition 3x3 origins", "[partition]") {
+  RankPartition p(Dim3(10, 14, 2), 9);
+  REQUIRE(p.dim() == Dim3(3, 3, 1));
+  REQUIRE(p.subdomain_origin(Dim3(0, 0, 0)) == Dim3(0, 0, 0));
+  REQUIRE(p.subdomain_origin(Dim3(1, 1, 0)) == Dim3(4, 5, 0));
+  REQUIRE(p.subdomain_origin(Dim3(2, 2, 0)) == Dim3(7, 10, 0));
+  /* tiles cover the domain exactly */
+  int64_t cells = 0;
+  for (int64_t i = 0; i < p.dim().flatten(); ++i) cells += p.subdomain_size(p.dimensionize(i)).flatten();
+  REQUIRE(cells == 10 * 14 * 2);
+  REQUIRE(p.linearize(p.dimensionize(7)) == 7);
+}
+
+static Radius faces(size_t r) {
+  Radius x = Radius::constant(0);
+  x.set_face(r);
+  return x;
+}
+
+TEST_CASE("node partition weak-scaling shapes", "[partition]") {
+  /* jacobi3d weak scaling, face radius 1 */
+  REQUIRE(NodePartition(Dim3(512, 512, 512), faces(1), 1, 1).dim() == Dim3(1, 1, 1));
+  NodePartition p2(Dim3(645, 645, 645), faces(1), 1, 2);
+  REQUIRE(p2.dim() == Dim3(2, 1, 1));
+  REQUIRE(p2.subdomain_size(Dim3(0, 0, 0)) == Dim3(323, 645, 645));
+  REQUIRE(p2.subdomain_size(Dim3(1, 0, 0)) == Dim3(322, 645, 645));
+  NodePartition p4(Dim3(813, 813, 813), faces(1), 1, 4);
+  REQUIRE(p4.dim() == Dim3(2, 2, 1));
+  REQUIRE(p4.subdomain_size(Dim3(0, 0, 0)) == Dim3(407, 407, 813));
+  REQUIRE(p4.subdomain_size(Dim3(1, 1, 0)) == Dim3(406, 406, 813));
+  NodePartition p8(Dim3(1024, 1024, 1024), faces(1), 1, 8);
+  REQUIRE(p8.dim() == Dim3(2, 2, 2));
+  REQUIRE(p8.subdomain_size(Dim3(1, 1, 1)) == Dim3(512, 512, 512));
+  REQUIRE(p8.subdomain_origin(Dim3(1, 0, 1)) == Dim3(512, 0, 512));
+}
+
+TEST_CASE("node partition uneven radius changes the cut order", "[partition]") {
+  Radius r = Radius::constant(1);
+  r.dir(1, 0, 0) = 2; // +x=2, -x=1 => x interface weighted 3, y/z weighted 2
+  REQUIRE(NodePartition(Dim3(1024, 1024, 1024), r, 1, 2).dim() == Dim3(1, 2, 1));
+  REQUIRE(NodePartition(Dim3(1024, 1024, 1024), r, 1, 4).dim() == Dim3(1, 2, 2));
+  REQUIRE(NodePartition(Dim3(1024, 1024, 1024), r, 1, 8).dim() == Dim3(2, 2, 2));
+  REQUIRE(RankPartition(Dim3(1024, 1024, 1024), 2).dim() == Dim3(2, 1, 1));
+}
+
+TEST_CASE("node partition two levels and odd sizes", "[partition]") {
+  NodePartition p(Dim3(1024, 1024, 1024), Radius::constant(3), 2, 4);
+  REQUIRE(p.sys_dim() == Dim3(2, 1, 1));
+  REQUIRE(p.node_dim() == Dim3(1, 2, 2));
+  REQUIRE(p.dim() == Dim3(2, 2, 2));
+  NodePartition q(Dim3(1023, 1024, 1025), Radius::constant(1), 1, 8);
+  REQUIRE(q.subdomain_size(Dim3(0, 0, 0)) == Dim3(512, 512, 513));
+  REQUIRE(q.subdomain_size(Dim3(1, 1, 1)) == Dim3(511, 512, 512));
+  NodePartition s(Dim3(1000, 1000, 1000), Radius::constant(1), 1, 6);
+  REQUIRE(s.dim() == Dim3(3, 2, 1));
+  REQUIRE(s.subdomain_size(Dim3(0, 0, 0)) == Dim3(334, 500, 1000));
+  REQUIRE(s.subdomain_size(Dim3(2, 1, 0)) == Dim3(333, 500, 1000));
+  REQUIRE(s.sys_idx(0) == Dim3(0, 0, 0));
+  REQUIRE(s.node_idx(4) == Dim3(1, 1, 0));
+  REQUIRE(s.idx(5) == Dim3(2, 1, 0));
+}
