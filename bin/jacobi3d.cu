@@ -1,0 +1,101 @@
+/* jacobi3d: 7-point Jacobi heat solver, weak-scaled by the number of subdomains.
+   CLI and CSV line follow the reference's bin/jacobi3d.cu:110-128,378-379:
+     jacobi3d X Y Z [--iters/-n N] [--staged --colo --peer --kernel --direct] [--trivial] [--no-overlap]
+              [--paraview --prefix P --period/-q Q]
+   prints on rank 0:  jacobi3d,<methods>,<ranks>,<devCount>,<x>,<y>,<z>,<min iter s>,<trimean iter s>
+   Additions: --direct (MethodFlags::NvlinkDirect), --no-fused (use the reference's exchange() schedule instead of
+   the fused compute+push kernel), --exact-size (do not weak-scale the positional size), --tile-z. */
+#include <cmath>
+#include <iostream>
+
+#include "stencil/argparse.hpp"
+#include "stencil/jacobi.hpp"
+#include "stencil/statistics.hpp"
+
+int main(int argc, char **argv) {
+  bool useStaged = false, useColo = false, usePeer = false, useKernel = false, useDirect = false;
+  bool trivial = false, noOverlap = false, paraview = false, noFused = false, exactSize = false;
+  size_t x = 512, y = 512, z = 512;
+  std::string prefix;
+  int iters = 30, period = -1, tileZ = 32;
+
+  argparse::Parser parser("7-point Jacobi on a periodic box with a hot and a cold sphere");
+  parser.add_flag(useStaged, "--staged")->help("enable the host-staged transport (CudaMpi)");
+  parser.add_flag(useColo, "--colo")->help("enable the colocated IPC transport (CudaMpiColocated)");
+  parser.add_flag(usePeer, "--peer")->help("enable pack + cudaMemcpyPeer (CudaMemcpyPeer)");
+  parser.add_flag(useKernel, "--kernel")->help("enable same-GPU copies (CudaKernel)");
+  parser.add_flag(useDirect, "--direct")->help("enable device-initiated NVLink stores (NvlinkDirect)");
+  parser.add_flag(trivial, "--trivial")->help("skip node-aware placement");
+  parser.add_flag(noOverlap, "--no-overlap")->help("don't overlap communication and computation");
+  parser.add_flag(noFused, "--no-fused")->help("use exchange() + separate kernels instead of the fused kernel");
+  parser.add_flag(exactSize, "--exact-size")->help("use X Y Z as the whole domain (no weak scaling)");
+  parser.add_option(prefix, "--prefix")->help("prefix for paraview files");
+  parser.add_flag(paraview, "--paraview")->help("dump paraview files");
+  parser.add_option(iters, "--iters", "-n")->help("number of iterations");
+  parser.add_option(period, "--period", "-q")->help("iterations between checkpoints");
+  parser.add_option(tileZ, "--tile-z")->help("planes marched per CTA");
+  parser.add_positional(x)->required();
+  parser.add_positional(y)->required();
+  parser.add_positional(z)->required();
+  if (!parser.parse(argc, argv)) {
+    std::cerr << parser.help() << "\n";
+    return EXIT_FAILURE;
+  }
+  if (parser.need_help()) {
+    std::cerr << parser.help() << "\n";
+    return 0;
+  }
+  if (period <= 0) period = std::max(1, iters / 10);
+
+  stencil::Comm &comm = stencil::world();
+  const int rank = comm.rank(), size = comm.size();
+  int devCount = 0;
+  CUDA_RUNTIME(cudaGetDeviceCount(&devCount));
+  int numSubdoms;
+  {
+    MpiTopology topo(comm);
+    numSubdoms = size / topo.colocated_size() * devCount;
+  }
+  if (rank == 0) std::cerr << "assuming " << numSubdoms << " subdomains\n";
+  if (!exactSize) {
+    const double s = std::pow(double(numSubdoms), 0.33333);
+    x = size_t(double(x) * s + 0.5);
+    y = size_t(double(y) * s + 0.5);
+    z = size_t(double(z) * s + 0.5);
+  }
+
+  MethodFlags methods = MethodFlags::None;
+  if (useStaged) methods |= MethodFlags::CudaMpi;
+  if (useColo) methods |= MethodFlags::CudaMpiColocated;
+  if (usePeer) methods |= MethodFlags::CudaMemcpyPeer;
+  if (useKernel) methods |= MethodFlags::CudaKernel;
+  if (useDirect) methods |= MethodFlags::NvlinkDirect;
+  if (methods == MethodFlags::None) methods = MethodFlags::All;
+
+  Statistics iterTime;
+  {
+    stencil::Jacobi3D::Options opt;
+    opt.methods = methods;
+    opt.placement = trivial ? PlacementStrategy::Trivial : PlacementStrategy::NodeAware;
+    opt.mode = noOverlap ? stencil::Jacobi3D::Mode::NoOverlap : (noFused ? stencil::Jacobi3D::Mode::Overlap : stencil::Jacobi3D::Mode::Fused);
+    opt.tileZ = tileZ;
+    opt.planFile = true;
+    stencil::Jacobi3D solver(x, y, z, opt);
+    comm.barrier();
+    if (paraview) solver.domain().write_paraview(prefix + "jacobi3d_init");
+    for (int iter = 0; iter < iters; ++iter) {
+      /* per-iteration time as the reference measures it: wall clock around launch .. completion, max over ranks */
+      const double t0 = stencil::Comm::wtime();
+      solver.step();
+      solver.sync();
+      iterTime.insert(comm.allreduce_max(stencil::Comm::wtime() - t0));
+      if (paraview && iter % period == 0) solver.domain().write_paraview(prefix + "jacobi3d_" + std::to_string(iter));
+    }
+    if (paraview) solver.domain().write_paraview(prefix + "jacobi3d_final");
+  }
+  if (rank == 0)
+    std::cout << "jacobi3d," << method_string(methods) << "," << size << "," << devCount << "," << x << "," << y << "," << z << ","
+              << iterTime.min() << "," << iterTime.trimean() << "\n";
+  stencil::finalize_world();
+  return 0;
+}

@@ -1,0 +1,81 @@
+#pragma once
+/* Jacobi3D: the 7-point Jacobi heat solver of the reference's bin/jacobi3d.cu (fp32, face radius 1, hot and cold
+   Dirichlet spheres standing in for boundary conditions, periodic domain) as a reusable engine, so the CLI app,
+   the C ABI / Python binding and bench.py all run the same code.
+
+   Reference behaviour kept (bin/jacobi3d.cu:18-87, :205-352): init to (HOT+COLD)/2 = 0.5; a cell within
+   sphereRadius = X/10 of the hot centre (X/3, Y/2, Z/2) is 1, of the cold centre (2X/3, Y/2, Z/2) is 0, where the
+   distance is truncated to an integer; otherwise the cell becomes (+x + -x + +y + -y + +z + -z) / 6 in exactly that
+   summation order (bit-exact against a host loop). Three execution modes:
+
+     Mode::Fused     (default) ONE kernel per subdomain per iteration computes the whole compute region; tiles on a
+                     subdomain face also store their results straight into the neighbour GPU's `next` halo over
+                     NVLink and the last boundary tile raises the neighbour's epoch flag. No exchange() call, no
+                     host synchronisation inside the loop; boundary tiles are scheduled first so the transfer hides
+                     behind the interior tiles. (N2 + N3.)
+     Mode::Overlap   the reference's schedule: interior kernel, exchange(), exterior slabs, synchronise, swap.
+     Mode::NoOverlap exchange(), whole-region kernel, synchronise, swap (reference --no-overlap). */
+#include <memory>
+#include <vector>
+
+#include "stencil/stencil.hpp"
+
+namespace stencil {
+
+class Jacobi3D {
+public:
+  enum class Mode { Fused, Overlap, NoOverlap };
+  struct Options {
+    MethodFlags methods = MethodFlags::All;
+    PlacementStrategy placement = PlacementStrategy::NodeAware;
+    Mode mode = Mode::Fused;
+    std::vector<int> gpus; // empty: the rank's default devices
+    int tileZ = 32;        // z-extent of a tile (planes marched per CTA)
+    bool planFile = false;
+  };
+
+  Jacobi3D(size_t x, size_t y, size_t z, const Options &opt);
+  Jacobi3D(size_t x, size_t y, size_t z, const Options &opt, Comm &comm);
+  ~Jacobi3D();
+
+  DistributedDomain &domain() { return *dd_; }
+  const DataHandle<float> &handle() const { return h_; }
+  Mode mode() const { return opt_.mode; }
+
+  /* curr = 0.5 on every compute region (halos are filled by the first exchange / fused step) */
+  void init();
+  /* enqueue one iteration and swap. Fused mode does not block the host. */
+  void step();
+  /* One iteration with per-step host I/O, all stream-ordered (no host blocking): first copy `nbytes`
+     (<= kParamBytes) of run-time parameters from PINNED host memory to every local GPU — floats [0] hot sphere
+     temperature, [1] cold sphere temperature — then step(), then copy the new value at the centre of each local
+     compute region to resultPinned[di] (pinned). Call sync() before reading the results. */
+  static constexpr size_t kParamBytes = 64;
+  void step_io(const void *paramsPinned, size_t nbytes, float *resultPinned);
+  /* block until every local GPU finished all enqueued iterations */
+  void sync();
+  /* run `iters` iterations and return the device time in seconds: CUDA events per local GPU around the whole
+     batch, max over GPUs and over ranks */
+  double run(int iters);
+  /* kernels enqueued by this object so far (all local GPUs) */
+  unsigned long long launches() const { return launches_; }
+
+  /* sum of curr over the compute regions of all ranks (fp64 accumulation) */
+  double checksum();
+  /* value at global coordinate p if this rank owns it (returns false otherwise) */
+  bool probe(const Dim3 &p, float *out);
+
+private:
+  struct Impl;
+  void build(size_t x, size_t y, size_t z, Comm *comm);
+  Options opt_;
+  std::unique_ptr<DistributedDomain> dd_;
+  DataHandle<float> h_;
+  std::unique_ptr<Impl> impl_;
+  unsigned long long launches_ = 0;
+};
+
+/* host reference of one Jacobi iteration on a dense periodic X*Y*Z array (same arithmetic and order as the kernel) */
+void jacobi_host_step(std::vector<float> &next, const std::vector<float> &curr, const Dim3 &size);
+
+} // namespace stencil

@@ -72,6 +72,19 @@ std::string method_string(MethodFlags m, const char *sep = "/");
 namespace stencil {
 class Exchanger; // owns plans, transports, streams (src/stencil.cu)
 
+/* What a device-initiated (fused compute + push) kernel needs to know about the subdomain on side `dir` of a local
+   subdomain: a strided view of one of its quantities as seen from the local GPU (a peer / IPC-mapped address when
+   it lives elsewhere), its control-block flag words, and where it runs. `reachable` is false when the neighbour
+   is on another node or peer access is unavailable (then only exchange() can talk to it). */
+struct NeighborInfo {
+  bool exists = false;    // false across a non-periodic global boundary
+  bool reachable = false; // loads/stores from the local GPU work
+  bool sameRank = false, sameDevice = false;
+  int rank = -1, dom = -1, dev = -1;
+  Dim3 idx, size;
+  BoxView view;             // base[b] = buffer b (0/1) of the quantity, logical element (0,0,0)
+  unsigned *control = nullptr; // the neighbour's control block (LocalDomain::kControlBytes), as mapped locally
+};
 } // namespace stencil
 
 class DistributedDomain {
@@ -155,6 +168,8 @@ public:
   /* number of completed exchange() calls (the epoch published in the arrival flags) */
   unsigned epoch() const noexcept;
   stencil::Exchanger *exchanger() const noexcept { return ex_.get(); }
+  /* neighbour of local subdomain di on side dir, for quantity qi (valid after realize()) */
+  stencil::NeighborInfo neighbor(size_t di, const Dim3 &dir, size_t qi);
 
   /* accumulated max-over-ranks seconds; valid on rank 0 (exchange/swap only with STENCIL_EXCHANGE_STATS or
      set_exchange_stats(true): they add a barrier per call) */

@@ -253,6 +253,30 @@ public:
   }
 
   cudaStream_t stream(size_t i) const { return streams_.at(i); }
+
+  NeighborInfo neighbor(size_t di, const Dim3 &dir, size_t qi) {
+    NeighborInfo n;
+    Placement *pl = dd_.placement_.get();
+    const Dim3 grid = pl->dim();
+    const Where me = where(pl->get_idx(dd_.rank_, int(di)));
+    if (crosses_open_boundary(me.idx, dir, grid)) return n;
+    const Where nb = where((me.idx + dir).wrapped(grid));
+    n.exists = true;
+    n.rank = nb.rank;
+    n.dom = nb.dom;
+    n.dev = nb.dev;
+    n.idx = nb.idx;
+    n.size = pl->subdomain_size(nb.idx);
+    n.sameRank = nb.rank == dd_.rank_;
+    n.sameDevice = nb.dev == me.dev;
+    const bool sameNode = n.sameRank || dd_.topo_->colocated(nb.rank);
+    n.reachable = sameNode && (n.sameDevice || gpu_topo::peer(me.dev, nb.dev)) && (n.sameRank || !n.sameDevice);
+    if (n.reachable) {
+      n.view = view_of(nb, qi, me.dev);
+      n.control = flags_of(nb, me.dev);
+    }
+    return n;
+  }
   unsigned epoch() const { return epoch_; }
   const std::vector<PlanLine> &plan_lines() const { return planLines_; }
 
@@ -703,6 +727,8 @@ Dim3 DistributedDomain::get_subdomain_idx(int64_t i) const { return placement_->
 Dim3 DistributedDomain::subdomain_grid() const { return placement_->dim(); }
 cudaStream_t DistributedDomain::exchange_stream(size_t i) const { return ex_->stream(i); }
 unsigned DistributedDomain::epoch() const noexcept { return ex_ ? ex_->epoch() : 0; }
+
+stencil::NeighborInfo DistributedDomain::neighbor(size_t di, const Dim3 &dir, size_t qi) { return ex_->neighbor(di, dir, qi); }
 
 uint64_t DistributedDomain::exchange_bytes_for_method(const MethodFlags &m) const {
   uint64_t r = 0;

@@ -1,0 +1,116 @@
+/* Jacobi3D engine against the host loop, bit for bit, in all three schedules (fused push, reference-style
+   overlap, no overlap), with 1..8 subdomains on GPU 0, uneven sizes, and on every visible GPU. */
+#include "harness.hpp"
+#include <cmath>
+#include <cstring>
+#include <vector>
+#include "stencil/jacobi.hpp"
+
+namespace {
+
+std::vector<float> gather(stencil::Jacobi3D &j) {
+  DistributedDomain &dd = j.domain();
+  const Dim3 g = dd.size();
+  std::vector<float> out(size_t(g.flatten()), -7.f);
+  j.sync();
+  for (LocalDomain &ld : dd.domains()) {
+    const std::vector<unsigned char> b = ld.interior_to_host(0);
+    const float *v = reinterpret_cast<const float *>(b.data());
+    const Dim3 sz = ld.size(), o = ld.origin();
+    size_t i = 0;
+    for (int64_t z = 0; z < sz.z; ++z)
+      for (int64_t y = 0; y < sz.y; ++y)
+        for (int64_t x = 0; x < sz.x; ++x) out[size_t(((o.z + z) * g.y + o.y + y) * g.x + o.x + x)] = v[i++];
+  }
+  return out;
+}
+
+size_t mismatches(const Dim3 &size, stencil::Jacobi3D::Mode mode, const std::vector<int> &gpus, int iters, int tileZ = 32,
+                  MethodFlags methods = MethodFlags::All) {
+  stencil::Jacobi3D::Options opt;
+  opt.mode = mode;
+  opt.gpus = gpus;
+  opt.tileZ = tileZ;
+  opt.methods = methods;
+  stencil::Jacobi3D j(size_t(size.x), size_t(size.y), size_t(size.z), opt);
+  std::vector<float> ref(size_t(size.flatten()), 0.5f), tmp;
+  size_t bad = 0;
+  for (int it = 0; it < iters; ++it) {
+    j.step();
+    stencil::jacobi_host_step(tmp, ref, size);
+    ref.swap(tmp);
+    if (it == 0 || it == iters - 1) {
+      const std::vector<float> got = gather(j);
+      for (size_t i = 0; i < got.size(); ++i) bad += std::memcmp(&got[i], &ref[i], 4) != 0;
+    }
+  }
+  return bad;
+}
+
+int device_count() {
+  int n = 0;
+  cudaGetDeviceCount(&n);
+  return n;
+}
+
+} // namespace
+
+TEST_CASE("jacobi: one subdomain, all schedules, bit exact", "[cuda][jacobi]") {
+  using M = stencil::Jacobi3D::Mode;
+  for (M m : {M::Fused, M::Overlap, M::NoOverlap}) {
+    REQUIRE(mismatches(Dim3(40, 24, 20), m, {0}, 6) == 0);
+    REQUIRE(mismatches(Dim3(130, 17, 9), m, {0}, 4, 4) == 0);   // partial x tile, partial row block, short z tiles
+    REQUIRE(mismatches(Dim3(257, 33, 35), m, {0}, 3, 16) == 0); // three x tiles, last one a single column
+  }
+}
+
+TEST_CASE("jacobi: 2, 3, 4 and 8 subdomains on GPU 0", "[cuda][jacobi]") {
+  using M = stencil::Jacobi3D::Mode;
+  for (M m : {M::Fused, M::Overlap, M::NoOverlap}) {
+    REQUIRE(mismatches(Dim3(40, 24, 20), m, {0, 0}, 6) == 0);
+    REQUIRE(mismatches(Dim3(41, 23, 19), m, {0, 0, 0}, 5, 8) == 0);
+    REQUIRE(mismatches(Dim3(64, 30, 22), m, {0, 0, 0, 0}, 5, 8) == 0);
+    REQUIRE(mismatches(Dim3(36, 34, 30), m, {0, 0, 0, 0, 0, 0, 0, 0}, 5, 8) == 0);
+  }
+}
+
+TEST_CASE("jacobi: legacy transports under the reference schedule", "[cuda][jacobi]") {
+  using M = stencil::Jacobi3D::Mode;
+  REQUIRE(mismatches(Dim3(40, 24, 20), M::Overlap, {0, 0}, 4, 32, MethodFlags::CudaMpi) == 0);
+  REQUIRE(mismatches(Dim3(40, 24, 20), M::Overlap, {0, 0}, 4, 32, MethodFlags::CudaMemcpyPeer) == 0);
+  REQUIRE(mismatches(Dim3(40, 24, 20), M::NoOverlap, {0, 0, 0, 0}, 4, 32, MethodFlags::CudaKernel | MethodFlags::CudaMpi) == 0);
+}
+
+TEST_CASE("jacobi: hot and cold spheres appear and the field stays in [0,1]", "[cuda][jacobi]") {
+  stencil::Jacobi3D::Options opt;
+  opt.gpus = {0};
+  stencil::Jacobi3D j(60, 30, 30, opt);
+  for (int i = 0; i < 10; ++i) j.step();
+  float hot = -1, cold = -1, far = -1;
+  REQUIRE(j.probe(Dim3(20, 15, 15), &hot));
+  REQUIRE(j.probe(Dim3(40, 15, 15), &cold));
+  REQUIRE(j.probe(Dim3(0, 0, 0), &far));
+  REQUIRE(hot == 1.0f);
+  REQUIRE(cold == 0.0f);
+  REQUIRE(far == 0.5f); // ten steps cannot reach the corner
+  const double sum = j.checksum();
+  REQUIRE(sum > 0.45 * 60 * 30 * 30);
+  REQUIRE(sum < 0.55 * 60 * 30 * 30);
+  REQUIRE(j.launches() >= 10);
+}
+
+TEST_CASE("jacobi: every visible GPU, fused NVLink pushes", "[cuda][jacobi][multigpu]") {
+  const int n = device_count();
+  if (n < 2) {
+    std::printf("  (1 GPU visible: multi-GPU fused path not exercised)\n");
+    return;
+  }
+  std::vector<int> gpus;
+  for (int i = 0; i < n; ++i) gpus.push_back(i);
+  using M = stencil::Jacobi3D::Mode;
+  REQUIRE(mismatches(Dim3(70, 40, 36), M::Fused, gpus, 8, 8) == 0);
+  REQUIRE(mismatches(Dim3(70, 40, 36), M::Overlap, gpus, 4, 8) == 0);
+  std::vector<int> twice = gpus;
+  twice.insert(twice.end(), gpus.begin(), gpus.end());
+  REQUIRE(mismatches(Dim3(70, 40, 36), M::Fused, twice, 8, 8) == 0);
+}

@@ -1,0 +1,124 @@
+"""CPU-side checks of the Python binding: partition / QAP / placement through the C ABI, Statistics, the process
+group over loopback with 2 real processes, and the host Jacobi loop."""
+import os
+import subprocess
+import sys
+import textwrap
+
+import numpy as np
+
+FACES1 = {(1, 0, 0): 1, (-1, 0, 0): 1, (0, 1, 0): 1, (0, -1, 0): 1, (0, 0, 1): 1, (0, 0, -1): 1}
+
+
+def test_version_and_loader(built):
+    import stencil2_b200
+    assert stencil2_b200.version().startswith("stencil-b200")
+    assert os.path.exists(stencil2_b200.library_path())
+
+
+def test_rank_partition_matches_reference_cases(built):
+    from stencil2_b200.parallel import RankPartition
+    p = RankPartition((10, 3, 1), 4)
+    assert p.dim == (4, 1, 1)
+    assert [p.subdomain((i, 0, 0)) for i in range(4)] == [((3, 3, 1), (0, 0, 0)), ((3, 3, 1), (3, 0, 0)), ((2, 3, 1), (6, 0, 0)), ((2, 3, 1), (8, 0, 0))]
+    q = RankPartition((10, 14, 2), 9)
+    assert q.dim == (3, 3, 1)
+    assert q.subdomain((1, 1, 0))[1] == (4, 5, 0)
+    assert q.subdomain((2, 2, 0))[1] == (7, 10, 0)
+
+
+def test_node_partition_baseline_configs(built):
+    from stencil2_b200.parallel import NodePartition
+    assert NodePartition((1024,) * 3, FACES1, 1, 8).dim == (2, 2, 2)
+    p2 = NodePartition((645,) * 3, FACES1, 1, 2)
+    assert p2.subdomain((0, 0, 0))[0] == (323, 645, 645) and p2.subdomain((1, 0, 0))[0] == (322, 645, 645)
+    p4 = NodePartition((813,) * 3, FACES1, 1, 4)
+    assert p4.dim == (2, 2, 1) and p4.subdomain((1, 1, 0))[0] == (406, 406, 813)
+    uneven = {d: 1 for d in [(x, y, z) for x in (-1, 0, 1) for y in (-1, 0, 1) for z in (-1, 0, 1)]}
+    uneven[(1, 0, 0)] = 2
+    assert NodePartition((1024,) * 3, uneven, 1, 2).dim == (1, 2, 1)
+    two = NodePartition((1024,) * 3, 3, 2, 4)
+    assert two.sys_dim == (2, 1, 1) and two.node_dim == (1, 2, 2)
+
+
+def test_qap_pinned_permutations(built):
+    from stencil2_b200.parallel import qap_solve
+    inf = float("inf")
+    bw = [[900, 75, 64, 64], [75, 900, 64, 64], [64, 64, 900, 75], [64, 64, 75, 900]]
+    comm = [[7, 5, 10, 1], [5, 7, 1, 10], [10, 1, 7, 5], [1, 10, 5, 7]]
+    dist = [[(inf if v == 0 else 1.0 / v) for v in row] for row in bw]
+    f, c = qap_solve(comm, dist, exact=True)
+    assert f == [0, 2, 1, 3]
+    g, c2 = qap_solve(comm, dist, exact=False)
+    assert g == [3, 1, 2, 0]
+    assert abs(c - c2) < 1e-12
+
+
+def test_placement_512_cubed_on_synthetic_8gpu_topologies(built):
+    """BASELINE config 1: 512^3 partition + QAP placement on synthetic 8-GPU NVLink topologies, no GPU."""
+    from stencil2_b200.parallel import place_node_aware
+    n = 8
+    uniform = [[10.0 if i == j else 1.0 for j in range(n)] for i in range(n)]
+    cuda, dim = place_node_aware((512, 512, 512), 3, uniform)
+    assert dim == (2, 2, 2) and cuda == list(range(8))  # NVSwitch: identity
+    # two islands of four GPUs with interleaved numbering: {0,2,4,6} and {1,3,5,7}
+    isl = [[100.0 if i == j else (25.0 if i % 2 == j % 2 else 1.0) for j in range(n)] for i in range(n)]
+    cuda, dim = place_node_aware((512, 512, 1024), 3, isl)
+    # the heaviest interfaces must stay inside an island: subdomains that are x- or y-neighbours (512x1024 / 2 faces)
+    sub = lambda x, y, z: cuda[x + dim[0] * (y + dim[1] * z)]
+    assert sorted(cuda) == list(range(8))
+    heavy_cross = 0
+    for z in range(dim[2]):
+        for y in range(dim[1]):
+            for x in range(dim[0]):
+                for dx, dy, dz in ((1, 0, 0), (0, 1, 0), (0, 0, 1)):
+                    a = sub(x, y, z)
+                    b = sub((x + dx) % dim[0], (y + dy) % dim[1], (z + dz) % dim[2])
+                    if a != b and a % 2 != b % 2:
+                        heavy_cross += 1
+    # a 2x2x2 grid cut into two islands of four always has exactly one axis crossing: 4 pairs x 1 axis
+    # (each counted from both ends here) — any more means a heavier face than necessary went over the slow link
+    assert heavy_cross == 8
+
+
+def test_statistics_trimean(built):
+    from stencil2_b200.utils import Statistics
+    s = Statistics()
+    for v in [4, 1, 3, 2, 5, 8, 7, 6]:
+        s.insert(v)
+    assert s.trimean() == (3 + 2 * 5 + 7) / 4 and s.med() == 4.5 and s.min() == 1 and s.max() == 8
+
+
+def test_host_jacobi_step_properties(built):
+    from stencil2_b200.models import jacobi_host_step
+    a = np.full((20, 30, 60), 0.5, dtype=np.float32)
+    b = jacobi_host_step(a)
+    assert b.shape == a.shape
+    assert b[10, 15, 20] == 1.0 and b[10, 15, 40] == 0.0  # hot / cold centres (z=Z/2, y=Y/2, x=X/3 | 2X/3)
+    assert b[0, 0, 0] == 0.5
+    # radius X/10 = 6, truncated distance: a cell at distance 6.9 is inside, at 7.0 is outside
+    assert b[10, 15, 26] == 1.0 and b[10, 15, 27] != 1.0
+
+
+def test_two_process_tcp_group(built, tmp_path):
+    """world_size 2 on this machine: the native Comm joins through MASTER_ADDR/MASTER_PORT like under torchrun."""
+    script = tmp_path / "w.py"
+    script.write_text(textwrap.dedent(f"""
+        import sys
+        sys.path.insert(0, {built!r})
+        from stencil2_b200.parallel import comm
+        r, n = comm.init_from_env()
+        assert n == 2 and comm.rank() == r
+        assert comm.allreduce_max(float(r)) == 1.0
+        comm.barrier()
+        comm.finalize()
+        print("ok", r)
+    """))
+    port = 24000 + os.getpid() % 2000
+    procs = []
+    for r in range(2):
+        env = dict(os.environ, RANK=str(r), WORLD_SIZE="2", MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), LOCAL_RANK=str(r))
+        procs.append(subprocess.Popen([sys.executable, str(script)], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True))
+    outs = [p.communicate(timeout=120)[0] for p in procs]
+    assert all(p.returncode == 0 for p in procs), outs
+    assert "ok 0" in outs[0] and "ok 1" in outs[1]

@@ -1,0 +1,62 @@
+"""GPU checks through the Python binding (the same path bench.py and smoke() use)."""
+import json
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def test_smoke_entry(built):
+    import __graft_entry__
+    __graft_entry__.smoke()
+
+
+def test_jacobi_modes_agree_with_host(built):
+    from stencil2_b200.models import Jacobi3D, jacobi_host_step
+    size = (70, 20, 18)
+    ref = np.full((size[2], size[1], size[0]), 0.5, dtype=np.float32)
+    for _ in range(5):
+        ref = jacobi_host_step(ref)
+    for mode in (Jacobi3D.FUSED, Jacobi3D.OVERLAP, Jacobi3D.NO_OVERLAP):
+        j = Jacobi3D(*size, gpus=[0, 0, 0], mode=mode, tile_z=8)
+        for _ in range(5):
+            j.step()
+        assert np.array_equal(j.gather(), ref), f"mode {mode}"
+        assert abs(j.checksum() - float(ref.astype(np.float64).sum())) < 1e-6 * ref.size
+        j.close()
+
+
+def test_ops_pack_and_reduce_against_numpy(built):
+    import torch
+    from stencil2_b200.ops import pack, unpack, reduce_sum_f32
+    src = torch.arange(40 * 12 * 9, dtype=torch.float32, device="cuda").reshape(9, 12, 40)
+    dst = torch.zeros(4, 5, 16, dtype=torch.float32, device="cuda")
+    pack(dst.data_ptr(), src.data_ptr(), (40, 12, 9), (8, 3, 2), (16, 5, 4), 4)
+    torch.cuda.synchronize()
+    assert torch.equal(dst, src[2:6, 3:8, 8:24])
+    back = torch.zeros_like(src)
+    unpack(back.data_ptr(), (40, 12, 9), (8, 3, 2), (16, 5, 4), dst.data_ptr(), 4)
+    torch.cuda.synchronize()
+    assert torch.equal(back[2:6, 3:8, 8:24], dst) and back.sum().item() == dst.sum().item()
+    field = torch.rand(33, 47, 200, dtype=torch.float32, device="cuda")
+    got = reduce_sum_f32(field.data_ptr() + 4 * 3, (200, 47, 33), (150, 47, 33))
+    want = field[:, :, 3:153].to(torch.float64).sum().item()
+    assert abs(got - want) <= 1e-9 * abs(want)
+
+
+def test_bench_contract_small(built):
+    """bench.py prints one JSON line with the contract's keys (tiny size so it finishes in seconds)."""
+    r = subprocess.run([sys.executable, os.path.join(built, "bench.py"), "--gpus", "1", "--steps", "4", "--warmup", "3", "--size", "96"],
+                       stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-3000:]
+    line = [l for l in r.stdout.splitlines() if l.startswith("{")][-1]
+    out = json.loads(line)
+    for k in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "vs_baseline", "dtype",
+              "data", "config", "clocks", "e2e", "gpu_launches"):
+        assert k in out, k
+    assert out["value"] > 0 and out["e2e"]["value"] > 0 and out["gpu_launches"] >= 4
+    assert out["e2e"]["h2d_bytes_per_step"] > 0 and out["e2e"]["d2h_bytes_per_step"] > 0
