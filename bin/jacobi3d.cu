@@ -14,7 +14,7 @@
 
 int main(int argc, char **argv) {
   bool useStaged = false, useColo = false, usePeer = false, useKernel = false, useDirect = false;
-  bool trivial = false, noOverlap = false, paraview = false, noFused = false, exactSize = false;
+  bool trivial = false, noOverlap = false, paraview = false, noFused = false, exactSize = false, ldg = false, boundaryFirst = false;
   size_t x = 512, y = 512, z = 512;
   std::string prefix;
   int iters = 30, period = -1, tileZ = 32;
@@ -28,6 +28,8 @@ int main(int argc, char **argv) {
   parser.add_flag(trivial, "--trivial")->help("skip node-aware placement");
   parser.add_flag(noOverlap, "--no-overlap")->help("don't overlap communication and computation");
   parser.add_flag(noFused, "--no-fused")->help("use exchange() + separate kernels instead of the fused kernel");
+  parser.add_flag(ldg, "--ldg")->help("use the plain-load kernel variant instead of the TMA pipeline");
+  parser.add_flag(boundaryFirst, "--boundary-first")->help("schedule pushing tiles before interior tiles");
   parser.add_flag(exactSize, "--exact-size")->help("use X Y Z as the whole domain (no weak scaling)");
   parser.add_option(prefix, "--prefix")->help("prefix for paraview files");
   parser.add_flag(paraview, "--paraview")->help("dump paraview files");
@@ -79,6 +81,8 @@ int main(int argc, char **argv) {
     opt.placement = trivial ? PlacementStrategy::Trivial : PlacementStrategy::NodeAware;
     opt.mode = noOverlap ? stencil::Jacobi3D::Mode::NoOverlap : (noFused ? stencil::Jacobi3D::Mode::Overlap : stencil::Jacobi3D::Mode::Fused);
     opt.tileZ = tileZ;
+    opt.useTma = !ldg;
+    opt.boundaryFirst = boundaryFirst;
     opt.planFile = true;
     stencil::Jacobi3D solver(x, y, z, opt);
     comm.barrier();

@@ -11,8 +11,8 @@
      Mode::Fused     (default) ONE kernel per subdomain per iteration computes the whole compute region; tiles on a
                      subdomain face also store their results straight into the neighbour GPU's `next` halo over
                      NVLink and the last boundary tile raises the neighbour's epoch flag. No exchange() call, no
-                     host synchronisation inside the loop; boundary tiles are scheduled first so the transfer hides
-                     behind the interior tiles. (N2 + N3.)
+                     host synchronisation inside the loop; the stores to the neighbours are spread over the whole
+                     kernel, so the transfer hides behind the computation. (N2 + N3.)
      Mode::Overlap   the reference's schedule: interior kernel, exchange(), exterior slabs, synchronise, swap.
      Mode::NoOverlap exchange(), whole-region kernel, synchronise, swap (reference --no-overlap). */
 #include <memory>
@@ -31,6 +31,8 @@ public:
     Mode mode = Mode::Fused;
     std::vector<int> gpus; // empty: the rank's default devices
     int tileZ = 32;        // z-extent of a tile (planes marched per CTA)
+    bool useTma = true;    // TMA + mbarrier pipelined kernel (false: plain LDG variant, kept for comparison)
+    bool boundaryFirst = false; // schedule the tiles that push to neighbours before the interior tiles
     bool planFile = false;
   };
 
@@ -74,6 +76,9 @@ private:
   std::unique_ptr<Impl> impl_;
   unsigned long long launches_ = 0;
 };
+
+/* test hook: how many of `values` does the kernel's 3-instruction x/6 round differently from IEEE division (expect 0) */
+unsigned jacobi_div6_mismatches(const std::vector<float> &values);
 
 /* host reference of one Jacobi iteration on a dense periodic X*Y*Z array (same arithmetic and order as the kernel) */
 void jacobi_host_step(std::vector<float> &next, const std::vector<float> &curr, const Dim3 &size);

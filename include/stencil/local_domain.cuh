@@ -192,6 +192,9 @@ public:
   size_t buffer_offset(size_t qi, int which) const {
     return layout_.at(qi).off[which] + size_t(layout_[qi].lead) * elemSize_[qi];
   }
+  /* first byte of the padded buffer (row 0 starts here, `lead_elems` before logical element (0,0,0)) */
+  size_t buffer_start_offset(size_t qi, int which) const { return layout_.at(qi).off[which]; }
+  int64_t lead_elems(size_t qi) const { return layout_.at(qi).lead; }
   /* arrival-flag array (kArriveFlags x uint32) at the start of the slab */
   unsigned *arrive_flags() const noexcept { return reinterpret_cast<unsigned *>(slab_); }
 

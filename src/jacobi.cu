@@ -1,7 +1,18 @@
 /* Jacobi3D engine and its sm_100a kernels (N2 jacobi7 fused exterior, N3 jacobi7 interior, N9 init).
    Replaces reference kernels K8/K9 (bin/jacobi3d.cu:18-87). See include/stencil/jacobi.hpp for the modes.
 
-   Kernel shape. A CTA is 32 lanes x 8 rows; a lane owns 4 consecutive x cells (one 16-byte vector), so a tile is
+   Two kernel variants compute the same thing (Options::useTma picks; TMA is the default):
+
+   jacobi7_tma_kernel — the Blackwell path. A tile is 128 x 16 cells in xy, marched along z. One producer thread
+   streams the (128+8) x (16+2) input planes of the tile into a 6-deep shared-memory ring with
+   cp.async.bulk.tensor.3d (TMA; out-of-range parts of edge tiles are zero-filled by the hardware) and arms one
+   mbarrier per stage; eight consumer warps wait on the stage's mbarrier, read their centre / +-y rows as 16-byte
+   LDS, take +-x from the neighbouring lane, and hand the stage back through a second mbarrier. The centre column
+   of the last two planes and the in-plane partial sum live in registers, so every plane is read from shared
+   memory exactly once. Bytes in flight are set by the ring (6 x 9.8 KB per CTA, 3 CTAs per SM), not by registers,
+   which is what a latency-bound streaming stencil needs to reach HBM speed.
+
+   jacobi7_kernel — plain LDG version kept for comparison. A CTA is 32 lanes x 8 rows; a lane owns 4 consecutive x cells (one 16-byte vector), so a tile is
    128 x 8 cells in xy and is marched along z for tileZ planes with the centre column kept in registers
    (below / cur / above rotate). Per plane a thread issues three 16-byte loads (above, +y row, -y row); the x
    neighbours come from the adjacent lanes by shuffle, only lane 0 / lane 31 load one scalar each. Rows start on
@@ -21,6 +32,8 @@
 #include <cstring>
 #include <set>
 
+#include <cuda.h>
+
 #include "stencil/copy_plan.hpp"
 #include "stencil/reduce.hpp"
 
@@ -29,6 +42,13 @@ namespace stencil {
 namespace {
 
 constexpr int kLanes = 32, kRows = 8, kThreads = kLanes * kRows, kVec = 4, kTileX = kLanes * kVec;
+/* TMA variant geometry */
+constexpr int kTmaRows = 16, kTmaBoxX = kTileX + 8, kTmaBoxY = kTmaRows + 2, kTmaStages = 6;
+constexpr int kTmaConsumerWarps = kTmaRows / 2, kTmaThreads = kTmaConsumerWarps * 32;
+constexpr int kTmaLag = 2; // the producer refills the slot that was consumed kTmaLag planes ago
+constexpr int kTmaPlaneBytes = kTmaBoxX * kTmaBoxY * 4;
+constexpr int kTmaStageBytes = (kTmaPlaneBytes + 127) / 128 * 128;
+constexpr int kTmaSmemBytes = kTmaStages * kTmaStageBytes + 2 * kTmaStages * 8;
 constexpr size_t kDynBytes = Jacobi3D::kParamBytes;
 constexpr int kFusedFlagBase = 64; // word offset of the fused-iteration flags inside a control block
 
@@ -45,6 +65,8 @@ struct JacobiParams {
   int sx, sy, sz;            // compute-region size
   int lox, loy, loz, hix, hiy, hiz; // cells to update (compute coordinates, half open)
   int tileZ;
+  unsigned debugSkip; // diagnostics only (STENCIL_JACOBI_DEBUG_SKIP): 1 no signal, 2 no x push, 4 no y/z push
+  int tmaX0; // index of compute cell x=0 inside a padded row (TMA coordinates count from the row start)
   /* Dirichlet spheres in global coordinates */
   long long ox, oy, oz;   // global coordinate of compute cell (0,0,0)
   long long hcx, ccx, cy, cz, r2; // hot/cold centre x, shared centre y/z, (R+1)^2
@@ -79,6 +101,17 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
   return t;
 }
 
+/* x / 6 correctly rounded in three instructions (Markstein: q = RN(x*y), r = x - 6q exactly by FMA, RN(q + r*y) is the
+   correctly rounded quotient when y = RN(1/6)); bit-identical to IEEE division for the normal range, which is all a
+   field bounded by the sphere temperatures produces. The compiler's generic division sequence costs ~4x more issue
+   slots, and issue slots — not HBM — are what this kernel would otherwise run out of first. */
+__device__ __forceinline__ float div6(float x) {
+  const float y = 0x1.555556p-3f; // RN(1/6)
+  const float q = x * y;
+  const float r = __fmaf_rn(-6.0f, q, x);
+  return __fmaf_rn(r, y, q);
+}
+
 /* one output value, in the reference's summation order, with the sphere override */
 __device__ __forceinline__ float relax(float px, float mx, float py, float my, float pz, float mz) {
   float v = 0;
@@ -88,7 +121,7 @@ __device__ __forceinline__ float relax(float px, float mx, float py, float my, f
   v += my;
   v += pz;
   v += mz;
-  return __fdiv_rn(v, 6.0f);
+  return div6(v);
 }
 
 __device__ __forceinline__ float sphere_or(const JacobiParams &P, long long gx, long long gy, long long gz, float v) {
@@ -241,6 +274,300 @@ template <bool FUSED> __global__ void __launch_bounds__(kThreads) jacobi7_kernel
   }
 }
 
+
+/* ---- mbarrier / TMA primitives (PTX ISA: mbarrier, cp.async.bulk.tensor) ---- */
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return unsigned(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long *bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long *bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity) {
+  asm volatile("{\n\t.reg .pred p;\n\tWAIT_%=:\n\t"
+               "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+               "@p bra DONE_%=;\n\tbra WAIT_%=;\n\tDONE_%=:\n\t}" ::"r"(smem_u32(bar)),
+               "r"(parity)
+               : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *map, int cx, int cy, int cz, unsigned long long *bar) {
+  asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(
+                   smem_u32(dst)),
+               "l"(map), "r"(smem_u32(bar)), "r"(cx), "r"(cy), "r"(cz)
+               : "memory");
+}
+
+struct Cells { // four consecutive x cells of one row
+  float4 v;
+};
+
+/* Boundary tiles only: copy one finished row segment into the neighbours' halos. Deliberately NOT inlined: it runs for
+   a few percent of the rows, and inlining it would make the six peer pointers and pitches live across the whole
+   plane loop (108 registers instead of 72: one CTA less per SM). */
+__device__ __noinline__ void push_cells(const JacobiParams &P, unsigned faces, int x0, int y, int z, float4 o) {
+  const bool full = x0 + kVec <= P.sx;
+  const float ov[4] = {o.x, o.y, o.z, o.w};
+  /* neighbour halo addresses are pre-offset so that (y, z, x) of MY compute coordinates index them directly */
+  auto row_store = [&](float *q) {
+    if (full) {
+      *reinterpret_cast<float4 *>(q) = o;
+    } else {
+#pragma unroll
+      for (int k = 0; k < kVec; ++k)
+        if (x0 + k < P.sx) q[k] = ov[k];
+    }
+  };
+  if ((faces & (1u << YM)) && y == 0) row_store(P.nb[YM] + (long long)z * P.nbPitchXY[YM] + x0);
+  if ((faces & (1u << YP)) && y == P.sy - 1) row_store(P.nb[YP] + (long long)z * P.nbPitchXY[YP] + x0);
+  if ((faces & (1u << ZM)) && z == 0) row_store(P.nb[ZM] + (long long)y * P.nbPitchX[ZM] + x0);
+  if ((faces & (1u << ZP)) && z == P.sz - 1) row_store(P.nb[ZP] + (long long)y * P.nbPitchX[ZP] + x0);
+  if ((faces & (1u << XM)) && x0 == 0) P.nb[XM][(long long)z * P.nbPitchXY[XM] + (long long)y * P.nbPitchX[XM]] = o.x;
+  if ((faces & (1u << XP)) && x0 <= P.sx - 1 && P.sx - 1 < x0 + kVec) {
+    const int k = P.sx - 1 - x0; // which of my four cells is the last one of the row
+    P.nb[XP][(long long)z * P.nbPitchXY[XP] + (long long)y * P.nbPitchX[XP]] = k == 0 ? o.x : (k == 1 ? o.y : (k == 2 ? o.z : o.w));
+  }
+}
+
+/* store one finished row segment (4 cells at x0.., row y, plane z) locally and, for boundary tiles, into the
+   neighbours' halos. Shared by both kernel variants. */
+template <bool FUSED>
+__device__ __forceinline__ void store_cells(const JacobiParams &P, const Tile &t, int x0, int y, int z, float4 o) {
+  if (!(y >= P.loy && y < P.hiy && x0 < P.hix && x0 + kVec > P.lox)) return;
+  const bool full = x0 >= P.lox && x0 + kVec <= P.hix;
+  float *dp = P.dst + (long long)z * P.pitchXY + (long long)y * P.pitchX + x0;
+  if (full) {
+    *reinterpret_cast<float4 *>(dp) = o;
+  } else {
+    const float ov[4] = {o.x, o.y, o.z, o.w};
+#pragma unroll
+    for (int k = 0; k < kVec; ++k)
+      if (x0 + k >= P.lox && x0 + k < P.hix) dp[k] = ov[k];
+  }
+  if (FUSED && t.faces) {
+    /* does this row segment touch any face at all? (cheap, mostly false even inside boundary tiles) */
+    const bool onFace = y == 0 || y == P.sy - 1 || z == 0 || z == P.sz - 1 || x0 == 0 || (x0 <= P.sx - 1 && P.sx - 1 < x0 + kVec);
+    if (onFace) push_cells(P, t.faces, x0, y, z, o);
+  }
+}
+
+/* boundary tiles: wait until every neighbour has delivered the previous iteration (threads 0..5, then CTA barrier) */
+__device__ __forceinline__ void wait_neighbours(const JacobiParams &P) {
+  if (threadIdx.x < 6) {
+    const unsigned *f = P.myFlag[threadIdx.x];
+    if (f) {
+      const unsigned long long t0 = globaltimer_ns();
+      while (int(ld_acquire_sys(f) - (P.epoch - 1)) < 0) {
+        __nanosleep(64);
+        if (globaltimer_ns() - t0 > P.timeoutNs) {
+          atomicCAS(P.err, 0u, 100u + threadIdx.x);
+          break;
+        }
+      }
+    }
+  }
+}
+
+/* boundary tiles: count this CTA as done; the last one raises the neighbours' flags.
+   Ordering chain: every thread's (peer) stores -> CTA barrier -> thread 0: fence at GPU scope + counter increment ->
+   the CTA that sees the full count: system-scope fence -> release stores of the flags. Causality is transitive
+   across the scopes, so only the one final fence has to be system-wide; a system fence per boundary CTA measured
+   ~20 us per 512^3 iteration on B200. */
+__device__ __forceinline__ void signal_neighbours(const JacobiParams &P) {
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const unsigned prev = atomicAdd(P.done, 1u);
+    if (prev == P.nBoundary - 1) {
+      *P.done = 0;
+      __threadfence_system();
+      for (int f = 0; f < 6; ++f)
+        if (P.nbFlag[f]) st_release_sys(P.nbFlag[f], P.epoch);
+    }
+  }
+}
+
+__device__ __forceinline__ bool tile_near_sphere(const JacobiParams &P, const Tile &t, int rows, int z0, int z1) {
+  const long long gy0 = P.oy + t.ty * rows, gy1 = gy0 + rows - 1;
+  const long long gz0 = P.oz + z0, gz1 = P.oz + z1 - 1;
+  const long long gx0 = P.ox + t.tx * kTileX, gx1 = gx0 + kTileX - 1;
+  auto gap = [](long long a0, long long a1, long long c) { return c < a0 ? a0 - c : (c > a1 ? c - a1 : 0); };
+  const long long dy = gap(gy0, gy1, P.cy), dz = gap(gz0, gz1, P.cz);
+  const long long dh = gap(gx0, gx1, P.hcx), dc = gap(gx0, gx1, P.ccx);
+  return (dy * dy + dz * dz + dh * dh < P.r2) || (dy * dy + dz * dz + dc * dc < P.r2);
+}
+
+template <bool FUSED, int MINB>
+__global__ void __launch_bounds__(kTmaThreads, MINB) jacobi7_tma_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ JacobiParams P) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  unsigned long long *full = reinterpret_cast<unsigned long long *>(smem + kTmaStages * kTmaStageBytes);
+  unsigned long long *empty = full + kTmaStages;
+  const Tile t = P.tiles[blockIdx.x];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kTmaStages; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], kTmaConsumerWarps);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (FUSED && t.faces) wait_neighbours(P);
+  __syncthreads();
+
+  const int z0 = max(int(t.tz) * P.tileZ, P.loz), z1 = min(int(t.tz + 1) * P.tileZ, P.hiz);
+  const int nplanes = z1 > z0 ? z1 - z0 + 2 : 0; // input planes z0-1 .. z1
+
+  /* There is no producer warp: a ninth warp would cost a tenth warp's worth of registers (warps are allocated in
+     pairs) and with it a resident CTA. Thread 0 issues the TMA loads itself — a prologue of kTmaStages - kTmaLag
+     planes, then one refill per iteration into the slot every warp released kTmaLag planes ago, so its wait on the
+     `empty` barrier is almost always already satisfied. */
+  const int cx = P.tmaX0 + t.tx * kTileX - 4; // 4 cells of left margin keep the centre 16-byte aligned in smem
+  const int cy = t.ty * kTmaRows;             // raw row of compute row (ty*rows - 1)
+  auto issue = [&](int j) {                   // load input plane j (compute plane z0 - 1 + j, raw plane z0 + j)
+    const int sj = j % kTmaStages;
+    if (j >= kTmaStages) mbar_wait(&empty[sj], ((j / kTmaStages) - 1) & 1);
+    mbar_arrive_expect_tx(&full[sj], kTmaPlaneBytes);
+    tma_load_3d(smem + sj * kTmaStageBytes, &tmap, cx, cy, z0 + j, &full[sj]);
+  };
+  if (threadIdx.x == 0)
+    for (int j = 0; j < kTmaStages - kTmaLag && j < nplanes; ++j) issue(j);
+  {
+    /* ---- consumers: warp w owns tile rows 2w and 2w+1, a lane owns 4 cells of each ---- */
+    const int r0 = 2 * warp;
+    const int x0 = t.tx * kTileX + lane * kVec;
+    const int y0 = t.ty * kTmaRows + r0;
+    const bool nearSphere = tile_near_sphere(P, t, kTmaRows, z0, z1);
+    /* x faces: exactly one lane of a boundary warp owns the face cell of a row. Its destination pointer (row part) is
+       set up once; per plane the store is a single predicated STG — no call, no divergence worth mentioning.
+       y / z faces are whole-row vector stores and go through push_cells under a warp-uniform condition. */
+    float *qx[2] = {nullptr, nullptr};
+    long long qxStride = 0;
+    int qxK = 0;
+    bool qxWide = false; // the destination halo cell starts (XM) or ends (XP) a 32-byte sector of otherwise unused cells
+    unsigned yzFaces = 0;
+    if (FUSED && t.faces) {
+      yzFaces = t.faces & ~((1u << XM) | (1u << XP));
+      if (P.debugSkip & 4u) yzFaces = 0;
+      const bool ownsXM = !(P.debugSkip & 2u) && (t.faces & (1u << XM)) && x0 == 0;
+      const bool ownsXP = !(P.debugSkip & 2u) && (t.faces & (1u << XP)) && x0 <= P.sx - 1 && P.sx - 1 < x0 + kVec;
+      if (ownsXM && ownsXP) {
+        yzFaces = t.faces; // a row of at most four cells: both x faces in one lane, take the generic path
+      } else if (ownsXM || ownsXP) {
+        const int f = ownsXM ? XM : XP;
+        qxK = ownsXM ? 0 : P.sx - 1 - x0;
+        qxStride = P.nbPitchXY[f];
+        /* start of the 32-byte sector holding the destination halo cell: my x=0 lands in the neighbour's +x halo, the
+           first cell after its interior (sector = halo + 7 padding cells); my last x lands in its -x halo, the last
+           cell before its 128-byte aligned interior (sector = 7 padding cells + halo) */
+        const long long sectorShift = ownsXM ? 0 : -7;
+        qxWide = ((reinterpret_cast<unsigned long long>(P.nb[f] + sectorShift) | (unsigned long long)(P.nbPitchX[f] * 4)) & 31ull) == 0;
+        for (int r = 0; r < 2; ++r)
+          if (y0 + r < P.sy) qx[r] = P.nb[f] + (long long)(y0 + r) * P.nbPitchX[f] + (qxWide ? sectorShift : 0);
+      }
+    }
+    float4 cm2[2], cm1[2], part[2];
+    cm2[0] = cm2[1] = cm1[0] = cm1[1] = part[0] = part[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i = 0; i < nplanes; ++i) {
+      const int s = i % kTmaStages;
+      mbar_wait(&full[s], (i / kTmaStages) & 1);
+      const float *pl = reinterpret_cast<const float *>(smem + s * kTmaStageBytes);
+      /* smem row j holds compute row ty*rows + j - 1; smem column 4 + k holds compute x = tx*128 + k */
+      const float *rowC0 = pl + (r0 + 1) * kTmaBoxX + 4 + lane * kVec;
+      const float4 c0 = *reinterpret_cast<const float4 *>(rowC0);
+      const float4 c1 = *reinterpret_cast<const float4 *>(rowC0 + kTmaBoxX);
+      float4 pn[2];
+      if (i >= 1 && i <= nplanes - 2) {
+        const float4 south = *reinterpret_cast<const float4 *>(rowC0 - kTmaBoxX);     // y-1 of row r0
+        const float4 north = *reinterpret_cast<const float4 *>(rowC0 + 2 * kTmaBoxX); // y+1 of row r1
+        float w0 = __shfl_up_sync(0xffffffffu, c0.w, 1), e0 = __shfl_down_sync(0xffffffffu, c0.x, 1);
+        float w1 = __shfl_up_sync(0xffffffffu, c1.w, 1), e1 = __shfl_down_sync(0xffffffffu, c1.x, 1);
+        if (lane == 0) {
+          w0 = rowC0[-1];
+          w1 = rowC0[kTmaBoxX - 1];
+        }
+        if (lane == 31) {
+          e0 = rowC0[kVec];
+          e1 = rowC0[kTmaBoxX + kVec];
+        }
+        /* ((px + mx) + py) + my, the first four terms of the reference's sum */
+        pn[0].x = ((c0.y + w0) + c1.x) + south.x;
+        pn[0].y = ((c0.z + c0.x) + c1.y) + south.y;
+        pn[0].z = ((c0.w + c0.y) + c1.z) + south.z;
+        pn[0].w = ((e0 + c0.z) + c1.w) + south.w;
+        pn[1].x = ((c1.y + w1) + north.x) + c0.x;
+        pn[1].y = ((c1.z + c1.x) + north.y) + c0.y;
+        pn[1].z = ((c1.w + c1.y) + north.z) + c0.z;
+        pn[1].w = ((e1 + c1.z) + north.w) + c0.w;
+      } else {
+        pn[0] = pn[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      /* this stage's data is in registers now: hand the slot back before doing the arithmetic and the stores */
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[s]);
+      if (threadIdx.x == 0 && i + kTmaStages - kTmaLag < nplanes) issue(i + kTmaStages - kTmaLag);
+      if (i >= 2) {
+        const int z = z0 + i - 2; // output plane: above = centre of this plane, below = centre two planes back
+        const float4 cc[2] = {c0, c1};
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+          float4 o;
+          o.x = div6((part[r].x + cc[r].x) + cm2[r].x);
+          o.y = div6((part[r].y + cc[r].y) + cm2[r].y);
+          o.z = div6((part[r].z + cc[r].z) + cm2[r].z);
+          o.w = div6((part[r].w + cc[r].w) + cm2[r].w);
+          if (nearSphere) {
+            const long long gx = P.ox + x0, gy = P.oy + y0 + r, gz = P.oz + z;
+            o.x = sphere_or(P, gx, gy, gz, o.x);
+            o.y = sphere_or(P, gx + 1, gy, gz, o.y);
+            o.z = sphere_or(P, gx + 2, gy, gz, o.z);
+            o.w = sphere_or(P, gx + 3, gy, gz, o.w);
+          }
+          store_cells<false>(P, t, x0, y0 + r, z, o);
+          if (FUSED && t.faces) {
+            if (qx[r]) {
+              /* The halo cell shares its 32-byte sector with row padding only (LocalDomain layout), so the whole
+                 sector is written: a 4-byte store would make the receiver's memory system read-modify-write the
+                 sector (ECC), which measured as +160 MB of DRAM reads per 512^3 iteration. */
+              const float v = qxK == 0 ? o.x : (qxK == 1 ? o.y : (qxK == 2 ? o.z : o.w));
+              if (qxWide) {
+                float4 *q = reinterpret_cast<float4 *>(qx[r] + (long long)z * qxStride);
+                const float4 vv = make_float4(v, v, v, v);
+                q[0] = vv;
+                q[1] = vv;
+              } else { // neighbour's x extent is not a multiple of 8 cells: interior cells share the sector
+                qx[r][(long long)z * qxStride] = v;
+              }
+            }
+            const int y = y0 + r;
+            if (yzFaces && (y == 0 || y == P.sy - 1 || z == 0 || z == P.sz - 1 || (yzFaces & 3u)) && y < P.sy && x0 < P.sx)
+              push_cells(P, yzFaces, x0, y, z, o);
+          }
+        }
+      }
+      cm2[0] = cm1[0];
+      cm2[1] = cm1[1];
+      cm1[0] = c0;
+      cm1[1] = c1;
+      part[0] = pn[0];
+      part[1] = pn[1];
+    }
+  }
+
+  if (FUSED && t.faces && !(P.debugSkip & 1u)) {
+    __syncthreads();
+    signal_neighbours(P);
+  }
+}
+
+__global__ void div6_check_kernel(const float *in, unsigned *mismatches, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float a = div6(in[i]), b = __fdiv_rn(in[i], 6.0f);
+  if (__float_as_uint(a) != __float_as_uint(b)) atomicAdd(mismatches, 1u);
+}
+
 __global__ void fill_kernel(float *interior, long long pitchX, long long pitchXY, int sx, int sy, int sz, float v) {
   const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y;
   if (x >= sx || y >= sy) return;
@@ -274,6 +601,7 @@ struct Jacobi3D::Impl {
     unsigned *doneCounter = nullptr;
     float *dyn = nullptr; // kDynBytes of run-time parameters (hot, cold, ...)
     JacobiParams base[2]; // per parity: src = buffer[parity]
+    CUtensorMap tmap[2];  // per parity: the curr buffer as a 3-D tensor (padded row, rows, planes)
     std::vector<int> sameDevDeps;
     WaitSet finalWait;
   };
@@ -281,33 +609,42 @@ struct Jacobi3D::Impl {
   unsigned iter = 0;
   unsigned *err = nullptr;
   bool fusedOk = true;
+  bool useTma = true;
+  int minBlocks = 3; // resident CTAs per SM the TMA kernel is compiled for
+  int rows = kTmaRows; // tile rows of the selected kernel variant
 };
 
 namespace {
 
 /* tiles covering region [lo,hi) (compute coordinates) of a subdomain of size sz; faceMask selects which subdomain
    faces push (0 for non-fused launches). Boundary tiles are emitted first. */
-std::vector<Tile> make_tiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int tileZ, unsigned faceMask, unsigned *nBoundary) {
+std::vector<Tile> make_tiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int rows, int tileZ, unsigned faceMask, unsigned *nBoundary,
+                             bool boundaryFirst = false) {
   std::vector<Tile> boundary, inner;
+  unsigned nb = 0;
   if (hi.x <= lo.x || hi.y <= lo.y || hi.z <= lo.z) {
     if (nBoundary) *nBoundary = 0;
     return inner;
   }
   for (int64_t tz = lo.z / tileZ; tz * tileZ < hi.z; ++tz)
-    for (int64_t ty = lo.y / kRows; ty * kRows < hi.y; ++ty)
+    for (int64_t ty = lo.y / rows; ty * rows < hi.y; ++ty)
       for (int64_t tx = lo.x / kTileX; tx * kTileX < hi.x; ++tx) {
         unsigned f = 0;
         if (tx == 0) f |= 1u << XM;
         if (tx * kTileX <= sz.x - 1 && sz.x - 1 < (tx + 1) * kTileX) f |= 1u << XP;
         if (ty == 0) f |= 1u << YM;
-        if (ty * kRows <= sz.y - 1 && sz.y - 1 < (ty + 1) * kRows) f |= 1u << YP;
+        if (ty * rows <= sz.y - 1 && sz.y - 1 < (ty + 1) * rows) f |= 1u << YP;
         if (tz == 0) f |= 1u << ZM;
         if (tz * tileZ <= sz.z - 1 && sz.z - 1 < (tz + 1) * tileZ) f |= 1u << ZP;
         f &= faceMask;
         const Tile t{(unsigned short)tx, (unsigned short)ty, (unsigned short)tz, (unsigned short)f};
-        (f ? boundary : inner).push_back(t);
+        if (f) ++nb;
+        /* Natural (z, y, x) order keeps tiles that share halo rows / planes / margins resident together, so those
+           re-reads hit L2. Scheduling the pushing tiles first costs that locality (measured on B200: +160 MB of DRAM
+           reads and +50 us per 512^3 iteration) and buys nothing while all GPUs run in step. */
+        (f && boundaryFirst ? boundary : inner).push_back(t);
       }
-  if (nBoundary) *nBoundary = unsigned(boundary.size());
+  if (nBoundary) *nBoundary = nb;
   boundary.insert(boundary.end(), inner.begin(), inner.end());
   return boundary;
 }
@@ -318,6 +655,35 @@ Tile *upload(const std::vector<Tile> &t) {
   CUDA_RUNTIME(cudaMalloc(&d, t.size() * sizeof(Tile)));
   CUDA_RUNTIME(cudaMemcpy(d, t.data(), t.size() * sizeof(Tile), cudaMemcpyHostToDevice));
   return d;
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+/* the driver entry point is fetched through the runtime so that the library has no link dependency on libcuda */
+EncodeTiledFn encode_tiled() {
+  static EncodeTiledFn fn = [] {
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    CUDA_RUNTIME(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
+    if (!p || q != cudaDriverEntryPointSuccess) LOG_FATAL("cuTensorMapEncodeTiled is not available from this driver");
+    return reinterpret_cast<EncodeTiledFn>(p);
+  }();
+  return fn;
+}
+
+/* fp32 tensor over one padded buffer: dims (row pitch, rows, planes), box = one input plane of a tile */
+CUtensorMap make_plane_map(void *bufferStart, const Dim3 &pitch, const Dim3 &raw) {
+  CUtensorMap m;
+  const cuuint64_t dims[3] = {cuuint64_t(pitch.x), cuuint64_t(raw.y), cuuint64_t(raw.z)};
+  const cuuint64_t strides[2] = {cuuint64_t(pitch.x) * 4, cuuint64_t(pitch.x) * cuuint64_t(raw.y) * 4};
+  const cuuint32_t box[3] = {cuuint32_t(kTmaBoxX), cuuint32_t(kTmaBoxY), 1};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  const CUresult rc = encode_tiled()(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, bufferStart, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                     CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (rc != CUDA_SUCCESS) LOG_FATAL("cuTensorMapEncodeTiled failed with " << int(rc));
+  return m;
 }
 
 const Dim3 kFaceDir[6] = {Dim3(-1, 0, 0), Dim3(1, 0, 0), Dim3(0, -1, 0), Dim3(0, 1, 0), Dim3(0, 0, -1), Dim3(0, 0, 1)};
@@ -362,6 +728,9 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
   dd_->realize();
 
   impl_.reset(new Impl);
+  impl_->useTma = opt_.useTma;
+  impl_->rows = opt_.useTma ? kTmaRows : kRows;
+  if (const char *e = std::getenv("STENCIL_JACOBI_MINB")) impl_->minBlocks = std::atoi(e) == 2 ? 2 : 3;
   CUDA_RUNTIME(cudaHostAlloc(&impl_->err, sizeof(unsigned), cudaHostAllocMapped | cudaHostAllocPortable));
   *impl_->err = 0;
 
@@ -392,6 +761,16 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
     Impl::Dom &d = impl_->doms[di];
     DevGuard g(ld.gpu());
     d.stream = RcStream(ld.gpu());
+    if (opt_.useTma) { // function attributes are per device
+      for (auto *k : {&jacobi7_tma_kernel<true, 2>, &jacobi7_tma_kernel<false, 2>, &jacobi7_tma_kernel<true, 3>, &jacobi7_tma_kernel<false, 3>})
+        CUDA_RUNTIME(cudaFuncSetAttribute(*k, cudaFuncAttributeMaxDynamicSharedMemorySize, kTmaSmemBytes));
+      /* three 59 KB rings per SM fit the driver's default carve-out; forcing the maximum carve-out measured no better */
+      int carve = -1;
+      if (const char *e = std::getenv("STENCIL_JACOBI_CARVEOUT")) carve = std::atoi(e); // percent of the unified array; -1 = driver default
+      if (carve >= 0)
+        for (auto *k : {&jacobi7_tma_kernel<true, 2>, &jacobi7_tma_kernel<false, 2>, &jacobi7_tma_kernel<true, 3>, &jacobi7_tma_kernel<false, 3>})
+          CUDA_RUNTIME(cudaFuncSetAttribute(*k, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
+    }
     CUDA_RUNTIME(cudaEventCreateWithFlags(&d.done, cudaEventDisableTiming));
     CUDA_RUNTIME(cudaEventCreate(&d.t0));
     CUDA_RUNTIME(cudaEventCreate(&d.t1));
@@ -417,16 +796,17 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
       }
     d.sameDevDeps.assign(deps.begin(), deps.end());
 
-    const std::vector<Tile> all = make_tiles(Dim3(0, 0, 0), sz, sz, opt_.tileZ, faceMask, &d.nBoundary);
+    const int rows = impl_->rows;
+    const std::vector<Tile> all = make_tiles(Dim3(0, 0, 0), sz, sz, rows, opt_.tileZ, faceMask, &d.nBoundary, opt_.boundaryFirst);
     d.tilesAll = upload(all);
     d.nAll = unsigned(all.size());
     d.interior = interiors[di];
     d.exterior = exteriors[di];
-    const std::vector<Tile> in = make_tiles(d.interior.lo - org, d.interior.hi - org, sz, opt_.tileZ, 0, nullptr);
+    const std::vector<Tile> in = make_tiles(d.interior.lo - org, d.interior.hi - org, sz, rows, opt_.tileZ, 0, nullptr);
     d.tilesInterior = upload(in);
     d.nInterior = unsigned(in.size());
     for (const Rect3 &r : d.exterior) {
-      const std::vector<Tile> ex = make_tiles(r.lo - org, r.hi - org, sz, opt_.tileZ, 0, nullptr);
+      const std::vector<Tile> ex = make_tiles(r.lo - org, r.hi - org, sz, rows, opt_.tileZ, 0, nullptr);
       d.tilesExterior.emplace_back(upload(ex), unsigned(ex.size()));
     }
 
@@ -446,6 +826,13 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
       P.hiy = P.sy;
       P.hiz = P.sz;
       P.tileZ = opt_.tileZ;
+      if (const char *e = std::getenv("STENCIL_JACOBI_DEBUG_SKIP")) P.debugSkip = unsigned(std::atoi(e));
+      {
+        /* logical element (0,0,0) sits `lead` elements into the padded row; compute x=0 is one radius further */
+        const char *bufStart = static_cast<const char *>(ld.slab()) + ld.buffer_start_offset(h_.id(), parity);
+        P.tmaX0 = int(ld.lead_elems(h_.id())) + 1;
+        if (impl_->useTma) d.tmap[parity] = make_plane_map(const_cast<char *>(bufStart), pitch, ld.raw_size());
+      }
       P.ox = org.x;
       P.oy = org.y;
       P.oz = org.z;
@@ -529,10 +916,15 @@ void Jacobi3D::step() {
     P.hiy = int(reg.hi.y - org.y);
     P.hiz = int(reg.hi.z - org.z);
     P.epoch = impl_->iter;
-    if (fused)
+    if (impl_->useTma) {
+      auto *k = fused ? (impl_->minBlocks == 3 ? &jacobi7_tma_kernel<true, 3> : &jacobi7_tma_kernel<true, 2>)
+                      : (impl_->minBlocks == 3 ? &jacobi7_tma_kernel<false, 3> : &jacobi7_tma_kernel<false, 2>);
+      (*k)<<<n, kTmaThreads, kTmaSmemBytes, d.stream>>>(d.tmap[ld.parity()], P);
+    } else if (fused) {
       jacobi7_kernel<true><<<n, kThreads, 0, d.stream>>>(P);
-    else
+    } else {
       jacobi7_kernel<false><<<n, kThreads, 0, d.stream>>>(P);
+    }
     CUDA_RUNTIME(cudaGetLastError());
     ++launches_;
   };
@@ -660,6 +1052,20 @@ bool Jacobi3D::probe(const Dim3 &p, float *out) {
     return true;
   }
   return false;
+}
+
+unsigned jacobi_div6_mismatches(const std::vector<float> &values) {
+  float *d = nullptr;
+  unsigned *m = nullptr, h = 0;
+  CUDA_RUNTIME(cudaMalloc(&d, values.size() * sizeof(float)));
+  CUDA_RUNTIME(cudaMalloc(&m, sizeof(unsigned)));
+  CUDA_RUNTIME(cudaMemset(m, 0, sizeof(unsigned)));
+  CUDA_RUNTIME(cudaMemcpy(d, values.data(), values.size() * sizeof(float), cudaMemcpyHostToDevice));
+  div6_check_kernel<<<unsigned((values.size() + 255) / 256), 256>>>(d, m, int(values.size()));
+  CUDA_RUNTIME(cudaMemcpy(&h, m, sizeof(unsigned), cudaMemcpyDeviceToHost));
+  CUDA_RUNTIME(cudaFree(d));
+  CUDA_RUNTIME(cudaFree(m));
+  return h;
 }
 
 void jacobi_host_step(std::vector<float> &next, const std::vector<float> &curr, const Dim3 &size) {

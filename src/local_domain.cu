@@ -95,7 +95,9 @@ void LocalDomain::compute_layout() {
       l.lead = 0;
       l.pitchX = raw.x;
     }
-    l.bufBytes = size_t(l.pitchX) * size_t(raw.y) * size_t(raw.z) * es;
+    /* + one sector of slack: fused kernels write the whole 32-byte sector around a +x halo cell, which for the very
+       last row may extend past the last element */
+    l.bufBytes = size_t(l.pitchX) * size_t(raw.y) * size_t(raw.z) * es + 32;
     for (int b = 0; b < 2; ++b) {
       off = round_up_multiple(off, slabAlign);
       l.off[b] = off;
@@ -166,4 +168,7 @@ void LocalDomain::region_from_host(const void *host, const Dim3 &pos, const Dim3
   parms.extent = make_cudaExtent(size_t(ext.x) * es, size_t(ext.y), size_t(ext.z));
   parms.kind = cudaMemcpyHostToDevice;
   CUDA_RUNTIME(cudaMemcpy3D(&parms));
+  /* a copy from pageable memory may return while its DMA is still in flight on the legacy stream, and the
+     library's own streams are non-blocking (they do not wait for the legacy stream): finish it here */
+  CUDA_RUNTIME(cudaDeviceSynchronize());
 }

@@ -55,6 +55,50 @@ int device_count() {
 
 } // namespace
 
+TEST_CASE("jacobi: the 3-instruction divide by six is correctly rounded", "[cuda][jacobi]") {
+  std::vector<float> v;
+  unsigned seed = 12345u;
+  for (int i = 0; i < (1 << 20); ++i) {
+    seed = seed * 1664525u + 1013904223u;
+    /* sums of six values in [0,1]: cover [0,6] densely, plus a sweep of exponents */
+    v.push_back(float(seed >> 8) * (6.0f / 16777216.0f));
+  }
+  for (int e = -100; e <= 100; ++e)
+    for (int m = 0; m < 64; ++m) v.push_back(std::ldexp(1.0f + float(m) / 64.0f + 1e-7f * float(m), e));
+  for (int i = 0; i < (1 << 18); ++i) {
+    seed = seed * 1664525u + 1013904223u;
+    unsigned bits = (seed & 0x007fffffu) | (unsigned(64 + (seed >> 26)) << 23); // exponents 2^-63 .. 2^0
+    float f;
+    std::memcpy(&f, &bits, 4);
+    v.push_back(f);
+  }
+  REQUIRE(stencil::jacobi_div6_mismatches(v) == 0);
+}
+
+TEST_CASE("jacobi: both kernel variants agree with the host", "[cuda][jacobi]") {
+  using M = stencil::Jacobi3D::Mode;
+  for (bool tma : {true, false})
+    for (M m : {M::Fused, M::NoOverlap}) {
+      stencil::Jacobi3D::Options opt;
+      opt.mode = m;
+      opt.gpus = {0, 0};
+      opt.tileZ = 8;
+      opt.useTma = tma;
+      const Dim3 size(150, 37, 21);
+      stencil::Jacobi3D j(size_t(size.x), size_t(size.y), size_t(size.z), opt);
+      std::vector<float> ref(size_t(size.flatten()), 0.5f), tmp;
+      for (int it = 0; it < 5; ++it) {
+        j.step();
+        stencil::jacobi_host_step(tmp, ref, size);
+        ref.swap(tmp);
+      }
+      const std::vector<float> got = gather(j);
+      size_t bad = 0;
+      for (size_t i = 0; i < got.size(); ++i) bad += std::memcmp(&got[i], &ref[i], 4) != 0;
+      REQUIRE(bad == 0);
+    }
+}
+
 TEST_CASE("jacobi: one subdomain, all schedules, bit exact", "[cuda][jacobi]") {
   using M = stencil::Jacobi3D::Mode;
   for (M m : {M::Fused, M::Overlap, M::NoOverlap}) {
