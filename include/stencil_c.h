@@ -68,6 +68,28 @@ int stencil_translate(void *dst, const int64_t dst_pos[3], const int64_t dst_pit
    device. Allocates its scratch and result on the device, synchronises `stream`, frees, and writes *sum_out. */
 int stencil_reduce_sum_f32(const float *src, const int64_t pitch[3], const int64_t ext[3], void *stream, double *sum_out);
 
+/* Allocation-free form of stencil_reduce_sum_f32 (no counterpart in the reference).
+   For callers that must not call cudaMalloc/cudaFree where they need the sum: a monitor inside a free-running
+   fused iteration loop (allocation and free synchronise the device and would stall GPUs that wait on each other's
+   flags), a solver whose subdomains fill HBM, or code living under somebody else's memory pool. The reduction's
+   scratch (per-CTA partials + a ticket) is a fixed device array inside the library, STENCIL_NOALLOC_SCRATCH_BYTES
+   per GPU, held from library load to process exit. The function calls no allocator (CUDA's, torch's or any other)
+   and does not synchronise:
+     src, pitch, ext   as stencil_reduce_sum_f32, on the CURRENT device
+     sum_out           where the kernel writes the fp64 sum: device memory or mapped pinned host memory, caller-owned
+     stream            the result is valid once work enqueued on `stream` up to this call has completed
+   Limits: ext[0] <= STENCIL_NOALLOC_MAX_ROW_CELLS and ext[1]*ext[2] <= STENCIL_NOALLOC_MAX_ROWS; larger boxes are
+   refused with a message on stderr and return value -3 (nothing is launched). Other errors: -1 null argument,
+   -2 inconsistent pitch/extent, -10..-12 CUDA set-up failures.
+   The FIRST call on each device looks up the scratch array's device address and caches it — make that first call
+   outside any stream capture. All calls on a device share the one scratch array, which keeps the previous call's
+   contents: the ticket is cleared (stream-ordered) at every call, but two calls whose kernels can overlap on the
+   GPU — different streams without an ordering between them — race on it and give wrong sums. Serialise them. */
+#define STENCIL_NOALLOC_SCRATCH_BYTES 9728
+#define STENCIL_NOALLOC_MAX_ROW_CELLS 2147483647LL
+#define STENCIL_NOALLOC_MAX_ROWS 2147483647LL
+int stencil_reduce_sum_f32_noalloc(const float *src, const int64_t pitch[3], const int64_t ext[3], void *stream, double *sum_out);
+
 /* ---- DistributedDomain (reference: stencil.hpp) ---- */
 typedef struct stencil_domain stencil_domain_t;
 enum {

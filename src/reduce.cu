@@ -2,6 +2,11 @@
 #include "stencil/reduce.hpp"
 
 #include <algorithm>
+#include <climits>
+#include <cstdio>
+#include <mutex>
+
+#include "stencil_c.h"
 
 #include "stencil/cuda_runtime.hpp"
 
@@ -80,3 +85,83 @@ double reduce_sum_f32_sync(const float *src, const Dim3 &pitch, const Dim3 &ext,
 }
 
 } // namespace stencil
+
+/* ---------------------------------------------------------------------------------------------------------------
+   Allocation-free variant of the field sum.
+
+   Who needs it: code that may not call cudaMalloc/cudaFree at the point where it wants the sum. In this library
+   that is, first of all, a monitor inside a free-running fused iteration loop: cudaMalloc and cudaFree synchronise
+   the whole device, which would stall the per-GPU kernels that are waiting on each other's NVLink flags; second,
+   solvers that size their subdomains to fill HBM and have no room left for per-call temporaries; third, callers
+   that run under an allocator they do not control (another framework's memory pool).
+
+   So the two-stage reduction's scratch — one fp64 partial per CTA plus the ticket counter — does not come from an
+   allocator here: it is the file-scope device array below, present once per GPU that loads this library and held
+   until the process exits (STENCIL_NOALLOC_SCRATCH_BYTES = 9728 bytes).
+
+   In host code `g_noalloc_scratch` is only a handle for the symbol, not an address a kernel can use, so the device
+   address is looked up with cudaGetSymbolAddress — once per device, with that device current — and cached. */
+static __device__ __align__(256) unsigned char g_noalloc_scratch[STENCIL_NOALLOC_SCRATCH_BYTES];
+
+static_assert(STENCIL_NOALLOC_SCRATCH_BYTES >= stencil::kReduceScratchBytes, "scratch array too small for the reduction");
+
+namespace {
+constexpr int kMaxDevices = 64;
+void *g_noallocAddr[kMaxDevices] = {nullptr};
+std::mutex g_noallocMu;
+
+/* device address of g_noalloc_scratch on the CURRENT device (first call per device resolves and caches it) */
+int noalloc_scratch(void **out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+    std::fprintf(stderr, "stencil_reduce_sum_f32_noalloc: cannot identify the current device (%s)\n", cudaGetErrorString(e));
+    return -10;
+  }
+  std::lock_guard<std::mutex> lk(g_noallocMu);
+  if (!g_noallocAddr[dev]) {
+    void *p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (e != cudaSuccess || !p) {
+      std::fprintf(stderr, "stencil_reduce_sum_f32_noalloc: cudaGetSymbolAddress failed on device %d (%s)\n", dev, cudaGetErrorString(e));
+      return -11;
+    }
+    g_noallocAddr[dev] = p;
+  }
+  *out = g_noallocAddr[dev];
+  return 0;
+}
+} // namespace
+
+extern "C" int stencil_reduce_sum_f32_noalloc(const float *src, const int64_t pitch[3], const int64_t ext[3], void *stream, double *sum_out) {
+  if (!src || !sum_out || !pitch || !ext) {
+    std::fprintf(stderr, "stencil_reduce_sum_f32_noalloc: null argument\n");
+    return -1;
+  }
+  if (ext[0] < 0 || ext[1] < 0 || ext[2] < 0 || pitch[0] < ext[0] || pitch[1] < ext[1]) {
+    std::fprintf(stderr, "stencil_reduce_sum_f32_noalloc: negative extent or pitch smaller than the box\n");
+    return -2;
+  }
+  /* the fixed scratch serves boxes up to the kernel's 32-bit row arithmetic: reject anything beyond, loudly */
+  if (ext[0] > STENCIL_NOALLOC_MAX_ROW_CELLS || (ext[1] > 0 && ext[2] > STENCIL_NOALLOC_MAX_ROWS / ext[1])) {
+    std::fprintf(stderr,
+                 "stencil_reduce_sum_f32_noalloc: box %lld x %lld x %lld exceeds the supported maximum (%lld cells per row, %lld rows);"
+                 " use stencil_reduce_sum_f32, which allocates\n",
+                 (long long)ext[0], (long long)ext[1], (long long)ext[2], (long long)STENCIL_NOALLOC_MAX_ROW_CELLS,
+                 (long long)STENCIL_NOALLOC_MAX_ROWS);
+    return -3;
+  }
+  void *scratch = nullptr;
+  if (const int rc = noalloc_scratch(&scratch)) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  /* the array keeps whatever the previous call left behind; the partials are overwritten before they are read, but
+     the ticket must start at zero (a call that was aborted, or one on another stream, may have left it anywhere) */
+  unsigned char *ticket = static_cast<unsigned char *>(scratch) + stencil::kReduceMaxBlocks * sizeof(double);
+  cudaError_t e = cudaMemsetAsync(ticket, 0, sizeof(unsigned long long), st);
+  if (e != cudaSuccess) {
+    std::fprintf(stderr, "stencil_reduce_sum_f32_noalloc: clearing the ticket failed (%s)\n", cudaGetErrorString(e));
+    return -12;
+  }
+  stencil::reduce_sum_f32(src, Dim3(pitch[0], pitch[1], pitch[2]), Dim3(ext[0], ext[1], ext[2]), scratch, sum_out, st);
+  return 0;
+}

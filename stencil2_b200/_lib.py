@@ -47,6 +47,7 @@ def _declare(l):
         "stencil_unpack": (i, [vp, I64x3, I64x3, I64x3, vp, sz, vp]),
         "stencil_translate": (i, [vp, I64x3, I64x3, vp, I64x3, I64x3, I64x3, sz, vp]),
         "stencil_reduce_sum_f32": (i, [vp, I64x3, I64x3, vp, P(dbl)]),
+        "stencil_reduce_sum_f32_noalloc": (i, [vp, I64x3, I64x3, vp, vp]),
         "stencil_domain_create": (vp, [u64, u64, u64]),
         "stencil_domain_destroy": (None, [vp]),
         "stencil_domain_set_radius": (i, [vp, U64x27]),
