@@ -94,8 +94,16 @@ inline std::vector<size_t> solve_catch(const Mat2D<double> &w, const Mat2D<doubl
       }
     }
     if (!improved) break;
+    /* The incremental estimate carries rounding error; with tied costs a swap and its inverse can each look like an
+       improvement and the search would never end (the reference has this latent loop). Accept the swap only if the
+       exactly recomputed cost really went down — the cost is then strictly decreasing, so the loop terminates. */
     std::swap(best[bi], best[bj]);
-    bestCost = sweepCost;
+    const double exact = detail::cost(w, d, best);
+    if (!(exact < bestCost)) {
+      std::swap(best[bi], best[bj]);
+      break;
+    }
+    bestCost = exact;
   }
   if (costp) *costp = bestCost;
   return best;
