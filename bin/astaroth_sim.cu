@@ -1,0 +1,85 @@
+/* astaroth-sim: radius-3, multi-field stencil workload with interior/exterior overlap.
+   CLI follows the reference's bin/astaroth_sim.cu:87-101 (--x --y --z default 512 = size per run, --remote
+   --cuda-aware-mpi --colocated --peer --kernel --trivial, -f/--file accepted and unused). The reference runs exactly
+   one fp32 field, 5 iterations and prints no timing; defaults here reproduce that workload, and the options
+   --fields N, --double, --star (real 19-point radius-3 stencil), --iters, --no-overlap, --weak (scale the size by
+   numGpus^0.33333 like the other apps) cover BASELINE's "8 fp64 fields, radius 3, 256^3 per GPU" config.
+   Adds one CSV line on rank 0:
+     astaroth-sim,<methods>,<ranks>,<devCount>,x,y,z,<fields>,<fp32|fp64>,<avg7|star19>,<iters>,<s per iter>,<exchange s per iter>,<Gcell/s> */
+#include <iostream>
+
+#include "common.hpp"
+#include "stencil/astaroth.hpp"
+
+int main(int argc, char **argv) {
+  size_t x = 512, y = 512, z = 512;
+  int iters = 5, fields = 1;
+  bool remote = false, cudaAware = false, colocated = false, peer = false, kernel = false, direct = false, trivial = false;
+  bool fp64 = false, star = false, noOverlap = false, weak = false;
+  std::string file;
+  argparse::Parser p("radius-3 multi-field stencil (Astaroth stand-in)");
+  p.add_option(x, "--x");
+  p.add_option(y, "--y");
+  p.add_option(z, "--z");
+  p.add_flag(remote, "--remote")->help("host-staged transport");
+  p.add_flag(cudaAware, "--cuda-aware-mpi")->help("accepted for compatibility; needs a CUDA-aware MPI Comm");
+  p.add_flag(colocated, "--colocated")->help("colocated CUDA IPC transport");
+  p.add_flag(peer, "--peer")->help("pack + cudaMemcpyPeer");
+  p.add_flag(kernel, "--kernel")->help("same-GPU copies");
+  p.add_flag(direct, "--direct")->help("device-initiated NVLink stores");
+  p.add_flag(trivial, "--trivial")->help("skip node-aware placement");
+  p.add_option(file, "--file", "-f")->help("unused (reference compatibility)");
+  p.add_option(iters, "--iters");
+  p.add_option(fields, "--fields");
+  p.add_flag(fp64, "--double");
+  p.add_flag(star, "--star");
+  p.add_flag(noOverlap, "--no-overlap");
+  p.add_flag(weak, "--weak");
+  if (!p.parse(argc, argv)) {
+    std::cerr << p.help() << "\n";
+    return EXIT_FAILURE;
+  }
+  if (p.need_help()) {
+    std::cerr << p.help() << "\n";
+    return 0;
+  }
+  stencil::Comm &comm = stencil::world();
+  const JobShape job = job_shape(comm);
+  if (job.rank == 0) std::cerr << "assuming " << job.numGpus << " subdomains\n";
+  if (weak) {
+    x = weak_scale(x, job.numGpus);
+    y = weak_scale(y, job.numGpus);
+    z = weak_scale(z, job.numGpus);
+  }
+  if (job.rank == 0) std::cerr << "domain: " << x << "," << y << "," << z << "\n";
+  MethodFlags methods = MethodFlags::None;
+  if (remote) methods |= MethodFlags::CudaMpi;
+  if (colocated) methods |= MethodFlags::CudaMpiColocated;
+  if (peer) methods |= MethodFlags::CudaMemcpyPeer;
+  if (kernel) methods |= MethodFlags::CudaKernel;
+  if (direct) methods |= MethodFlags::NvlinkDirect;
+  if (methods == MethodFlags::None) methods = MethodFlags::All;
+  double perIter = 0, exPerIter = 0;
+  {
+    stencil::AstarothSim::Options opt;
+    opt.methods = methods;
+    opt.placement = trivial ? PlacementStrategy::Trivial : PlacementStrategy::NodeAware;
+    opt.fields = fields;
+    opt.fp64 = fp64;
+    opt.stencil = star ? stencil::AstarothSim::Stencil::Star19 : stencil::AstarothSim::Stencil::Average7;
+    opt.overlap = !noOverlap;
+    opt.planFile = true;
+    stencil::AstarothSim sim(x, y, z, opt);
+    sim.run(1); // warm up
+    double ex = 0;
+    const double t = sim.run(iters, &ex);
+    perIter = t / iters;
+    exPerIter = ex / iters;
+  }
+  if (job.rank == 0)
+    std::cout << "astaroth-sim," << method_string(methods) << "," << job.size << "," << job.devCount << "," << x << "," << y << "," << z << ","
+              << fields << "," << (fp64 ? "fp64" : "fp32") << "," << (star ? "star19" : "avg7") << "," << iters << "," << perIter << ","
+              << exPerIter << "," << double(x) * double(y) * double(z) / perIter / 1e9 << "\n";
+  stencil::finalize_world();
+  return 0;
+}

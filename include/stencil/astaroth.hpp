@@ -1,0 +1,65 @@
+#pragma once
+/* AstarothSim: the multi-field radius-3 workload of the reference's bin/astaroth_sim.cu as a reusable engine.
+
+   Reference behaviour kept (bin/astaroth_sim.cu:14-83, :185-274): radius 3 on all 26 directions, fields initialised
+   to sin(2*3.14159/period * (x + y + z)) (global coordinates, period 10) with -10 in the halo, and the schedule
+   interior kernel -> exchange() -> exterior slabs -> synchronise -> swap(). The reference ships ONE fp32 field and a
+   plain 7-point average as stand-in compute (Stencil::Average7); BASELINE's target config is 8 fp64 fields with a real
+   radius-3 stencil, so the engine is templated over the element type, takes any number of fields, and adds
+   Stencil::Star19: next = curr + dt * L(curr) with the 6th-order, 19-point radius-3 Laplacian every Astaroth-style
+   MHD code is built from. All fields are advanced by ONE launch per region (field index is a grid dimension). */
+#include <memory>
+#include <vector>
+
+#include "stencil/stencil.hpp"
+
+namespace stencil {
+
+class AstarothSim {
+public:
+  enum class Stencil { Average7, Star19 };
+  struct Options {
+    MethodFlags methods = MethodFlags::All;
+    PlacementStrategy placement = PlacementStrategy::NodeAware;
+    Stencil stencil = Stencil::Average7;
+    int fields = 1;
+    bool fp64 = false;
+    bool overlap = true;
+    std::vector<int> gpus;
+    double period = 10;
+    double dt = 0.01;
+    int tileZ = 32;
+    bool planFile = false;
+  };
+
+  AstarothSim(size_t x, size_t y, size_t z, const Options &opt);
+  ~AstarothSim();
+
+  DistributedDomain &domain() { return *dd_; }
+  const Options &options() const { return opt_; }
+  void init();
+  /* one iteration: interior, exchange, exterior, synchronise, swap */
+  void step();
+  void sync();
+  /* `iters` iterations; returns host wall seconds (max over ranks) and, in *exchangeSeconds, the part spent inside
+     exchange() */
+  double run(int iters, double *exchangeSeconds = nullptr);
+  unsigned long long launches() const { return launches_; }
+  /* dense host copy [z][y][x] of field f over the whole domain owned by this rank (NaN elsewhere), as double */
+  std::vector<double> gather(int field);
+
+private:
+  struct Impl;
+  Options opt_;
+  std::unique_ptr<DistributedDomain> dd_;
+  std::unique_ptr<Impl> impl_;
+  unsigned long long launches_ = 0;
+};
+
+/* host reference: one step of one field on a dense periodic array (same arithmetic order as the kernel) */
+void astaroth_host_step(std::vector<double> &next, const std::vector<double> &curr, const Dim3 &size, AstarothSim::Stencil st, bool fp64,
+                        double dt);
+/* the initial field value at a global coordinate */
+double astaroth_init_value(const Dim3 &p, double period, bool fp64);
+
+} // namespace stencil

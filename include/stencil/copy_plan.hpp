@@ -28,13 +28,18 @@ struct CopySeg {
   unsigned rowBytes; // contiguous bytes per row (extent.x * elemSize)
   unsigned ny, nz;   // rows per plane, planes
   unsigned vecLog2;  // log2 of the widest access (bytes) legal for every row of both sides: 0..4
+  /* "sector mode" for thin rows (x faces, edges, corners) whose destination row lies next to row padding: the row
+     is written as whole 32-byte sectors — padLoWords words of padding, the payload, padding up to totalWords — so the
+     receiving memory system never has to read-modify-write a partially written sector. 0 = plain mode. */
+  unsigned short padLoWords, totalWords;
 };
 
 struct CopyChunk {
   unsigned seg;   // index into the segment table
-  unsigned row0;  // first row (row = z * ny + y)
-  unsigned nrows; // rows in this chunk
-  unsigned pad_;
+  unsigned z;     // first plane of the box this chunk covers
+  unsigned y0;    // first row inside that plane (0 when the chunk spans several planes)
+  unsigned short nrows;   // rows per plane in this chunk
+  unsigned short nplanes; // whole planes covered (1: a run of rows inside one plane — no index division on device)
 };
 
 /* a strided 3-D array: address of element (0,0,0) per parity, pitches in bytes */
@@ -42,6 +47,8 @@ struct BoxView {
   char *base[2];
   long long pitchY, pitchZ;
   size_t elemSize;
+  /* bytes of don't-care padding before logical x = 0 and after logical x = rowElems of EVERY row (0: none / unknown) */
+  long long padLoBytes = 0, padHiBytes = 0, rowElems = 0;
   static BoxView dense(void *p, const Dim3 &ext, size_t elemSize) {
     BoxView v;
     v.base[0] = v.base[1] = static_cast<char *>(p);

@@ -169,8 +169,20 @@ public:
   void swap() noexcept { parity_ ^= 1; }
 
   /* strided view of quantity qi (both parities: base[p] is the curr buffer when parity() == p) for CopyPlan */
-  stencil::BoxView view(size_t qi) const {
-    return stencil::BoxView::pitched(buffer(qi, 0), buffer(qi, 1), pitch(qi), elemSize_[qi]);
+  stencil::BoxView view(size_t qi) const { return view_at(qi, slab_); }
+  /* the same view for a copy of this subdomain's slab mapped at `slabBase` (e.g. through CUDA IPC in a peer process) */
+  stencil::BoxView view_at(size_t qi, char *slabBase) const {
+    const Layout &l = layout_.at(qi);
+    const long long es = (long long)elemSize_[qi];
+    char *b0 = slabBase ? slabBase + l.off[0] + size_t(l.lead) * elemSize_[qi] : nullptr;
+    char *b1 = slabBase ? slabBase + l.off[1] + size_t(l.lead) * elemSize_[qi] : nullptr;
+    stencil::BoxView v = stencil::BoxView::pitched(b0, b1, pitch(qi), elemSize_[qi]);
+    /* the cells between the end of one logical row and the start of the next are padding (the buffer ends with 32
+       bytes of slack for the last row): movers may overwrite up to one sector's worth of it */
+    v.rowElems = raw_size().x;
+    v.padLoBytes = l.lead * es < 28 ? l.lead * es : 28;
+    v.padHiBytes = (l.pitchX - raw_size().x) * es < 28 ? (l.pitchX - raw_size().x) * es : 28;
+    return v;
   }
 
   /* dense copy of box [pos, pos+ext) (elements from logical (0,0,0)) of curr quantity qi */

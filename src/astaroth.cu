@@ -1,0 +1,357 @@
+/* AstarothSim engine and kernels (N4/N5 radius-3 multi-field stencil, N9 init).
+   Replaces reference kernels K10/K11 (bin/astaroth_sim.cu:14-83). See include/stencil/astaroth.hpp.
+
+   Kernel shape: a CTA is 32 lanes x 8 rows, a lane owns one 16-byte vector of cells (4 fp32 / 2 fp64) and marches
+   along z with the seven centre values z-3..z+3 rotating through registers, so the z direction costs one load per
+   plane; x and y neighbours are 16-byte loads that hit L1 (rows are 128-byte aligned). All fields go in one launch
+   (blockIdx.z = field x z-chunk). This round the exchange is the library's direct-push exchange() overlapped with the
+   interior kernel; folding the push into the exterior kernel as the Jacobi engine does is the next step. */
+#include "stencil/astaroth.hpp"
+
+#include <cmath>
+#include <cstring>
+#include <limits>
+
+namespace stencil {
+
+namespace {
+
+constexpr int kMaxFields = 16, kLanes = 32, kRows = 8, kR = 3;
+
+struct DevGuard {
+  int prev = 0;
+  explicit DevGuard(int d) {
+    CUDA_RUNTIME(cudaGetDevice(&prev));
+    if (prev != d) CUDA_RUNTIME(cudaSetDevice(d));
+  }
+  ~DevGuard() { cudaSetDevice(prev); }
+};
+
+template <typename T> struct Vec;
+template <> struct Vec<float> {
+  typedef float4 type;
+  static constexpr int n = 4;
+};
+template <> struct Vec<double> {
+  typedef double2 type;
+  static constexpr int n = 2;
+};
+
+template <typename T> struct FieldParams {
+  const T *src[kMaxFields]; // compute cell (0,0,0) of curr, per field
+  T *dst[kMaxFields];
+  long long pitchX, pitchXY;
+  int lox, loy, loz, hix, hiy, hiz; // compute coordinates, half open
+  int tileZ, nChunks;
+  T dt;
+};
+
+/* 6th-order second-derivative weights: c0 = -49/18 per axis, then 3/2, -3/20, 1/90 */
+template <typename T> __host__ __device__ inline T star19(const T c, const T xm[3], const T xp[3], const T ym[3], const T yp[3], const T zm[3], const T zp[3], T dt) {
+  const T c1 = T(1.5), c2 = T(-0.15), c3 = T(1.0 / 90.0), c0 = T(-49.0 / 18.0);
+  T lap = T(3) * c0 * c;
+  lap += c1 * (((((xm[0] + xp[0]) + ym[0]) + yp[0]) + zm[0]) + zp[0]);
+  lap += c2 * (((((xm[1] + xp[1]) + ym[1]) + yp[1]) + zm[1]) + zp[1]);
+  lap += c3 * (((((xm[2] + xp[2]) + ym[2]) + yp[2]) + zm[2]) + zp[2]);
+  return c + dt * lap;
+}
+
+/* the reference's stand-in: (-x + -y + -z + +x + +y + +z) / 6 in that order */
+template <typename T> __host__ __device__ inline T average7(T xm, T ym, T zm, T xp, T yp, T zp) {
+  T v = 0;
+  v += xm;
+  v += ym;
+  v += zm;
+  v += xp;
+  v += yp;
+  v += zp;
+  return v / T(6);
+}
+
+template <typename T, bool STAR> __global__ void __launch_bounds__(kLanes *kRows) astaroth_kernel(const __grid_constant__ FieldParams<T> P) {
+  typedef typename Vec<T>::type V;
+  constexpr int N = Vec<T>::n;
+  const int field = blockIdx.z / P.nChunks, chunk = blockIdx.z % P.nChunks;
+  const int x0 = (P.lox / N) * N + (blockIdx.x * kLanes + threadIdx.x) * N;
+  const int y = P.loy + blockIdx.y * kRows + threadIdx.y;
+  const int z0 = P.loz + chunk * P.tileZ, z1 = min(z0 + P.tileZ, P.hiz);
+  if (y >= P.hiy || x0 >= P.hix || x0 + N <= P.lox || z0 >= z1) return;
+  const T *s = P.src[field] + (long long)y * P.pitchX + x0;
+  T *d = P.dst[field] + (long long)y * P.pitchX + x0;
+  auto ldv = [](const T *p, T out[N]) {
+    const V v = *reinterpret_cast<const V *>(p);
+    std::memcpy(out, &v, sizeof(V));
+  };
+  /* centre column z-3 .. z+3 (STAR) or z-1 .. z+1 (average) */
+  T q[7][N];
+#pragma unroll
+  for (int k = 0; k < 7; ++k) {
+    if (STAR || (k >= 2 && k <= 4)) ldv(s + (long long)(z0 + k - 3) * P.pitchXY, q[k]);
+  }
+  for (int z = z0; z < z1; ++z) {
+    const T *sp = s + (long long)z * P.pitchXY;
+    T out[N];
+    if (STAR) {
+      /* x neighbours: the vectors left and right of mine (and one further for fp64) */
+      T xl[2 * N], xr[2 * N];
+      ldv(sp - N, xl + N);
+      ldv(sp + N, xr);
+      if (N < 3) {
+        ldv(sp - 2 * N, xl);
+        ldv(sp + 2 * N, xr + N);
+      }
+      T ym[3][N], yp[3][N];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        ldv(sp - (long long)(k + 1) * P.pitchX, ym[k]);
+        ldv(sp + (long long)(k + 1) * P.pitchX, yp[k]);
+      }
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+        /* cells in x order around cell i: window = [xl | q[3] | xr] */
+        T win[4 * N + N];
+#pragma unroll
+        for (int j = 0; j < 2 * N; ++j) win[j] = xl[j];
+#pragma unroll
+        for (int j = 0; j < N; ++j) win[2 * N + j] = q[3][j];
+#pragma unroll
+        for (int j = 0; j < 2 * N; ++j) win[3 * N + j] = xr[j];
+        const int c = 2 * N + i;
+        const T xm[3] = {win[c - 1], win[c - 2], win[c - 3]}, xp[3] = {win[c + 1], win[c + 2], win[c + 3]};
+        const T ymv[3] = {ym[0][i], ym[1][i], ym[2][i]}, ypv[3] = {yp[0][i], yp[1][i], yp[2][i]};
+        const T zm[3] = {q[2][i], q[1][i], q[0][i]}, zp[3] = {q[4][i], q[5][i], q[6][i]};
+        out[i] = star19<T>(q[3][i], xm, xp, ymv, ypv, zm, zp, P.dt);
+      }
+    } else {
+      T l[N], r[N], ym[N], yp[N];
+      ldv(sp - N, l);
+      ldv(sp + N, r);
+      ldv(sp - P.pitchX, ym);
+      ldv(sp + P.pitchX, yp);
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+        const T xm = i == 0 ? l[N - 1] : q[3][i - 1], xp = i == N - 1 ? r[0] : q[3][i + 1];
+        out[i] = average7<T>(xm, ym[i], q[2][i], xp, yp[i], q[4][i]);
+      }
+    }
+    T *dp = d + (long long)z * P.pitchXY;
+    if (x0 >= P.lox && x0 + N <= P.hix) {
+      V v;
+      std::memcpy(&v, out, sizeof(V));
+      *reinterpret_cast<V *>(dp) = v;
+    } else {
+#pragma unroll
+      for (int i = 0; i < N; ++i)
+        if (x0 + i >= P.lox && x0 + i < P.hix) dp[i] = out[i];
+    }
+    /* rotate the centre column and fetch the next plane */
+#pragma unroll
+    for (int k = (STAR ? 0 : 2); k < (STAR ? 6 : 4); ++k)
+#pragma unroll
+      for (int i = 0; i < N; ++i) q[k][i] = q[k + 1][i];
+    if (z + 1 < z1) ldv(s + (long long)(z + 1 + (STAR ? 3 : 1)) * P.pitchXY, q[STAR ? 6 : 4]);
+  }
+}
+
+template <typename T>
+__global__ void astaroth_init_kernel(T *logical0, long long pitchX, long long pitchXY, Dim3 raw, Dim3 haloOrigin, double period) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y;
+  if (x >= raw.x || y >= raw.y) return;
+  for (int z = blockIdx.z; z < raw.z; z += gridDim.z) {
+    const bool inside = x >= kR && y >= kR && z >= kR && x < raw.x - kR && y < raw.y - kR && z < raw.z - kR;
+    T v = T(-10);
+    if (inside) {
+      const double w = 2 * 3.14159 / period;
+      v = T(sin(w * double(haloOrigin.x + x) + w * double(haloOrigin.y + y) + w * double(haloOrigin.z + z)));
+    }
+    logical0[(long long)z * pitchXY + (long long)y * pitchX + x] = v;
+  }
+}
+
+} // namespace
+
+struct AstarothSim::Impl {
+  std::vector<RcStream> streams;
+  std::vector<Rect3> interior;
+  std::vector<std::vector<Rect3>> exterior;
+  double exchangeSeconds = 0;
+};
+
+AstarothSim::AstarothSim(size_t x, size_t y, size_t z, const Options &opt) : opt_(opt) {
+  if (opt_.fields < 1 || opt_.fields > kMaxFields) LOG_FATAL("AstarothSim supports 1.." << kMaxFields << " fields");
+  dd_.reset(new DistributedDomain(x, y, z));
+  if (!opt_.gpus.empty()) dd_->set_gpus(opt_.gpus);
+  dd_->set_radius(kR);
+  dd_->set_methods(opt_.methods);
+  dd_->set_placement(opt_.placement);
+  dd_->set_plan_file(opt_.planFile);
+  for (int f = 0; f < opt_.fields; ++f) dd_->add_data(opt_.fp64 ? sizeof(double) : sizeof(float), "d" + std::to_string(f));
+  dd_->realize();
+  impl_.reset(new Impl);
+  for (LocalDomain &ld : dd_->domains()) impl_->streams.emplace_back(ld.gpu());
+  impl_->interior = dd_->get_interior();
+  impl_->exterior = dd_->get_exterior();
+  init();
+}
+
+AstarothSim::~AstarothSim() {
+  if (dd_) sync();
+  impl_.reset();
+  dd_.reset();
+}
+
+void AstarothSim::init() {
+  for (size_t di = 0; di < dd_->domains().size(); ++di) {
+    LocalDomain &ld = dd_->domains()[di];
+    DevGuard g(ld.gpu());
+    const Dim3 raw = ld.raw_size();
+    const dim3 block(64, 4, 1), grid(unsigned((raw.x + 63) / 64), unsigned((raw.y + 3) / 4), unsigned(std::min<int64_t>(raw.z, 64)));
+    for (int f = 0; f < opt_.fields; ++f) {
+      const Dim3 pitch = ld.pitch(size_t(f));
+      if (opt_.fp64)
+        astaroth_init_kernel<double><<<grid, block, 0, impl_->streams[di]>>>(static_cast<double *>(ld.curr_data(size_t(f))), pitch.x, pitch.x * pitch.y,
+                                                                              raw, ld.halo_origin(), opt_.period);
+      else
+        astaroth_init_kernel<float><<<grid, block, 0, impl_->streams[di]>>>(static_cast<float *>(ld.curr_data(size_t(f))), pitch.x, pitch.x * pitch.y,
+                                                                             raw, ld.halo_origin(), opt_.period);
+      CUDA_RUNTIME(cudaGetLastError());
+      ++launches_;
+    }
+  }
+  sync();
+}
+
+template <typename T> static void launch_region(AstarothSim::Stencil st, LocalDomain &ld, int fields, const Rect3 &reg, int tileZ, T dt, cudaStream_t stream) {
+  if (reg.empty()) return;
+  FieldParams<T> P;
+  std::memset(&P, 0, sizeof(P));
+  const Dim3 pitch = ld.pitch(0), org = ld.origin();
+  const long long interiorOff = (long long)kR * (pitch.x * pitch.y + pitch.x + 1);
+  for (int f = 0; f < fields; ++f) {
+    P.src[f] = static_cast<const T *>(ld.curr_data(size_t(f))) + interiorOff;
+    P.dst[f] = static_cast<T *>(ld.next_data(size_t(f))) + interiorOff;
+  }
+  P.pitchX = pitch.x;
+  P.pitchXY = pitch.x * pitch.y;
+  P.lox = int(reg.lo.x - org.x);
+  P.loy = int(reg.lo.y - org.y);
+  P.loz = int(reg.lo.z - org.z);
+  P.hix = int(reg.hi.x - org.x);
+  P.hiy = int(reg.hi.y - org.y);
+  P.hiz = int(reg.hi.z - org.z);
+  P.tileZ = tileZ;
+  P.nChunks = (P.hiz - P.loz + tileZ - 1) / tileZ;
+  P.dt = dt;
+  constexpr int N = Vec<T>::n;
+  const int xSpan = P.hix - (P.lox / N) * N;
+  const dim3 block(kLanes, kRows, 1), grid(unsigned((xSpan + kLanes * N - 1) / (kLanes * N)), unsigned((P.hiy - P.loy + kRows - 1) / kRows),
+                                           unsigned(P.nChunks * fields));
+  if (st == AstarothSim::Stencil::Star19)
+    astaroth_kernel<T, true><<<grid, block, 0, stream>>>(P);
+  else
+    astaroth_kernel<T, false><<<grid, block, 0, stream>>>(P);
+  CUDA_RUNTIME(cudaGetLastError());
+}
+
+void AstarothSim::step() {
+  std::vector<LocalDomain> &doms = dd_->domains();
+  auto launch = [&](size_t di, const Rect3 &reg) {
+    if (reg.empty()) return;
+    DevGuard g(doms[di].gpu());
+    if (opt_.fp64)
+      launch_region<double>(opt_.stencil, doms[di], opt_.fields, reg, opt_.tileZ, opt_.dt, impl_->streams[di]);
+    else
+      launch_region<float>(opt_.stencil, doms[di], opt_.fields, reg, opt_.tileZ, float(opt_.dt), impl_->streams[di]);
+    ++launches_;
+  };
+  if (opt_.overlap)
+    for (size_t di = 0; di < doms.size(); ++di) launch(di, impl_->interior[di]);
+  const double t0 = Comm::wtime();
+  dd_->exchange();
+  impl_->exchangeSeconds += Comm::wtime() - t0;
+  for (size_t di = 0; di < doms.size(); ++di) {
+    if (opt_.overlap)
+      for (const Rect3 &r : impl_->exterior[di]) launch(di, r);
+    else
+      launch(di, doms[di].get_compute_region());
+  }
+  sync();
+  dd_->swap();
+}
+
+void AstarothSim::sync() {
+  for (size_t di = 0; di < dd_->domains().size(); ++di) {
+    DevGuard g(dd_->domains()[di].gpu());
+    CUDA_RUNTIME(cudaStreamSynchronize(impl_->streams[di]));
+  }
+}
+
+double AstarothSim::run(int iters, double *exchangeSeconds) {
+  sync();
+  dd_->comm().barrier();
+  impl_->exchangeSeconds = 0;
+  const double t0 = Comm::wtime();
+  for (int i = 0; i < iters; ++i) step();
+  const double t = dd_->comm().allreduce_max(Comm::wtime() - t0);
+  if (exchangeSeconds) *exchangeSeconds = dd_->comm().allreduce_max(impl_->exchangeSeconds);
+  return t;
+}
+
+std::vector<double> AstarothSim::gather(int field) {
+  sync();
+  const Dim3 g = dd_->size();
+  std::vector<double> out(size_t(g.flatten()), std::numeric_limits<double>::quiet_NaN());
+  for (LocalDomain &ld : dd_->domains()) {
+    const std::vector<unsigned char> b = ld.interior_to_host(size_t(field));
+    const Dim3 sz = ld.size(), o = ld.origin();
+    size_t i = 0;
+    for (int64_t z = 0; z < sz.z; ++z)
+      for (int64_t y = 0; y < sz.y; ++y)
+        for (int64_t x = 0; x < sz.x; ++x, ++i) {
+          const double v = opt_.fp64 ? reinterpret_cast<const double *>(b.data())[i] : double(reinterpret_cast<const float *>(b.data())[i]);
+          out[size_t(((o.z + z) * g.y + o.y + y) * g.x + o.x + x)] = v;
+        }
+  }
+  return out;
+}
+
+double astaroth_init_value(const Dim3 &p, double period, bool fp64) {
+  const double w = 2 * 3.14159 / period;
+  const double v = std::sin(w * double(p.x) + w * double(p.y) + w * double(p.z));
+  return fp64 ? v : double(float(v));
+}
+
+template <typename T> static void host_step(std::vector<double> &next, const std::vector<double> &curr, const Dim3 &size, AstarothSim::Stencil st, T dt) {
+  const int64_t X = size.x, Y = size.y, Z = size.z;
+  next.resize(curr.size());
+  auto at = [&](int64_t x, int64_t y, int64_t z) { return T(curr[size_t((((z + 3 * Z) % Z) * Y + (y + 3 * Y) % Y) * X + (x + 3 * X) % X)]); };
+  for (int64_t z = 0; z < Z; ++z)
+    for (int64_t y = 0; y < Y; ++y)
+      for (int64_t x = 0; x < X; ++x) {
+        T v;
+        if (st == AstarothSim::Stencil::Star19) {
+          T xm[3], xp[3], ym[3], yp[3], zm[3], zp[3];
+          for (int k = 0; k < 3; ++k) {
+            xm[k] = at(x - k - 1, y, z);
+            xp[k] = at(x + k + 1, y, z);
+            ym[k] = at(x, y - k - 1, z);
+            yp[k] = at(x, y + k + 1, z);
+            zm[k] = at(x, y, z - k - 1);
+            zp[k] = at(x, y, z + k + 1);
+          }
+          v = star19<T>(at(x, y, z), xm, xp, ym, yp, zm, zp, dt);
+        } else {
+          v = average7<T>(at(x - 1, y, z), at(x, y - 1, z), at(x, y, z - 1), at(x + 1, y, z), at(x, y + 1, z), at(x, y, z + 1));
+        }
+        next[size_t((z * Y + y) * X + x)] = double(v);
+      }
+}
+
+void astaroth_host_step(std::vector<double> &next, const std::vector<double> &curr, const Dim3 &size, AstarothSim::Stencil st, bool fp64, double dt) {
+  if (fp64)
+    host_step<double>(next, curr, size, st, dt);
+  else
+    host_step<float>(next, curr, size, st, float(dt));
+}
+
+} // namespace stencil

@@ -63,37 +63,100 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 }
 
 constexpr int kThreads = 256;
-constexpr int kUnroll = 4;
 
-/* copy rows [row0, row0+nrows) of one segment with BYTES-wide accesses */
+/* one thin row in sector mode: gather the payload words into their place inside 1-2 whole sectors, zero elsewhere */
+__device__ __forceinline__ void copy_row_sectors(const CopySeg &s, const char *__restrict__ a, char *__restrict__ b) {
+  const unsigned lo = s.padLoWords, nw = s.rowBytes / 4, total = s.totalWords;
+  const unsigned *src = reinterpret_cast<const unsigned *>(a);
+  unsigned w[16];
+#pragma unroll
+  for (unsigned j = 0; j < 16; ++j) w[j] = (j >= lo && j < lo + nw) ? ld_stream(src + (j - lo)) : 0u;
+  uint4 *dst = reinterpret_cast<uint4 *>(b - 4 * (long long)lo);
+#pragma unroll
+  for (unsigned q = 0; q < 4; ++q)
+    if (4 * q < total) dst[q] = make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
+}
+
+/* Copy `nrows` consecutive rows of one plane with BYTES-wide accesses. sp/dp point at the first row. No integer
+   division anywhere: thin rows (a handful of units, the x faces) are one row per thread; wide rows are one row per
+   warp with the lanes striding along the row, two rows in flight per warp. */
 template <int BYTES>
-__device__ __forceinline__ void copy_chunk(const CopySeg &s, const char *__restrict__ src, char *__restrict__ dst,
-                                           unsigned row0, unsigned nrows) {
+__device__ __forceinline__ void copy_rows(const CopySeg &s, const char *__restrict__ sp, char *__restrict__ dp, unsigned nrows) {
   typedef typename VecT<BYTES>::type V;
   const unsigned upr = s.rowBytes / BYTES; // units per row
-  const unsigned total = nrows * upr;
-  const unsigned ny = s.ny;
-  for (unsigned base = threadIdx.x; base < total; base += kThreads * kUnroll) {
-    V v[kUnroll];
-    long long doff[kUnroll];
+  if (s.totalWords) {
+    for (unsigned r = threadIdx.x; r < nrows; r += kThreads) copy_row_sectors(s, sp + (long long)r * s.srcPitchY, dp + (long long)r * s.dstPitchY);
+  } else if (upr <= 8) {
+    for (unsigned r = threadIdx.x; r < nrows; r += kThreads) {
+      const V *a = reinterpret_cast<const V *>(sp + (long long)r * s.srcPitchY);
+      V *b = reinterpret_cast<V *>(dp + (long long)r * s.dstPitchY);
+      V v[8];
 #pragma unroll
-    for (int k = 0; k < kUnroll; ++k) {
-      const unsigned i = base + k * kThreads;
-      if (i < total) {
-        const unsigned r = i / upr;
-        const unsigned u = i - r * upr;
-        const unsigned row = row0 + r;
-        const unsigned z = row / ny;
-        const unsigned y = row - z * ny;
-        const long long soff = (long long)z * s.srcPitchZ + (long long)y * s.srcPitchY + (long long)u * BYTES;
-        doff[k] = (long long)z * s.dstPitchZ + (long long)y * s.dstPitchY + (long long)u * BYTES;
-        v[k] = ld_stream(reinterpret_cast<const V *>(src + soff));
+      for (int u = 0; u < 8; ++u)
+        if (u < int(upr)) v[u] = ld_stream(a + u);
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        if (u < int(upr)) b[u] = v[u];
+    }
+  } else {
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, nwarps = kThreads / 32;
+    for (unsigned r = warp; r < nrows; r += 2 * nwarps) {
+      const unsigned r2 = r + nwarps;
+      const V *a0 = reinterpret_cast<const V *>(sp + (long long)r * s.srcPitchY);
+      V *b0 = reinterpret_cast<V *>(dp + (long long)r * s.dstPitchY);
+      const V *a1 = reinterpret_cast<const V *>(sp + (long long)r2 * s.srcPitchY);
+      V *b1 = reinterpret_cast<V *>(dp + (long long)r2 * s.dstPitchY);
+      const bool two = r2 < nrows;
+      for (unsigned u = lane; u < upr; u += 64) {
+        const unsigned u2 = u + 32;
+        V v00 = ld_stream(a0 + u), v01, v10, v11;
+        if (u2 < upr) v01 = ld_stream(a0 + u2);
+        if (two) {
+          v10 = ld_stream(a1 + u);
+          if (u2 < upr) v11 = ld_stream(a1 + u2);
+        }
+        b0[u] = v00;
+        if (u2 < upr) b0[u2] = v01;
+        if (two) {
+          b1[u] = v10;
+          if (u2 < upr) b1[u2] = v11;
+        }
       }
     }
+  }
+}
+
+/* Several whole planes of a box whose planes hold only a few rows (edges and corners): rows are enumerated across
+   planes so that all threads stay busy; one division per ROW (never per element). */
+template <int BYTES>
+__device__ __forceinline__ void copy_planes(const CopySeg &s, const char *__restrict__ sp, char *__restrict__ dp, unsigned nplanes) {
+  typedef typename VecT<BYTES>::type V;
+  const unsigned upr = s.rowBytes / BYTES, ny = s.ny, total = nplanes * ny;
+  if (s.totalWords) {
+    for (unsigned p = threadIdx.x; p < total; p += kThreads) {
+      const unsigned zi = p / ny, y = p - zi * ny;
+      copy_row_sectors(s, sp + (long long)zi * s.srcPitchZ + (long long)y * s.srcPitchY, dp + (long long)zi * s.dstPitchZ + (long long)y * s.dstPitchY);
+    }
+  } else if (upr <= 8) {
+    for (unsigned p = threadIdx.x; p < total; p += kThreads) {
+      const unsigned zi = p / ny, y = p - zi * ny;
+      const V *a = reinterpret_cast<const V *>(sp + (long long)zi * s.srcPitchZ + (long long)y * s.srcPitchY);
+      V *b = reinterpret_cast<V *>(dp + (long long)zi * s.dstPitchZ + (long long)y * s.dstPitchY);
+      V v[8];
 #pragma unroll
-    for (int k = 0; k < kUnroll; ++k) {
-      const unsigned i = base + k * kThreads;
-      if (i < total) *reinterpret_cast<V *>(dst + doff[k]) = v[k];
+      for (int u = 0; u < 8; ++u)
+        if (u < int(upr)) v[u] = ld_stream(a + u);
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        if (u < int(upr)) b[u] = v[u];
+    }
+  } else {
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, nwarps = kThreads / 32;
+    for (unsigned p = warp; p < total; p += nwarps) {
+      const unsigned zi = p / ny, y = p - zi * ny;
+      const V *a = reinterpret_cast<const V *>(sp + (long long)zi * s.srcPitchZ + (long long)y * s.srcPitchY);
+      V *b = reinterpret_cast<V *>(dp + (long long)zi * s.dstPitchZ + (long long)y * s.dstPitchY);
+      for (unsigned u = lane; u < upr; u += 32) b[u] = ld_stream(a + u);
     }
   }
 }
@@ -113,14 +176,24 @@ __global__ void __launch_bounds__(kThreads)
       __syncthreads();
       cached = ch.seg;
     }
-    const char *src = s.src[parity];
-    char *dst = s.dst[parity];
-    switch (s.vecLog2) {
-    case 4: copy_chunk<16>(s, src, dst, ch.row0, ch.nrows); break;
-    case 3: copy_chunk<8>(s, src, dst, ch.row0, ch.nrows); break;
-    case 2: copy_chunk<4>(s, src, dst, ch.row0, ch.nrows); break;
-    case 1: copy_chunk<2>(s, src, dst, ch.row0, ch.nrows); break;
-    default: copy_chunk<1>(s, src, dst, ch.row0, ch.nrows); break;
+    const char *src = s.src[parity] + (long long)ch.z * s.srcPitchZ + (long long)ch.y0 * s.srcPitchY;
+    char *dst = s.dst[parity] + (long long)ch.z * s.dstPitchZ + (long long)ch.y0 * s.dstPitchY;
+    if (ch.nplanes == 1) {
+      switch (s.vecLog2) {
+      case 4: copy_rows<16>(s, src, dst, ch.nrows); break;
+      case 3: copy_rows<8>(s, src, dst, ch.nrows); break;
+      case 2: copy_rows<4>(s, src, dst, ch.nrows); break;
+      case 1: copy_rows<2>(s, src, dst, ch.nrows); break;
+      default: copy_rows<1>(s, src, dst, ch.nrows); break;
+      }
+    } else {
+      switch (s.vecLog2) {
+      case 4: copy_planes<16>(s, src, dst, ch.nplanes); break;
+      case 3: copy_planes<8>(s, src, dst, ch.nplanes); break;
+      case 2: copy_planes<4>(s, src, dst, ch.nplanes); break;
+      case 1: copy_planes<2>(s, src, dst, ch.nplanes); break;
+      default: copy_planes<1>(s, src, dst, ch.nplanes); break;
+      }
     }
   }
   if (SIGNAL) {
@@ -158,17 +231,20 @@ __global__ void wait_flags_kernel(WaitSet ws, unsigned epoch, unsigned *errWord,
 /* a few boxes whose descriptors arrive as kernel parameters: blockIdx.y = box, blockIdx.x strides over row groups */
 __global__ void __launch_bounds__(kThreads) box_copy_batch_kernel(const __grid_constant__ SegBatch batch, int parity, unsigned rowsPerCta) {
   const CopySeg &s = batch.seg[blockIdx.y];
-  const unsigned rows = s.ny * s.nz;
-  const char *src = s.src[parity];
-  char *dst = s.dst[parity];
-  for (unsigned row0 = blockIdx.x * rowsPerCta; row0 < rows; row0 += gridDim.x * rowsPerCta) {
-    const unsigned n = min(rowsPerCta, rows - row0);
+  /* work items = (plane, group of rowsPerCta rows inside the plane); one division per item, none per element */
+  const unsigned groupsPerPlane = (s.ny + rowsPerCta - 1) / rowsPerCta;
+  const unsigned items = groupsPerPlane * s.nz;
+  for (unsigned it = blockIdx.x; it < items; it += gridDim.x) {
+    const unsigned z = it / groupsPerPlane, y0 = (it - z * groupsPerPlane) * rowsPerCta;
+    const unsigned n = min(rowsPerCta, s.ny - y0);
+    const char *src = s.src[parity] + (long long)z * s.srcPitchZ + (long long)y0 * s.srcPitchY;
+    char *dst = s.dst[parity] + (long long)z * s.dstPitchZ + (long long)y0 * s.dstPitchY;
     switch (s.vecLog2) {
-    case 4: copy_chunk<16>(s, src, dst, row0, n); break;
-    case 3: copy_chunk<8>(s, src, dst, row0, n); break;
-    case 2: copy_chunk<4>(s, src, dst, row0, n); break;
-    case 1: copy_chunk<2>(s, src, dst, row0, n); break;
-    default: copy_chunk<1>(s, src, dst, row0, n); break;
+    case 4: copy_rows<16>(s, src, dst, n); break;
+    case 3: copy_rows<8>(s, src, dst, n); break;
+    case 2: copy_rows<4>(s, src, dst, n); break;
+    case 1: copy_rows<2>(s, src, dst, n); break;
+    default: copy_rows<1>(s, src, dst, n); break;
     }
   }
 }
@@ -236,6 +312,30 @@ CopySeg make_seg(const BoxView &src, const Dim3 &srcPos, const BoxView &dst, con
   if (s.ny > 1) a |= (unsigned long long)src.pitchY | (unsigned long long)dst.pitchY;
   if (s.nz > 1) a |= (unsigned long long)src.pitchZ | (unsigned long long)dst.pitchZ;
   s.vecLog2 = log2_floor_pow2(a);
+  /* sector mode: thin rows whose destination touches row padding on the side(s) where it is not sector aligned */
+  s.padLoWords = s.totalWords = 0;
+  const bool pitchesOk = ((dst.pitchY | dst.pitchZ) & 31) == 0 && ((src.pitchY | src.pitchZ) & 3) == 0;
+  if (pitchesOk && (es % 4) == 0 && s.rowBytes <= 56) {
+    bool ok = true;
+    unsigned lo = 0, hi = 0;
+    for (int p = 0; p < 2 && ok; ++p) {
+      const unsigned long long start = (unsigned long long)(uintptr_t)s.dst[p], end = start + s.rowBytes;
+      const unsigned l = unsigned(start & 31), h = unsigned((32 - (end & 31)) & 31);
+      if (((uintptr_t)s.src[p] & 3) != 0) ok = false;
+      if (p == 0) {
+        lo = l;
+        hi = h;
+      } else if (l != lo || h != hi) {
+        ok = false;
+      }
+    }
+    if (lo && !(dstPos.x == 0 && (long long)lo <= dst.padLoBytes)) ok = false;
+    if (hi && !(dst.rowElems > 0 && dstPos.x + ext.x == dst.rowElems && (long long)hi <= dst.padHiBytes)) ok = false;
+    if (ok && (lo || hi) && lo + s.rowBytes + hi <= 64) {
+      s.padLoWords = (unsigned short)(lo / 4);
+      s.totalWords = (unsigned short)((lo + s.rowBytes + hi) / 4);
+    }
+  }
   return s;
 }
 
@@ -251,9 +351,17 @@ void CopyPlan::finalize(int dev, size_t chunkBytes) {
   chunks_.clear();
   for (size_t si = 0; si < segs_.size(); ++si) {
     const CopySeg &s = segs_[si];
-    const unsigned rows = s.ny * s.nz;
-    unsigned per = unsigned(std::max<size_t>(1, chunkBytes / std::max(1u, s.rowBytes)));
-    for (unsigned r = 0; r < rows; r += per) chunks_.push_back(CopyChunk{unsigned(si), r, std::min(per, rows - r), 0});
+    /* thin rows cost a sector each way whatever their length: count at least 32 bytes per row when sizing chunks */
+    const unsigned per = unsigned(std::min<size_t>(32768, std::max<size_t>(1, chunkBytes / std::max(32u, s.rowBytes))));
+    if (s.ny >= per) {
+      for (unsigned z = 0; z < s.nz; ++z)
+        for (unsigned y = 0; y < s.ny; y += per)
+          chunks_.push_back(CopyChunk{unsigned(si), z, y, (unsigned short)std::min(per, s.ny - y), (unsigned short)1});
+    } else { // few rows per plane (edges, corners): a chunk takes several whole planes
+      const unsigned planesPer = std::max(1u, per / s.ny);
+      for (unsigned z = 0; z < s.nz; z += planesPer)
+        chunks_.push_back(CopyChunk{unsigned(si), z, 0, (unsigned short)s.ny, (unsigned short)std::min(planesPer, s.nz - z)});
+    }
   }
   if (segs_.empty()) return;
   int prev = 0;
@@ -297,13 +405,11 @@ void CopyPlan::launch_and_signal(int parity, const SignalSet &sig, unsigned epoc
 
 void launch_box_copy(const SegBatch &batch, int parity, cudaStream_t stream) {
   if (batch.n == 0) return;
-  unsigned maxRows = 1, minRowBytes = 0xffffffffu;
-  for (unsigned i = 0; i < batch.n; ++i) {
-    maxRows = std::max(maxRows, batch.seg[i].ny * batch.seg[i].nz);
-    minRowBytes = std::min(minRowBytes, std::max(1u, batch.seg[i].rowBytes));
-  }
+  unsigned maxItems = 1, minRowBytes = 0xffffffffu;
+  for (unsigned i = 0; i < batch.n; ++i) minRowBytes = std::min(minRowBytes, std::max(32u, batch.seg[i].rowBytes));
   const unsigned rowsPerCta = std::max(1u, (32u * 1024u) / minRowBytes);
-  const unsigned gx = std::min((maxRows + rowsPerCta - 1) / rowsPerCta, 148u * 8u);
+  for (unsigned i = 0; i < batch.n; ++i) maxItems = std::max(maxItems, (batch.seg[i].ny + rowsPerCta - 1) / rowsPerCta * batch.seg[i].nz);
+  const unsigned gx = std::min(maxItems, 148u * 8u);
   box_copy_batch_kernel<<<dim3(gx, batch.n, 1), kThreads, 0, stream>>>(batch, parity, rowsPerCta);
   CUDA_RUNTIME(cudaGetLastError());
 }

@@ -199,9 +199,7 @@ class Exchanger {
   BoxView view_of(const Where &w, size_t qi, int myDev) {
     if (w.rank == dd_.rank_) return dd_.domains_[size_t(w.dom)].view(qi);
     RemoteSlab &rs = map_remote(myDev, w);
-    char *base = static_cast<char *>(rs.ptr);
-    const LocalDomain &sh = *rs.shadow;
-    return BoxView::pitched(base + sh.buffer_offset(qi, 0), base + sh.buffer_offset(qi, 1), sh.pitch(qi), sh.elem_size(qi));
+    return rs.shadow->view_at(qi, static_cast<char *>(rs.ptr));
   }
 
   unsigned *flags_of(const Where &w, int myDev) {

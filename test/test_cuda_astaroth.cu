@@ -1,0 +1,75 @@
+/* AstarothSim against the host loop: both stencils, fp32 and fp64, several fields, several subdomains, overlap on/off.
+   Average7 in fp32 is the reference's workload and must match bit for bit; Star19 is compared with an absolute tolerance of a
+   few ulp of 1 because the device contracts a*b+c into FMAs. */
+#include "harness.hpp"
+#include <cmath>
+#include <vector>
+#include "stencil/astaroth.hpp"
+
+namespace {
+double max_abs_err(const Dim3 &size, stencil::AstarothSim::Stencil st, bool fp64, int fields, const std::vector<int> &gpus, bool overlap, int iters,
+                   MethodFlags methods = MethodFlags::All) {
+  stencil::AstarothSim::Options opt;
+  opt.stencil = st;
+  opt.fp64 = fp64;
+  opt.fields = fields;
+  opt.gpus = gpus;
+  opt.overlap = overlap;
+  opt.tileZ = 8;
+  opt.methods = methods;
+  stencil::AstarothSim sim(size_t(size.x), size_t(size.y), size_t(size.z), opt);
+  /* start from the device's own initial field: the device and host sin() differ in the last bits of a double */
+  std::vector<double> ref = sim.gather(0), tmp;
+  double initErr = 0;
+  for (int64_t z = 0; z < size.z; ++z)
+    for (int64_t y = 0; y < size.y; ++y)
+      for (int64_t x = 0; x < size.x; ++x)
+        initErr = std::max(initErr, std::fabs(ref[size_t((z * size.y + y) * size.x + x)] - stencil::astaroth_init_value(Dim3(x, y, z), opt.period, fp64)));
+  if (!(initErr < 1e-6)) return 1e30; // the initial condition itself is wrong
+  for (int it = 0; it < iters; ++it) {
+    sim.step();
+    stencil::astaroth_host_step(tmp, ref, size, st, fp64, opt.dt);
+    ref.swap(tmp);
+  }
+  double worst = 0;
+  for (int f = 0; f < fields; ++f) {
+    const std::vector<double> got = sim.gather(f);
+    for (size_t i = 0; i < got.size(); ++i) {
+      const double e = std::fabs(got[i] - ref[i]); // field values are O(1)
+      if (!(e <= worst)) worst = e; // also catches NaN
+    }
+  }
+  return worst;
+}
+} // namespace
+
+TEST_CASE("astaroth: reference workload (1 x fp32, 7-point average) is bit exact", "[cuda][astaroth]") {
+  using S = stencil::AstarothSim::Stencil;
+  REQUIRE(max_abs_err(Dim3(40, 24, 20), S::Average7, false, 1, {0}, true, 4) == 0);
+  REQUIRE(max_abs_err(Dim3(40, 24, 20), S::Average7, false, 1, {0, 0}, true, 4) == 0);
+  REQUIRE(max_abs_err(Dim3(41, 23, 19), S::Average7, false, 2, {0, 0, 0}, false, 3) == 0);
+  REQUIRE(max_abs_err(Dim3(40, 24, 20), S::Average7, true, 2, {0, 0}, true, 3) == 0);
+}
+
+TEST_CASE("astaroth: 19-point radius-3 stencil, fp64 and fp32, many fields and subdomains", "[cuda][astaroth]") {
+  using S = stencil::AstarothSim::Stencil;
+  REQUIRE(max_abs_err(Dim3(40, 24, 20), S::Star19, true, 1, {0}, true, 3) < 1e-13);
+  REQUIRE(max_abs_err(Dim3(44, 26, 22), S::Star19, true, 8, {0, 0}, true, 3) < 1e-13);
+  REQUIRE(max_abs_err(Dim3(45, 27, 23), S::Star19, true, 3, {0, 0, 0, 0}, false, 3) < 1e-13);
+  REQUIRE(max_abs_err(Dim3(48, 26, 22), S::Star19, false, 4, {0, 0}, true, 3) < 5e-6);
+  REQUIRE(max_abs_err(Dim3(44, 26, 22), S::Star19, true, 2, {0, 0}, true, 3, MethodFlags::CudaMpi) < 1e-13);
+}
+
+TEST_CASE("astaroth: all visible GPUs", "[cuda][astaroth][multigpu]") {
+  int n = 0;
+  cudaGetDeviceCount(&n);
+  if (n < 2) {
+    std::printf("  (1 GPU visible: multi-GPU astaroth not exercised)\n");
+    return;
+  }
+  std::vector<int> gpus;
+  for (int i = 0; i < n; ++i) gpus.push_back(i);
+  using S = stencil::AstarothSim::Stencil;
+  REQUIRE(max_abs_err(Dim3(60, 40, 36), S::Star19, true, 8, gpus, true, 3) < 1e-13);
+  REQUIRE(max_abs_err(Dim3(60, 40, 36), S::Average7, false, 1, gpus, true, 3) == 0);
+}
