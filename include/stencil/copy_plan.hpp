@@ -32,6 +32,9 @@ struct CopySeg {
      is written as whole 32-byte sectors — padLoWords words of padding, the payload, padding up to totalWords — so the
      receiving memory system never has to read-modify-write a partially written sector. 0 = plain mode. */
   unsigned short padLoWords, totalWords;
+  /* 1: thin rows (<= 64 B) going to a dense destination (rows back to back): gathered through shared memory and
+     written as one contiguous, fully coalesced run — what a remote mailbox wants */
+  unsigned gatherDense;
 };
 
 struct CopyChunk {
@@ -49,6 +52,9 @@ struct BoxView {
   size_t elemSize;
   /* bytes of don't-care padding before logical x = 0 and after logical x = rowElems of EVERY row (0: none / unknown) */
   long long padLoBytes = 0, padHiBytes = 0, rowElems = 0;
+  /* destination lives behind NVLink: few large write packets matter more than instruction count (thin rows are then
+     gathered through shared memory and written as contiguous runs) */
+  bool acrossLink = false;
   static BoxView dense(void *p, const Dim3 &ext, size_t elemSize) {
     BoxView v;
     v.base[0] = v.base[1] = static_cast<char *>(p);

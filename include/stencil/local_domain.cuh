@@ -68,6 +68,13 @@ private:
   };
   std::vector<Layout> layout_;
 
+  /* x-side mailboxes (two parities): dense landing areas for halo messages whose rows are only a few cells long.
+     A remote GPU writes such a message here as one contiguous block (NVLink moves ~5 G packets/s whatever their
+     size, so 12-byte rows sent one by one reach a fifth of the link rate) and the owner scatters it into its halo. */
+  std::vector<size_t> mboxOff_; // [slot(side) * nq + qi], relative to the mailbox base; sides with x == 0 unused
+  size_t mboxBytes_ = 0;        // one parity
+  size_t mboxBase_[2] = {0, 0}; // slab offsets
+
   char *slab_ = nullptr;
   size_t slabBytes_ = 0;
   bool ownsSlab_ = false;
@@ -204,6 +211,12 @@ public:
   size_t buffer_offset(size_t qi, int which) const {
     return layout_.at(qi).off[which] + size_t(layout_[qi].lead) * elemSize_[qi];
   }
+  /* Mailbox of the halo on side `side` (side.x != 0) of quantity qi: slab offset of a dense halo_extent(side) box.
+     `parity` 0/1 alternates per exchange / iteration so a sender can fill one while the owner drains the other. */
+  size_t mailbox_offset(const Dim3 &side, size_t qi, int parity) const {
+    return mboxBase_[parity] + mboxOff_.at(size_t(DirectionMap<int>::slot(side)) * elemSize_.size() + qi);
+  }
+  size_t mailbox_bytes() const noexcept { return mboxBytes_; }
   /* first byte of the padded buffer (row 0 starts here, `lead_elems` before logical element (0,0,0)) */
   size_t buffer_start_offset(size_t qi, int which) const { return layout_.at(qi).off[which]; }
   int64_t lead_elems(size_t qi) const { return layout_.at(qi).lead; }

@@ -161,11 +161,41 @@ __device__ __forceinline__ void copy_planes(const CopySeg &s, const char *__rest
   }
 }
 
+constexpr unsigned kStageWords = 6144; // 24 KB of staging per CTA
+
+/* `rows` consecutive thin rows (row index -> source address through `rowSrc`) into a contiguous destination */
+template <typename RowSrc>
+__device__ __forceinline__ void gather_dense(const CopySeg &s, RowSrc rowSrc, char *__restrict__ dp, unsigned rows, unsigned *stage) {
+  const unsigned nw = s.rowBytes / 4;
+  const unsigned rowsPerPass = kStageWords / nw;
+  for (unsigned r0 = 0; r0 < rows; r0 += rowsPerPass) {
+    const unsigned n = min(rowsPerPass, rows - r0);
+    for (unsigned r = threadIdx.x; r < n; r += kThreads) {
+      const unsigned *a = reinterpret_cast<const unsigned *>(rowSrc(r0 + r));
+#pragma unroll
+      for (unsigned w = 0; w < 16; ++w)
+        if (w < nw) stage[r * nw + w] = ld_stream(a + w);
+    }
+    __syncthreads();
+    const unsigned words = n * nw;
+    unsigned *out = reinterpret_cast<unsigned *>(dp + (long long)r0 * s.rowBytes);
+    if ((reinterpret_cast<unsigned long long>(out) & 15ull) == 0) {
+      const unsigned quads = words / 4;
+      for (unsigned i = threadIdx.x; i < quads; i += kThreads) reinterpret_cast<uint4 *>(out)[i] = reinterpret_cast<const uint4 *>(stage)[i];
+      for (unsigned i = quads * 4 + threadIdx.x; i < words; i += kThreads) out[i] = stage[i];
+    } else {
+      for (unsigned i = threadIdx.x; i < words; i += kThreads) out[i] = stage[i];
+    }
+    __syncthreads();
+  }
+}
+
 template <bool SIGNAL>
 __global__ void __launch_bounds__(kThreads)
     box_copy_kernel(const CopySeg *__restrict__ segs, const CopyChunk *__restrict__ chunks, unsigned nchunks, int parity,
                     unsigned *done, SignalSet sig, unsigned epoch) {
   __shared__ CopySeg s;
+  __shared__ __align__(16) unsigned stage[kStageWords];
   unsigned cached = 0xffffffffu;
   for (unsigned c = blockIdx.x; c < nchunks; c += gridDim.x) {
     const CopyChunk ch = chunks[c];
@@ -178,7 +208,18 @@ __global__ void __launch_bounds__(kThreads)
     }
     const char *src = s.src[parity] + (long long)ch.z * s.srcPitchZ + (long long)ch.y0 * s.srcPitchY;
     char *dst = s.dst[parity] + (long long)ch.z * s.dstPitchZ + (long long)ch.y0 * s.dstPitchY;
-    if (ch.nplanes == 1) {
+    if (s.gatherDense) {
+      const long long spy = s.srcPitchY, spz = s.srcPitchZ;
+      if (ch.nplanes == 1) {
+        gather_dense(s, [=](unsigned r) { return src + (long long)r * spy; }, dst, ch.nrows, stage);
+      } else {
+        const unsigned ny = s.ny;
+        gather_dense(s, [=](unsigned p) {
+          const unsigned zi = p / ny, y = p - zi * ny;
+          return src + (long long)zi * spz + (long long)y * spy;
+        }, dst, unsigned(ch.nplanes) * ny, stage);
+      }
+    } else if (ch.nplanes == 1) {
       switch (s.vecLog2) {
       case 4: copy_rows<16>(s, src, dst, ch.nrows); break;
       case 3: copy_rows<8>(s, src, dst, ch.nrows); break;
@@ -335,6 +376,14 @@ CopySeg make_seg(const BoxView &src, const Dim3 &srcPos, const BoxView &dst, con
       s.padLoWords = (unsigned short)(lo / 4);
       s.totalWords = (unsigned short)((lo + s.rowBytes + hi) / 4);
     }
+  }
+  /* thin rows into a dense destination: gather through shared memory */
+  s.gatherDense = 0;
+  if (dst.acrossLink && s.totalWords == 0 && (es % 4) == 0 && s.rowBytes <= 64 && dst.pitchY == (long long)s.rowBytes &&
+      (s.nz == 1 || dst.pitchZ == (long long)s.rowBytes * s.ny) && ((src.pitchY | src.pitchZ) & 3) == 0) {
+    bool ok = true;
+    for (int p = 0; p < 2; ++p) ok = ok && (((uintptr_t)s.src[p] | (uintptr_t)s.dst[p]) & 3) == 0;
+    s.gatherDense = ok ? 1u : 0u;
   }
   return s;
 }

@@ -33,6 +33,10 @@ LocalDomain &LocalDomain::operator=(LocalDomain &&o) noexcept {
   elemSize_ = std::move(o.elemSize_);
   name_ = std::move(o.name_);
   layout_ = std::move(o.layout_);
+  mboxOff_ = std::move(o.mboxOff_);
+  mboxBytes_ = o.mboxBytes_;
+  mboxBase_[0] = o.mboxBase_[0];
+  mboxBase_[1] = o.mboxBase_[1];
   slab_ = o.slab_;
   slabBytes_ = o.slabBytes_;
   ownsSlab_ = o.ownsSlab_;
@@ -103,6 +107,25 @@ void LocalDomain::compute_layout() {
       l.off[b] = off;
       off += l.bufBytes;
     }
+  }
+  /* x-side mailboxes */
+  const size_t nq = elemSize_.size();
+  mboxOff_.assign(27 * nq, 0);
+  mboxBytes_ = 0;
+  for (int z = -1; z <= 1; ++z)
+    for (int y = -1; y <= 1; ++y)
+      for (int x = -1; x <= 1; x += 2) {
+        const Dim3 side(x, y, z);
+        if (radius_.dir(side) == 0) continue;
+        for (size_t qi = 0; qi < nq; ++qi) {
+          mboxOff_[size_t(DirectionMap<int>::slot(side)) * nq + qi] = mboxBytes_;
+          mboxBytes_ += round_up_multiple(size_t(halo_bytes(side, int64_t(qi))), 256);
+        }
+      }
+  for (int p = 0; p < 2; ++p) {
+    off = round_up_multiple(off, slabAlign);
+    mboxBase_[p] = off;
+    off += mboxBytes_;
   }
   slabBytes_ = round_up_multiple(off, slabAlign);
 }

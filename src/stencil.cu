@@ -83,12 +83,16 @@ class Exchanger {
 
   std::vector<RcStream> streams_;
   std::vector<cudaEvent_t> pushDone_;
+  /* STENCIL_EXCHANGE_TRACE=n: print per-subdomain device times of the first n exchanges (push kernel, flag wait) */
+  int trace_ = 0;
+  std::vector<cudaEvent_t> trA_, trB_, trC_;
   unsigned epoch_ = 0;
   unsigned *errWord_ = nullptr; // pinned + mapped
   unsigned long long timeoutNs_;
 
   /* ---- direct push (Kernel + NvlinkDirect) ---- */
   std::vector<CopyPlan> push_;
+  std::vector<CopyPlan> scatter_; // after the flags: my x-side mailboxes -> my halo cells (thin rows from other GPUs)
   std::vector<SignalSet> arriveSig_; // flags I raise in cross-device neighbours after my push
   std::vector<WaitSet> arriveWait_;  // my flags they raise
   std::vector<SignalSet> readySig_;  // cross-PROCESS neighbours: "my halos may be overwritten for epoch e"
@@ -202,6 +206,27 @@ class Exchanger {
     return rs.shadow->view_at(qi, static_cast<char *>(rs.ptr));
   }
 
+  /* dense landing box for the halo on side `side` of quantity qi of subdomain w, as addressed from device myDev */
+  BoxView mailbox_of(const Where &w, const Dim3 &side, size_t qi, const Dim3 &ext, int myDev) {
+    const LocalDomain *ld;
+    char *base;
+    if (w.rank == dd_.rank_) {
+      ld = &dd_.domains_[size_t(w.dom)];
+      base = static_cast<char *>(ld->slab());
+    } else {
+      RemoteSlab &rs = map_remote(myDev, w);
+      ld = rs.shadow.get();
+      base = static_cast<char *>(rs.ptr);
+    }
+    BoxView v = BoxView::dense(base + ld->mailbox_offset(side, qi, 0), ext, ld->elem_size(qi));
+    v.base[1] = base + ld->mailbox_offset(side, qi, 1);
+    v.acrossLink = w.dev != myDev;
+    return v;
+  }
+
+  /* rows this short are sent to another GPU through its mailbox instead of straight into its halo */
+  static bool thin_for_link(const Dim3 &dir, const Dim3 &ext, size_t elemSize) { return dir.x != 0 && size_t(ext.x) * elemSize <= 64 && elemSize % 4 == 0; }
+
   unsigned *flags_of(const Where &w, int myDev) {
     if (w.rank == dd_.rank_) return dd_.domains_[size_t(w.dom)].arrive_flags();
     return reinterpret_cast<unsigned *>(map_remote(myDev, w).ptr);
@@ -287,12 +312,22 @@ public:
     CUDA_RUNTIME(cudaHostAlloc(&errWord_, sizeof(unsigned), cudaHostAllocMapped | cudaHostAllocPortable));
     *errWord_ = 0;
 
+    if (const char *e = std::getenv("STENCIL_EXCHANGE_TRACE")) trace_ = std::atoi(e);
     for (size_t di = 0; di < nd_; ++di) {
       streams_.emplace_back(dd_.domains_[di].gpu(), RcStream::Priority::HIGH);
       DevGuard g(dd_.domains_[di].gpu());
       cudaEvent_t e;
       CUDA_RUNTIME(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
       pushDone_.push_back(e);
+      if (trace_) {
+        cudaEvent_t a, b, c;
+        CUDA_RUNTIME(cudaEventCreate(&a));
+        CUDA_RUNTIME(cudaEventCreate(&b));
+        CUDA_RUNTIME(cudaEventCreate(&c));
+        trA_.push_back(a);
+        trB_.push_back(b);
+        trC_.push_back(c);
+      }
     }
 
     /* publish every rank's slab handles (also a barrier: all slabs exist and their flags are zeroed after this) */
@@ -319,6 +354,7 @@ public:
     }
 
     push_.resize(nd_);
+    scatter_.resize(nd_);
     arriveSig_.assign(nd_, SignalSet{0, {}});
     arriveWait_.assign(nd_, WaitSet{0, {}});
     readySig_.assign(nd_, SignalSet{0, {}});
@@ -361,7 +397,12 @@ public:
                 const Dim3 srcPos = dom.halo_pos(dir, false);
                 const Dim3 nbSize = pl->subdomain_size(nb.idx);
                 const Dim3 dstPos = stencil::halo_pos(dir * -1, nbSize, radius, true);
-                for (size_t qi = 0; qi < nq; ++qi) push_[di].add(dom.view(qi), srcPos, view_of(nb, qi, me.dev), dstPos, ext);
+                for (size_t qi = 0; qi < nq; ++qi) {
+                  if (nb.dev != me.dev && thin_for_link(dir, ext, dd_.elemSizes_[qi]))
+                    push_[di].add(dom.view(qi), srcPos, mailbox_of(nb, dir * -1, qi, ext, me.dev), Dim3(0, 0, 0), ext);
+                  else
+                    push_[di].add(dom.view(qi), srcPos, view_of(nb, qi, me.dev), dstPos, ext);
+                }
                 break;
               }
               case Route::PeerCopy: peerOut[di][RD(nb.rank, nb.dom)].push_back(msg); break;
@@ -372,6 +413,13 @@ public:
             if (iRecv) {
               /* message from nb travelling in direction -dir */
               const Message msg(dir * -1, nb.dom, int(di));
+              if ((route == Route::Direct || route == Route::Kernel) && nb.dev != me.dev) {
+                /* the sender used my mailbox for the quantities whose rows are thin: scatter those into the halo */
+                const Dim3 ext = dom.halo_extent(dir);
+                for (size_t qi = 0; qi < nq; ++qi)
+                  if (thin_for_link(dir, ext, dd_.elemSizes_[qi]))
+                    scatter_[di].add(mailbox_of(me, dir, qi, ext, me.dev), Dim3(0, 0, 0), dom.view(qi), dom.halo_pos(dir, true), ext);
+              }
               if (route == Route::Staged) stagedIn[di][RD(nb.rank, nb.dom)].push_back(msg);
               if (route == Route::Colo) coloIn[di][RD(nb.rank, nb.dom)].push_back(msg);
             }
@@ -397,6 +445,7 @@ public:
           }
       sameDevDeps_[di].assign(depSet.begin(), depSet.end());
       push_[di].finalize(dom.gpu());
+      scatter_[di].finalize(dom.gpu());
     }
 
     /* peer copies: one packer/unpacker pair per (src, dst) local pair */
@@ -551,7 +600,9 @@ public:
       if (push_[di].empty() && arriveSig_[di].n == 0) continue;
       DevGuard g(doms[di].gpu());
       launch_wait_flags(readyWait_[di], epoch_, errWord_, timeoutNs_, streams_[di]);
+      if (trace_) CUDA_RUNTIME(cudaEventRecord(trA_[di], streams_[di]));
       push_[di].launch_and_signal(doms[di].parity(), arriveSig_[di], epoch_, streams_[di]);
+      if (trace_) CUDA_RUNTIME(cudaEventRecord(trB_[di], streams_[di]));
       CUDA_RUNTIME(cudaEventRecord(pushDone_[di], streams_[di]));
     }
 
@@ -566,6 +617,8 @@ public:
       DevGuard g(doms[di].gpu());
       for (int dep : sameDevDeps_[di]) CUDA_RUNTIME(cudaStreamWaitEvent(streams_[di], pushDone_[size_t(dep)], 0));
       launch_wait_flags(arriveWait_[di], epoch_, errWord_, timeoutNs_, streams_[di]);
+      scatter_[di].launch(doms[di].parity(), streams_[di]);
+      if (trace_) CUDA_RUNTIME(cudaEventRecord(trC_[di], streams_[di]));
     }
 
     /* 6. host progress loop for the host-mediated transports */
@@ -611,6 +664,17 @@ public:
     for (size_t di = 0; di < nd_; ++di) {
       DevGuard g(doms[di].gpu());
       CUDA_RUNTIME(cudaStreamSynchronize(streams_[di]));
+    }
+    if (trace_ > 0) {
+      --trace_;
+      for (size_t di = 0; di < nd_; ++di) {
+        if (push_[di].empty()) continue;
+        float push = 0, wait = 0;
+        cudaEventElapsedTime(&push, trA_[di], trB_[di]);
+        cudaEventElapsedTime(&wait, trB_[di], trC_[di]);
+        std::fprintf(stderr, "exchange %u rank %d dom %zu: push %.1f us (%zu B, %zu segs, %zu chunks), flag wait %.1f us\n", epoch_, dd_.rank_, di,
+                     push * 1e3, push_[di].bytes(), push_[di].num_segments(), push_[di].num_chunks(), wait * 1e3);
+      }
     }
     for (ColoRecv &r : coloRecvs_) {
       const char ack = 1;
