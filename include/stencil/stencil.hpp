@@ -84,6 +84,8 @@ struct NeighborInfo {
   Dim3 idx, size;
   BoxView view;             // base[b] = buffer b (0/1) of the quantity, logical element (0,0,0)
   unsigned *control = nullptr; // the neighbour's control block (LocalDomain::kControlBytes), as mapped locally
+  char *slab = nullptr;               // base of the neighbour's slab as mapped locally
+  const LocalDomain *layout = nullptr; // its geometry/layout (a shadow object for other ranks): slab offsets, mailboxes
 };
 } // namespace stencil
 

@@ -45,6 +45,7 @@ constexpr int kLanes = 32, kRows = 8, kThreads = kLanes * kRows, kVec = 4, kTile
 /* TMA variant geometry */
 constexpr int kTmaRows = 16, kTmaBoxX = kTileX + 8, kTmaBoxY = kTmaRows + 2, kTmaStages = 6;
 constexpr int kTmaConsumerWarps = kTmaRows / 2, kTmaThreads = kTmaConsumerWarps * 32;
+constexpr int kMaxTileZ = 64; // bound on Options::tileZ for the TMA variant (size of the x-face staging tile)
 constexpr int kTmaLag = 2; // the producer refills the slot that was consumed kTmaLag planes ago
 constexpr int kTmaPlaneBytes = kTmaBoxX * kTmaBoxY * 4;
 constexpr int kTmaStageBytes = (kTmaPlaneBytes + 127) / 128 * 128;
@@ -75,6 +76,7 @@ struct JacobiParams {
   /* fused push */
   float *nb[6];            // neighbour's next buffer: address of ITS halo cell that receives my face cell (0,0) ...
   long long nbPitchX[6], nbPitchXY[6];
+  float *mbox[2];          // XM / XP: the neighbour's dense x-side mailbox (nullptr: store straight into its halo)
   unsigned *nbFlag[6];     // neighbour flag to raise (nullptr: ordered by the stream / same kernel)
   const unsigned *myFlag[6]; // my flag the neighbour raises (nullptr: no wait)
   unsigned epoch;          // iteration number being computed (1-based)
@@ -401,6 +403,8 @@ __device__ __forceinline__ bool tile_near_sphere(const JacobiParams &P, const Ti
 template <bool FUSED, int MINB>
 __global__ void __launch_bounds__(kTmaThreads, MINB) jacobi7_tma_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ JacobiParams P) {
   extern __shared__ __align__(128) unsigned char smem[];
+  /* x-face values of this tile on their way to another GPU's mailbox: [face][plane of the tile][row] */
+  __shared__ float xstage[FUSED ? 2 : 1][FUSED ? kMaxTileZ : 1][kTmaRows];
   unsigned long long *full = reinterpret_cast<unsigned long long *>(smem + kTmaStages * kTmaStageBytes);
   unsigned long long *empty = full + kTmaStages;
   const Tile t = P.tiles[blockIdx.x];
@@ -445,6 +449,7 @@ __global__ void __launch_bounds__(kTmaThreads, MINB) jacobi7_tma_kernel(const __
     float *qx[2] = {nullptr, nullptr};
     long long qxStride = 0;
     int qxK = 0;
+    int qxMail = -1; // >= 0: this lane's x-face cells go to xstage[qxMail] (and from there to the neighbour's mailbox)
     bool qxWide = false; // the destination halo cell starts (XM) or ends (XP) a 32-byte sector of otherwise unused cells
     unsigned yzFaces = 0;
     if (FUSED && t.faces) {
@@ -457,6 +462,7 @@ __global__ void __launch_bounds__(kTmaThreads, MINB) jacobi7_tma_kernel(const __
       } else if (ownsXM || ownsXP) {
         const int f = ownsXM ? XM : XP;
         qxK = ownsXM ? 0 : P.sx - 1 - x0;
+        if (P.mbox[f]) qxMail = f;
         qxStride = P.nbPitchXY[f];
         /* start of the 32-byte sector holding the destination halo cell: my x=0 lands in the neighbour's +x halo, the
            first cell after its interior (sector = halo + 7 padding cells); my last x lands in its -x halo, the last
@@ -526,7 +532,9 @@ __global__ void __launch_bounds__(kTmaThreads, MINB) jacobi7_tma_kernel(const __
           }
           store_cells<false>(P, t, x0, y0 + r, z, o);
           if (FUSED && t.faces) {
-            if (qx[r]) {
+            if (qxMail >= 0) {
+              xstage[qxMail][z - z0][r0 + r] = qxK == 0 ? o.x : (qxK == 1 ? o.y : (qxK == 2 ? o.z : o.w));
+            } else if (qx[r]) {
               /* The halo cell shares its 32-byte sector with row padding only (LocalDomain layout), so the whole
                  sector is written: a 4-byte store would make the receiver's memory system read-modify-write the
                  sector (ECC), which measured as +160 MB of DRAM reads per 512^3 iteration. */
@@ -555,9 +563,23 @@ __global__ void __launch_bounds__(kTmaThreads, MINB) jacobi7_tma_kernel(const __
     }
   }
 
-  if (FUSED && t.faces && !(P.debugSkip & 1u)) {
+  if (FUSED && t.faces) {
     __syncthreads();
-    signal_neighbours(P);
+    /* x faces bound for another GPU: one 64-byte run (16 rows) per plane instead of one packet per row. NVLink moves a
+       roughly fixed number of packets per second, so per-row stores reach a fraction of the link rate. Layout of the
+       mailbox: dense [plane][row] of the neighbour's (1, sy, sz) halo box. */
+    for (int f = 0; f < 2; ++f) {
+      if (!((t.faces >> f) & 1u) || !P.mbox[f]) continue;
+      const int ybase = t.ty * kTmaRows, nz = z1 - z0;
+      for (int i = threadIdx.x; i < nz * kTmaRows; i += kTmaThreads) {
+        const int zl = i / kTmaRows, r = i % kTmaRows;
+        if (ybase + r < P.sy) P.mbox[f][(long long)(z0 + zl) * P.sy + ybase + r] = xstage[f][zl][r];
+      }
+    }
+    if (!(P.debugSkip & 1u)) {
+      __syncthreads();
+      signal_neighbours(P);
+    }
   }
 }
 
@@ -604,6 +626,7 @@ struct Jacobi3D::Impl {
     CUtensorMap tmap[2];  // per parity: the curr buffer as a 3-D tensor (padded row, rows, planes)
     std::vector<int> sameDevDeps;
     WaitSet finalWait;
+    CopyPlan scatter; // my x-side mailboxes -> the x halos of `next` (faces whose neighbour is on another GPU)
   };
   std::vector<Dom> doms;
   unsigned iter = 0;
@@ -716,6 +739,8 @@ Jacobi3D::~Jacobi3D() {
 
 void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
   if (opt_.tileZ < 1) opt_.tileZ = 32;
+  if (opt_.useTma && opt_.tileZ > kMaxTileZ) opt_.tileZ = kMaxTileZ;
+  if (std::getenv("STENCIL_JACOBI_XMAILBOX")) opt_.xMailbox = true;
   dd_.reset(comm ? new DistributedDomain(x, y, z, *comm) : new DistributedDomain(x, y, z));
   if (!opt_.gpus.empty()) dd_->set_gpus(opt_.gpus);
   Radius radius = Radius::constant(0);
@@ -795,6 +820,19 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
         if (nbs[f].sameRank && nbs[f].sameDevice && nbs[f].dom != int(di)) deps.insert(nbs[f].dom);
       }
     d.sameDevDeps.assign(deps.begin(), deps.end());
+    if (opt_.mode == Mode::Fused && impl_->useTma && opt_.xMailbox) {
+      for (int f = XM; f <= XP; ++f) {
+        if (!nbs[f].exists || nbs[f].sameDevice) continue;
+        /* what the neighbour on side f put into my mailbox belongs in the x halo of `next` on that side */
+        const Dim3 side = kFaceDir[f], ext = ld.halo_extent(side);
+        BoxView src = BoxView::dense(static_cast<char *>(ld.slab()) + ld.mailbox_offset(side, h_.id(), 0), ext, sizeof(float));
+        src.base[1] = static_cast<char *>(ld.slab()) + ld.mailbox_offset(side, h_.id(), 1);
+        BoxView dst = ld.view(h_.id());
+        std::swap(dst.base[0], dst.base[1]); // parity p selects curr = buffer p; the target is next = buffer p^1
+        d.scatter.add(src, Dim3(0, 0, 0), dst, ld.halo_pos(side, true), ext);
+      }
+      d.scatter.finalize(ld.gpu());
+    }
 
     const int rows = impl_->rows;
     const std::vector<Tile> all = make_tiles(Dim3(0, 0, 0), sz, sz, rows, opt_.tileZ, faceMask, &d.nBoundary, opt_.boundaryFirst);
@@ -868,6 +906,11 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
         P.nb[f] = nbase + (rz * npxy + ry * npx + rx);
         P.nbPitchX[f] = npx;
         P.nbPitchXY[f] = npxy;
+        if ((f == XM || f == XP) && impl_->useTma && opt_.xMailbox && !n.sameDevice) {
+          /* my x = 0 cells are the neighbour's +x halo, my last x its -x halo; mailbox parity = buffer parity */
+          const Dim3 side = kFaceDir[f] * -1;
+          P.mbox[f] = reinterpret_cast<float *>(n.slab + n.layout->mailbox_offset(side, h_.id(), parity));
+        }
         const bool viaFlag = !(n.sameRank && n.sameDevice);
         if (viaFlag) {
           /* I raise the slot "from direction -dir" in the neighbour; the neighbour raises slot "from dir" in me */
@@ -938,8 +981,15 @@ void Jacobi3D::step() {
     }
     for (size_t di = 0; di < nd; ++di) {
       DevGuard g(doms[di].gpu());
-      launch(di, impl_->doms[di].tilesAll, impl_->doms[di].nAll, doms[di].get_compute_region(), true);
-      if (!impl_->doms[di].sameDevDeps.empty() || nd > 1) CUDA_RUNTIME(cudaEventRecord(impl_->doms[di].done, impl_->doms[di].stream));
+      Impl::Dom &d = impl_->doms[di];
+      launch(di, d.tilesAll, d.nAll, doms[di].get_compute_region(), true);
+      if (!d.scatter.empty()) {
+        /* x faces from other GPUs arrive in my mailbox: once their flags are up, move them into the halo of `next` */
+        launch_wait_flags(d.finalWait, impl_->iter, impl_->err, 5000000000ull, d.stream);
+        d.scatter.launch(doms[di].parity(), d.stream);
+        launches_ += 2;
+      }
+      if (!d.sameDevDeps.empty() || nd > 1) CUDA_RUNTIME(cudaEventRecord(d.done, d.stream));
     }
     dd_->swap();
     return;

@@ -297,6 +297,14 @@ public:
     if (n.reachable) {
       n.view = view_of(nb, qi, me.dev);
       n.control = flags_of(nb, me.dev);
+      if (n.sameRank) {
+        n.layout = &dd_.domains_[size_t(nb.dom)];
+        n.slab = static_cast<char *>(n.layout->slab());
+      } else {
+        RemoteSlab &rs = map_remote(me.dev, nb);
+        n.layout = rs.shadow.get();
+        n.slab = static_cast<char *>(rs.ptr);
+      }
     }
     return n;
   }
