@@ -79,6 +79,7 @@ struct JacobiParams {
   float *mbox[2];          // XM / XP: the neighbour's dense x-side mailbox (nullptr: store straight into its halo)
   unsigned *nbFlag[6];     // neighbour flag to raise (nullptr: ordered by the stream / same kernel)
   const unsigned *myFlag[6]; // my flag the neighbour raises (nullptr: no wait)
+  unsigned flagMask;       // faces whose neighbour is synchronised through a flag (another GPU); 0 on a single GPU
   unsigned epoch;          // iteration number being computed (1-based)
   unsigned nBoundary;      // number of tiles that push
   unsigned *done;          // boundary tile counter
@@ -140,7 +141,7 @@ template <bool FUSED> __global__ void __launch_bounds__(kThreads) jacobi7_kernel
   const Tile t = P.tiles[blockIdx.x];
   const int lane = threadIdx.x & (kLanes - 1), row = threadIdx.x / kLanes;
 
-  if (FUSED && t.faces) {
+  if (FUSED && (t.faces & P.flagMask)) {
     /* boundary tiles read halo cells: wait until every neighbour has delivered iteration epoch-1 */
     if (threadIdx.x < 6) {
       const unsigned *f = P.myFlag[threadIdx.x];
@@ -261,10 +262,10 @@ template <bool FUSED> __global__ void __launch_bounds__(kThreads) jacobi7_kernel
     }
   }
 
-  if (FUSED && t.faces) {
+  if (FUSED && (t.faces & P.flagMask)) {
     __syncthreads();
     if (threadIdx.x == 0) {
-      __threadfence_system();
+      __threadfence();
       const unsigned prev = atomicAdd(P.done, 1u);
       if (prev == P.nBoundary - 1) {
         *P.done = 0;
@@ -400,6 +401,24 @@ __device__ __forceinline__ bool tile_near_sphere(const JacobiParams &P, const Ti
   return (dy * dy + dz * dz + dh * dh < P.r2) || (dy * dy + dz * dz + dc * dc < P.r2);
 }
 
+/* rare paths of the plane loop, kept out of line so they cost the hot path nothing but a branch */
+__device__ __noinline__ float4 apply_spheres(const JacobiParams &P, int x0, int y, int z, float4 o) {
+  /* by value in and out: passing the result array by reference would pin it in local memory for every plane */
+  const long long gx = P.ox + x0, gy = P.oy + y, gz = P.oz + z;
+  o.x = sphere_or(P, gx, gy, gz, o.x);
+  o.y = sphere_or(P, gx + 1, gy, gz, o.y);
+  o.z = sphere_or(P, gx + 2, gy, gz, o.z);
+  o.w = sphere_or(P, gx + 3, gy, gz, o.w);
+  return o;
+}
+
+__device__ __noinline__ void store_partial(const JacobiParams &P, float *dp, int x0, float4 o) {
+  const float ov[4] = {o.x, o.y, o.z, o.w};
+#pragma unroll
+  for (int k = 0; k < kVec; ++k)
+    if (x0 + k >= P.lox && x0 + k < P.hix) dp[k] = ov[k];
+}
+
 template <bool FUSED, int MINB>
 __global__ void __launch_bounds__(kTmaThreads, MINB) jacobi7_tma_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ JacobiParams P) {
   extern __shared__ __align__(128) unsigned char smem[];
@@ -417,7 +436,7 @@ __global__ void __launch_bounds__(kTmaThreads, MINB) jacobi7_tma_kernel(const __
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (FUSED && t.faces) wait_neighbours(P);
+  if (FUSED && (t.faces & P.flagMask)) wait_neighbours(P);
   __syncthreads();
 
   const int z0 = max(int(t.tz) * P.tileZ, P.loz), z1 = min(int(t.tz + 1) * P.tileZ, P.hiz);
@@ -473,72 +492,86 @@ __global__ void __launch_bounds__(kTmaThreads, MINB) jacobi7_tma_kernel(const __
           if (y0 + r < P.sy) qx[r] = P.nb[f] + (long long)(y0 + r) * P.nbPitchX[f] + (qxWide ? sectorShift : 0);
       }
     }
+    /* Everything that does not change from plane to plane is decided here, so the plane loop is loads, adds and one
+       store per row: where this lane's rows go (running pointers, advanced by one plane per iteration), whether the
+       store is a full vector, and whether this lane has anything to push at all. */
+    float *dp[2];
+    int mode[2]; // 0: nothing to store, 1: full 16-byte store, 2: partial row segment (region edge)
+    bool rowPush[2];
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      const int y = y0 + r;
+      const bool in = y >= P.loy && y < P.hiy && x0 < P.hix && x0 + kVec > P.lox;
+      mode[r] = !in ? 0 : ((x0 >= P.lox && x0 + kVec <= P.hix) ? 1 : 2);
+      dp[r] = P.dst + (long long)z0 * P.pitchXY + (long long)y * P.pitchX + x0;
+      /* y faces are whole rows of a boundary warp; z faces are handled per plane below */
+      rowPush[r] = FUSED && yzFaces && in && ((yzFaces & 3u) || y == 0 || y == P.sy - 1);
+    }
+    const bool zPush = FUSED && (yzFaces & ((1u << ZM) | (1u << ZP)));
+    const long long planeStride = P.pitchXY;
     float4 cm2[2], cm1[2], part[2];
     cm2[0] = cm2[1] = cm1[0] = cm1[1] = part[0] = part[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+    int s = 0;
+    unsigned phase = 0;
     for (int i = 0; i < nplanes; ++i) {
-      const int s = i % kTmaStages;
-      mbar_wait(&full[s], (i / kTmaStages) & 1);
+      mbar_wait(&full[s], phase);
       const float *pl = reinterpret_cast<const float *>(smem + s * kTmaStageBytes);
       /* smem row j holds compute row ty*rows + j - 1; smem column 4 + k holds compute x = tx*128 + k */
       const float *rowC0 = pl + (r0 + 1) * kTmaBoxX + 4 + lane * kVec;
       const float4 c0 = *reinterpret_cast<const float4 *>(rowC0);
       const float4 c1 = *reinterpret_cast<const float4 *>(rowC0 + kTmaBoxX);
-      float4 pn[2];
-      if (i >= 1 && i <= nplanes - 2) {
-        const float4 south = *reinterpret_cast<const float4 *>(rowC0 - kTmaBoxX);     // y-1 of row r0
-        const float4 north = *reinterpret_cast<const float4 *>(rowC0 + 2 * kTmaBoxX); // y+1 of row r1
-        float w0 = __shfl_up_sync(0xffffffffu, c0.w, 1), e0 = __shfl_down_sync(0xffffffffu, c0.x, 1);
-        float w1 = __shfl_up_sync(0xffffffffu, c1.w, 1), e1 = __shfl_down_sync(0xffffffffu, c1.x, 1);
-        if (lane == 0) {
-          w0 = rowC0[-1];
-          w1 = rowC0[kTmaBoxX - 1];
-        }
-        if (lane == 31) {
-          e0 = rowC0[kVec];
-          e1 = rowC0[kTmaBoxX + kVec];
-        }
-        /* ((px + mx) + py) + my, the first four terms of the reference's sum */
-        pn[0].x = ((c0.y + w0) + c1.x) + south.x;
-        pn[0].y = ((c0.z + c0.x) + c1.y) + south.y;
-        pn[0].z = ((c0.w + c0.y) + c1.z) + south.z;
-        pn[0].w = ((e0 + c0.z) + c1.w) + south.w;
-        pn[1].x = ((c1.y + w1) + north.x) + c0.x;
-        pn[1].y = ((c1.z + c1.x) + north.y) + c0.y;
-        pn[1].z = ((c1.w + c1.y) + north.z) + c0.z;
-        pn[1].w = ((e1 + c1.z) + north.w) + c0.w;
-      } else {
-        pn[0] = pn[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+      const float4 south = *reinterpret_cast<const float4 *>(rowC0 - kTmaBoxX);     // y-1 of row r0
+      const float4 north = *reinterpret_cast<const float4 *>(rowC0 + 2 * kTmaBoxX); // y+1 of row r1
+      float w0 = __shfl_up_sync(0xffffffffu, c0.w, 1), e0 = __shfl_down_sync(0xffffffffu, c0.x, 1);
+      float w1 = __shfl_up_sync(0xffffffffu, c1.w, 1), e1 = __shfl_down_sync(0xffffffffu, c1.x, 1);
+      if (lane == 0) {
+        w0 = rowC0[-1];
+        w1 = rowC0[kTmaBoxX - 1];
+      }
+      if (lane == 31) {
+        e0 = rowC0[kVec];
+        e1 = rowC0[kTmaBoxX + kVec];
       }
       /* this stage's data is in registers now: hand the slot back before doing the arithmetic and the stores */
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty[s]);
       if (threadIdx.x == 0 && i + kTmaStages - kTmaLag < nplanes) issue(i + kTmaStages - kTmaLag);
+      if (++s == kTmaStages) {
+        s = 0;
+        phase ^= 1u;
+      }
       if (i >= 2) {
         const int z = z0 + i - 2; // output plane: above = centre of this plane, below = centre two planes back
-        const float4 cc[2] = {c0, c1};
+        float4 o[2];
+        o[0].x = div6((part[0].x + c0.x) + cm2[0].x);
+        o[0].y = div6((part[0].y + c0.y) + cm2[0].y);
+        o[0].z = div6((part[0].z + c0.z) + cm2[0].z);
+        o[0].w = div6((part[0].w + c0.w) + cm2[0].w);
+        o[1].x = div6((part[1].x + c1.x) + cm2[1].x);
+        o[1].y = div6((part[1].y + c1.y) + cm2[1].y);
+        o[1].z = div6((part[1].z + c1.z) + cm2[1].z);
+        o[1].w = div6((part[1].w + c1.w) + cm2[1].w);
+        if (nearSphere) {
+          o[0] = apply_spheres(P, x0, y0, z, o[0]);
+          o[1] = apply_spheres(P, x0, y0 + 1, z, o[1]);
+        }
 #pragma unroll
         for (int r = 0; r < 2; ++r) {
-          float4 o;
-          o.x = div6((part[r].x + cc[r].x) + cm2[r].x);
-          o.y = div6((part[r].y + cc[r].y) + cm2[r].y);
-          o.z = div6((part[r].z + cc[r].z) + cm2[r].z);
-          o.w = div6((part[r].w + cc[r].w) + cm2[r].w);
-          if (nearSphere) {
-            const long long gx = P.ox + x0, gy = P.oy + y0 + r, gz = P.oz + z;
-            o.x = sphere_or(P, gx, gy, gz, o.x);
-            o.y = sphere_or(P, gx + 1, gy, gz, o.y);
-            o.z = sphere_or(P, gx + 2, gy, gz, o.z);
-            o.w = sphere_or(P, gx + 3, gy, gz, o.w);
-          }
-          store_cells<false>(P, t, x0, y0 + r, z, o);
-          if (FUSED && t.faces) {
+          if (mode[r] == 1)
+            *reinterpret_cast<float4 *>(dp[r]) = o[r];
+          else if (mode[r] == 2)
+            store_partial(P, dp[r], x0, o[r]);
+          dp[r] += planeStride;
+        }
+        if (FUSED && t.faces) {
+#pragma unroll
+          for (int r = 0; r < 2; ++r) {
             if (qxMail >= 0) {
-              xstage[qxMail][z - z0][r0 + r] = qxK == 0 ? o.x : (qxK == 1 ? o.y : (qxK == 2 ? o.z : o.w));
+              xstage[qxMail][z - z0][r0 + r] = qxK == 0 ? o[r].x : (qxK == 1 ? o[r].y : (qxK == 2 ? o[r].z : o[r].w));
             } else if (qx[r]) {
               /* The halo cell shares its 32-byte sector with row padding only (LocalDomain layout), so the whole
-                 sector is written: a 4-byte store would make the receiver's memory system read-modify-write the
-                 sector (ECC), which measured as +160 MB of DRAM reads per 512^3 iteration. */
-              const float v = qxK == 0 ? o.x : (qxK == 1 ? o.y : (qxK == 2 ? o.z : o.w));
+                 sector is written: a 4-byte store would make the receiver's memory system read-modify-write it. */
+              const float v = qxK == 0 ? o[r].x : (qxK == 1 ? o[r].y : (qxK == 2 ? o[r].z : o[r].w));
               if (qxWide) {
                 float4 *q = reinterpret_cast<float4 *>(qx[r] + (long long)z * qxStride);
                 const float4 vv = make_float4(v, v, v, v);
@@ -548,9 +581,7 @@ __global__ void __launch_bounds__(kTmaThreads, MINB) jacobi7_tma_kernel(const __
                 qx[r][(long long)z * qxStride] = v;
               }
             }
-            const int y = y0 + r;
-            if (yzFaces && (y == 0 || y == P.sy - 1 || z == 0 || z == P.sz - 1 || (yzFaces & 3u)) && y < P.sy && x0 < P.sx)
-              push_cells(P, yzFaces, x0, y, z, o);
+            if (rowPush[r] || (zPush && mode[r] && (z == 0 || z == P.sz - 1))) push_cells(P, yzFaces, x0, y0 + r, z, o[r]);
           }
         }
       }
@@ -558,8 +589,15 @@ __global__ void __launch_bounds__(kTmaThreads, MINB) jacobi7_tma_kernel(const __
       cm2[1] = cm1[1];
       cm1[0] = c0;
       cm1[1] = c1;
-      part[0] = pn[0];
-      part[1] = pn[1];
+      /* ((px + mx) + py) + my, the first four terms of the reference's sum, for the plane just read */
+      part[0].x = ((c0.y + w0) + c1.x) + south.x;
+      part[0].y = ((c0.z + c0.x) + c1.y) + south.y;
+      part[0].z = ((c0.w + c0.y) + c1.z) + south.z;
+      part[0].w = ((e0 + c0.z) + c1.w) + south.w;
+      part[1].x = ((c1.y + w1) + north.x) + c0.x;
+      part[1].y = ((c1.z + c1.x) + north.y) + c0.y;
+      part[1].z = ((c1.w + c1.y) + north.z) + c0.z;
+      part[1].w = ((e1 + c1.z) + north.w) + c0.w;
     }
   }
 
@@ -576,7 +614,9 @@ __global__ void __launch_bounds__(kTmaThreads, MINB) jacobi7_tma_kernel(const __
         if (ybase + r < P.sy) P.mbox[f][(long long)(z0 + zl) * P.sy + ybase + r] = xstage[f][zl][r];
       }
     }
-    if (!(P.debugSkip & 1u)) {
+    /* only tiles that stored into ANOTHER GPU take part in the completion count (same-GPU neighbours are ordered by
+       the stream, or are this very kernel when an axis wraps onto the subdomain itself) */
+    if ((t.faces & P.flagMask) && !(P.debugSkip & 1u)) {
       __syncthreads();
       signal_neighbours(P);
     }
@@ -633,7 +673,8 @@ struct Jacobi3D::Impl {
   unsigned *err = nullptr;
   bool fusedOk = true;
   bool useTma = true;
-  int minBlocks = 3; // resident CTAs per SM the TMA kernel is compiled for
+  int minBlocks = 3; // resident CTAs per SM the TMA kernel is compiled for (when forced through the environment)
+  bool minBlocksForced = false;
   int rows = kTmaRows; // tile rows of the selected kernel variant
 };
 
@@ -642,7 +683,7 @@ namespace {
 /* tiles covering region [lo,hi) (compute coordinates) of a subdomain of size sz; faceMask selects which subdomain
    faces push (0 for non-fused launches). Boundary tiles are emitted first. */
 std::vector<Tile> make_tiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int rows, int tileZ, unsigned faceMask, unsigned *nBoundary,
-                             bool boundaryFirst = false) {
+                             bool boundaryFirst = false, unsigned countMask = 0) {
   std::vector<Tile> boundary, inner;
   unsigned nb = 0;
   if (hi.x <= lo.x || hi.y <= lo.y || hi.z <= lo.z) {
@@ -661,7 +702,7 @@ std::vector<Tile> make_tiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int
         if (tz * tileZ <= sz.z - 1 && sz.z - 1 < (tz + 1) * tileZ) f |= 1u << ZP;
         f &= faceMask;
         const Tile t{(unsigned short)tx, (unsigned short)ty, (unsigned short)tz, (unsigned short)f};
-        if (f) ++nb;
+        if (f & countMask) ++nb; // tiles that store into another GPU and therefore take part in the completion count
         /* Natural (z, y, x) order keeps tiles that share halo rows / planes / margins resident together, so those
            re-reads hit L2. Scheduling the pushing tiles first costs that locality (measured on B200: +160 MB of DRAM
            reads and +50 us per 512^3 iteration) and buys nothing while all GPUs run in step. */
@@ -755,7 +796,10 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
   impl_.reset(new Impl);
   impl_->useTma = opt_.useTma;
   impl_->rows = opt_.useTma ? kTmaRows : kRows;
-  if (const char *e = std::getenv("STENCIL_JACOBI_MINB")) impl_->minBlocks = std::atoi(e) == 2 ? 2 : 3;
+  if (const char *e = std::getenv("STENCIL_JACOBI_MINB")) {
+    impl_->minBlocks = std::atoi(e) == 2 ? 2 : 3;
+    impl_->minBlocksForced = true;
+  }
   CUDA_RUNTIME(cudaHostAlloc(&impl_->err, sizeof(unsigned), cudaHostAllocMapped | cudaHostAllocPortable));
   *impl_->err = 0;
 
@@ -808,7 +852,7 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
     }
 
     const Dim3 sz = ld.size(), org = ld.origin(), pitch = ld.pitch(h_.id());
-    unsigned faceMask = 0;
+    unsigned faceMask = 0, flagMask = 0;
     NeighborInfo nbs[6];
     std::set<int> deps;
     d.finalWait.n = 0;
@@ -817,6 +861,7 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
         nbs[f] = dd_->neighbor(di, kFaceDir[f], h_.id());
         if (!nbs[f].exists) continue;
         faceMask |= 1u << f;
+        if (!(nbs[f].sameRank && nbs[f].sameDevice)) flagMask |= 1u << f;
         if (nbs[f].sameRank && nbs[f].sameDevice && nbs[f].dom != int(di)) deps.insert(nbs[f].dom);
       }
     d.sameDevDeps.assign(deps.begin(), deps.end());
@@ -835,7 +880,7 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
     }
 
     const int rows = impl_->rows;
-    const std::vector<Tile> all = make_tiles(Dim3(0, 0, 0), sz, sz, rows, opt_.tileZ, faceMask, &d.nBoundary, opt_.boundaryFirst);
+    const std::vector<Tile> all = make_tiles(Dim3(0, 0, 0), sz, sz, rows, opt_.tileZ, faceMask, &d.nBoundary, opt_.boundaryFirst, flagMask);
     d.tilesAll = upload(all);
     d.nAll = unsigned(all.size());
     d.interior = interiors[di];
@@ -913,6 +958,7 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
         }
         const bool viaFlag = !(n.sameRank && n.sameDevice);
         if (viaFlag) {
+          P.flagMask |= 1u << f;
           /* I raise the slot "from direction -dir" in the neighbour; the neighbour raises slot "from dir" in me */
           P.nbFlag[f] = n.control + kFusedFlagBase + DirectionMap<int>::slot(kFaceDir[f] * -1);
           P.myFlag[f] = ld.arrive_flags() + kFusedFlagBase + DirectionMap<int>::slot(kFaceDir[f]);
@@ -960,8 +1006,11 @@ void Jacobi3D::step() {
     P.hiz = int(reg.hi.z - org.z);
     P.epoch = impl_->iter;
     if (impl_->useTma) {
-      auto *k = fused ? (impl_->minBlocks == 3 ? &jacobi7_tma_kernel<true, 3> : &jacobi7_tma_kernel<true, 2>)
-                      : (impl_->minBlocks == 3 ? &jacobi7_tma_kernel<false, 3> : &jacobi7_tma_kernel<false, 2>);
+      /* the fused variant needs ~100 registers: at 3 CTAs/SM (80 registers) it spills inside the plane loop, and with
+         the shared-memory-heavy carve-out those spills miss L1 (measured 4x slower); the plain variant fits in 80 */
+      const int mb = impl_->minBlocksForced ? impl_->minBlocks : (fused ? 2 : 3);
+      auto *k = fused ? (mb == 3 ? &jacobi7_tma_kernel<true, 3> : &jacobi7_tma_kernel<true, 2>)
+                      : (mb == 3 ? &jacobi7_tma_kernel<false, 3> : &jacobi7_tma_kernel<false, 2>);
       (*k)<<<n, kTmaThreads, kTmaSmemBytes, d.stream>>>(d.tmap[ld.parity()], P);
     } else if (fused) {
       jacobi7_kernel<true><<<n, kThreads, 0, d.stream>>>(P);
