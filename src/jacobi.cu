@@ -509,11 +509,14 @@ __global__ void __launch_bounds__(kTmaThreads, MINB) jacobi7_tma_kernel(const __
     }
     const bool zPush = FUSED && (yzFaces & ((1u << ZM) | (1u << ZP)));
     const long long planeStride = P.pitchXY;
-    float4 cm2[2], cm1[2], part[2];
-    cm2[0] = cm2[1] = cm1[0] = cm1[1] = part[0] = part[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+    /* Register plan without copies: the centre of plane i is needed again two planes later (as "below"), so two
+       register sets alternate (even / odd planes) and the loop is unrolled by two; the in-plane partial sum is
+       overwritten in place once the output that needs it has been formed. */
+    float4 cmA[2], cmB[2], part[2];
+    cmA[0] = cmA[1] = cmB[0] = cmB[1] = part[0] = part[1] = make_float4(0.f, 0.f, 0.f, 0.f);
     int s = 0;
     unsigned phase = 0;
-    for (int i = 0; i < nplanes; ++i) {
+    auto plane = [&](const int i, float4 (&below)[2]) { // `below` holds plane i-2 on entry and plane i on exit
       mbar_wait(&full[s], phase);
       const float *pl = reinterpret_cast<const float *>(smem + s * kTmaStageBytes);
       /* smem row j holds compute row ty*rows + j - 1; smem column 4 + k holds compute x = tx*128 + k */
@@ -543,14 +546,14 @@ __global__ void __launch_bounds__(kTmaThreads, MINB) jacobi7_tma_kernel(const __
       if (i >= 2) {
         const int z = z0 + i - 2; // output plane: above = centre of this plane, below = centre two planes back
         float4 o[2];
-        o[0].x = div6((part[0].x + c0.x) + cm2[0].x);
-        o[0].y = div6((part[0].y + c0.y) + cm2[0].y);
-        o[0].z = div6((part[0].z + c0.z) + cm2[0].z);
-        o[0].w = div6((part[0].w + c0.w) + cm2[0].w);
-        o[1].x = div6((part[1].x + c1.x) + cm2[1].x);
-        o[1].y = div6((part[1].y + c1.y) + cm2[1].y);
-        o[1].z = div6((part[1].z + c1.z) + cm2[1].z);
-        o[1].w = div6((part[1].w + c1.w) + cm2[1].w);
+        o[0].x = div6((part[0].x + c0.x) + below[0].x);
+        o[0].y = div6((part[0].y + c0.y) + below[0].y);
+        o[0].z = div6((part[0].z + c0.z) + below[0].z);
+        o[0].w = div6((part[0].w + c0.w) + below[0].w);
+        o[1].x = div6((part[1].x + c1.x) + below[1].x);
+        o[1].y = div6((part[1].y + c1.y) + below[1].y);
+        o[1].z = div6((part[1].z + c1.z) + below[1].z);
+        o[1].w = div6((part[1].w + c1.w) + below[1].w);
         if (nearSphere) {
           o[0] = apply_spheres(P, x0, y0, z, o[0]);
           o[1] = apply_spheres(P, x0, y0 + 1, z, o[1]);
@@ -585,10 +588,8 @@ __global__ void __launch_bounds__(kTmaThreads, MINB) jacobi7_tma_kernel(const __
           }
         }
       }
-      cm2[0] = cm1[0];
-      cm2[1] = cm1[1];
-      cm1[0] = c0;
-      cm1[1] = c1;
+      below[0] = c0;
+      below[1] = c1;
       /* ((px + mx) + py) + my, the first four terms of the reference's sum, for the plane just read */
       part[0].x = ((c0.y + w0) + c1.x) + south.x;
       part[0].y = ((c0.z + c0.x) + c1.y) + south.y;
@@ -598,7 +599,13 @@ __global__ void __launch_bounds__(kTmaThreads, MINB) jacobi7_tma_kernel(const __
       part[1].y = ((c1.z + c1.x) + north.y) + c0.y;
       part[1].z = ((c1.w + c1.y) + north.z) + c0.z;
       part[1].w = ((e1 + c1.z) + north.w) + c0.w;
+    };
+    int i = 0;
+    for (; i + 1 < nplanes; i += 2) {
+      plane(i, cmA);
+      plane(i + 1, cmB);
     }
+    if (i < nplanes) plane(i, cmA);
   }
 
   if (FUSED && t.faces) {
@@ -1008,7 +1015,7 @@ void Jacobi3D::step() {
     if (impl_->useTma) {
       /* the fused variant needs ~100 registers: at 3 CTAs/SM (80 registers) it spills inside the plane loop, and with
          the shared-memory-heavy carve-out those spills miss L1 (measured 4x slower); the plain variant fits in 80 */
-      const int mb = impl_->minBlocksForced ? impl_->minBlocks : (fused ? 2 : 3);
+      const int mb = impl_->minBlocksForced ? impl_->minBlocks : 2;
       auto *k = fused ? (mb == 3 ? &jacobi7_tma_kernel<true, 3> : &jacobi7_tma_kernel<true, 2>)
                       : (mb == 3 ? &jacobi7_tma_kernel<false, 3> : &jacobi7_tma_kernel<false, 2>);
       (*k)<<<n, kTmaThreads, kTmaSmemBytes, d.stream>>>(d.tmap[ld.parity()], P);
