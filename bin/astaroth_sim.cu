@@ -15,7 +15,7 @@ int main(int argc, char **argv) {
   size_t x = 512, y = 512, z = 512;
   int iters = 5, fields = 1;
   bool remote = false, cudaAware = false, colocated = false, peer = false, kernel = false, direct = false, trivial = false;
-  bool fp64 = false, star = false, noOverlap = false, weak = false;
+  bool fp64 = false, star = false, noOverlap = false, forceOverlap = false, weak = false;
   std::string file;
   argparse::Parser p("radius-3 multi-field stencil (Astaroth stand-in)");
   p.add_option(x, "--x");
@@ -34,6 +34,7 @@ int main(int argc, char **argv) {
   p.add_flag(fp64, "--double");
   p.add_flag(star, "--star");
   p.add_flag(noOverlap, "--no-overlap");
+  p.add_flag(forceOverlap, "--overlap")->help("keep the interior/exterior schedule even where the engine would drop it");
   p.add_flag(weak, "--weak");
   if (!p.parse(argc, argv)) {
     std::cerr << p.help() << "\n";
@@ -68,6 +69,7 @@ int main(int argc, char **argv) {
     opt.fp64 = fp64;
     opt.stencil = star ? stencil::AstarothSim::Stencil::Star19 : stencil::AstarothSim::Stencil::Average7;
     opt.overlap = !noOverlap;
+    opt.autoSchedule = !forceOverlap;
     opt.planFile = true;
     stencil::AstarothSim sim(x, y, z, opt);
     sim.run(1); // warm up

@@ -24,7 +24,10 @@ public:
     Stencil stencil = Stencil::Average7;
     int fields = 1;
     bool fp64 = false;
-    bool overlap = true;
+    bool overlap = true;       // interior kernel, exchange(), exterior slabs (the reference's schedule)
+    bool autoSchedule = true;  // let the engine drop the overlap when the TMA kernel is used: thin exterior slabs cannot
+                               // fill its tiles, and exchange() + one whole-region launch measured 1.8x faster on B200
+    bool useTma = true; // Star19: TMA + mbarrier pipelined kernel for regions wide enough to fill its tiles
     std::vector<int> gpus;
     double period = 10;
     double dt = 0.01;

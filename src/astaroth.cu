@@ -12,6 +12,8 @@
 #include <cstring>
 #include <limits>
 
+#include "stencil/detail/tma.cuh"
+
 namespace stencil {
 
 namespace {
@@ -153,6 +155,181 @@ template <typename T, bool STAR> __global__ void __launch_bounds__(kLanes *kRows
   }
 }
 
+/* ---------------- TMA-pipelined radius-3 star kernel ----------------
+   Same structure as the Jacobi kernel (src/jacobi.cu): a tile is 32 lanes x 16 rows, a lane owns one 16-byte vector
+   of cells (N = 4 fp32 / 2 fp64), thread 0 streams (32N + 8) x (16 + 6) input planes of ONE field into a 6-stage
+   shared-memory ring with cp.async.bulk.tensor.3d, eight warps (two rows each) consume. The z direction never goes
+   back to memory: each arriving plane adds its "above" contribution to the three pending outputs and its centre
+   stays in registers for the three "below" contributions that follow, so a plane is read from shared memory once. */
+constexpr int kTRows = 16, kTMargin = 4, kTStages = 6, kTLag = 2, kTThreads = 256;
+
+template <typename T> struct TmaGeom {
+  static constexpr int N = Vec<T>::n;
+  static constexpr int tileX = 32 * N;
+  static constexpr int boxX = tileX + 2 * kTMargin;
+  static constexpr int boxY = kTRows + 2 * kR;
+  static constexpr int planeBytes = boxX * boxY * int(sizeof(T));
+  static constexpr int stageBytes = (planeBytes + 127) / 128 * 128;
+  static constexpr int smemBytes = kTStages * stageBytes + 2 * kTStages * 8;
+};
+
+template <typename T> struct TmaParams {
+  T *dst[kMaxFields];      // compute cell (0,0,0) of next, per field
+  const CUtensorMap *maps; // device array: one map per field over the CURRENT curr buffers
+  long long pitchX, pitchXY;
+  int lox, loy, loz, hix, hiy, hiz; // cells to update, compute coordinates, half open
+  int tileZ, tilesX, tilesY, nChunks;
+  int tx0, ty0;            // first tile column / row of the region (tile grid is anchored at compute cell 0)
+  int x0pad;               // index of compute x = 0 inside a padded row (TMA coordinates start at the row start)
+  T dt;
+};
+
+template <typename T> __global__ void __launch_bounds__(kTThreads, 2) astaroth_tma_kernel(const __grid_constant__ TmaParams<T> P) {
+  typedef TmaGeom<T> G;
+  typedef typename Vec<T>::type V;
+  constexpr int N = G::N;
+  extern __shared__ __align__(128) unsigned char smem[];
+  unsigned long long *full = reinterpret_cast<unsigned long long *>(smem + kTStages * G::stageBytes);
+  unsigned long long *empty = full + kTStages;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, field = blockIdx.y;
+  int tile = blockIdx.x;
+  const int tx = P.tx0 + tile % P.tilesX;
+  tile /= P.tilesX;
+  const int ty = P.ty0 + tile % P.tilesY, chunk = tile / P.tilesY;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kTStages; ++s) {
+      tma::mbar_init(&full[s], 1);
+      tma::mbar_init(&empty[s], kTThreads / 32);
+    }
+    tma::mbar_fence_init();
+  }
+  __syncthreads();
+
+  const int z0 = P.loz + chunk * P.tileZ, z1 = min(z0 + P.tileZ, P.hiz);
+  const int nplanes = z1 - z0 + 2 * kR; // input planes z0-3 .. z1+2
+  const CUtensorMap *map = P.maps + field;
+  const int cx = P.x0pad + tx * G::tileX - kTMargin; // raw x of smem column 0
+  const int cy = ty * kTRows;                        // raw row of compute row ty*16 - 3 (raw = compute + 3)
+  auto issue = [&](int j) {                          // input plane j = compute plane z0 - 3 + j = raw plane z0 + j
+    const int sj = j % kTStages;
+    if (j >= kTStages) tma::mbar_wait(&empty[sj], ((j / kTStages) - 1) & 1);
+    tma::mbar_arrive_expect_tx(&full[sj], G::planeBytes);
+    tma::load_3d(smem + sj * G::stageBytes, map, cx, cy, z0 + j, &full[sj]);
+  };
+  if (threadIdx.x == 0)
+    for (int j = 0; j < kTStages - kTLag && j < nplanes; ++j) issue(j);
+
+  const int r0 = 2 * warp;
+  const int x0 = tx * G::tileX + lane * N, y0 = ty * kTRows + r0;
+  /* where the two rows of this lane go, decided once */
+  T *dp[2];
+  int mode[2];
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    const int y = y0 + r;
+    const bool in = y >= P.loy && y < P.hiy && x0 < P.hix && x0 + N > P.lox;
+    mode[r] = !in ? 0 : ((x0 >= P.lox && x0 + N <= P.hix) ? 1 : 2);
+    dp[r] = P.dst[field] + (long long)z0 * P.pitchXY + (long long)y * P.pitchX + x0;
+  }
+  const T c1 = T(1.5), c2 = T(-0.15), c3 = T(1.0 / 90.0), c0x3 = T(3) * T(-49.0 / 18.0);
+  /* pending sums for the planes 1, 2, 3 behind the newest one, and the centres of those planes */
+  T a1[2][N], a2[2][N], a3[2][N], h1[2][N], h2[2][N], h3[2][N];
+#pragma unroll
+  for (int r = 0; r < 2; ++r)
+#pragma unroll
+    for (int i = 0; i < N; ++i) a1[r][i] = a2[r][i] = a3[r][i] = h1[r][i] = h2[r][i] = h3[r][i] = T(0);
+
+  int s = 0;
+  unsigned phase = 0;
+  for (int j = 0; j < nplanes; ++j) {
+    tma::mbar_wait(&full[s], phase);
+    const T *pl = reinterpret_cast<const T *>(smem + s * G::stageBytes);
+    /* smem row q holds compute row ty*16 + q - 3; smem column kTMargin + k holds compute x = tx*tileX + k */
+    const T *base = pl + (r0 + kR) * G::boxX + kTMargin + lane * N;
+    T col[8][N]; // rows r0-3 .. r0+4 at my x: col[3], col[4] are my two centre rows
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      const V v = *reinterpret_cast<const V *>(base + (q - 3) * G::boxX);
+      memcpy(col[q], &v, sizeof(V));
+    }
+    const bool inPlane = j >= kR && j < nplanes - kR; // this plane is an output plane: it needs its in-plane sum
+    T an[2][N];
+    if (inPlane) {
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        /* x window of row r: cells x0 - kTMargin .. x0 + N + kTMargin - 1 */
+        T win[N + 2 * kTMargin];
+        const T *row = base + r * G::boxX;
+#pragma unroll
+        for (int v = 0; v < (N + 2 * kTMargin) / N; ++v) {
+          if (v * N == kTMargin) {
+#pragma unroll
+            for (int i = 0; i < N; ++i) win[kTMargin + i] = col[3 + r][i];
+          } else {
+            const V t = *reinterpret_cast<const V *>(row + v * N - kTMargin);
+            memcpy(win + v * N, &t, sizeof(V));
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+          const int c = kTMargin + i;
+          T lap = c0x3 * win[c];
+          lap += c1 * (((win[c - 1] + win[c + 1]) + col[3 + r - 1][i]) + col[3 + r + 1][i]);
+          lap += c2 * (((win[c - 2] + win[c + 2]) + col[3 + r - 2][i]) + col[3 + r + 2][i]);
+          lap += c3 * (((win[c - 3] + win[c + 3]) + col[3 + r - 3][i]) + col[3 + r + 3][i]);
+          /* contributions of the three planes below, whose centres are still in registers */
+          lap += c1 * h1[r][i];
+          lap += c2 * h2[r][i];
+          lap += c3 * h3[r][i];
+          an[r][i] = lap;
+        }
+      }
+    } else {
+#pragma unroll
+      for (int r = 0; r < 2; ++r)
+#pragma unroll
+        for (int i = 0; i < N; ++i) an[r][i] = T(0);
+    }
+    /* the slot can be refilled: everything needed from it is in registers */
+    __syncwarp();
+    if (lane == 0) tma::mbar_arrive(&empty[s]);
+    if (threadIdx.x == 0 && j + kTStages - kTLag < nplanes) issue(j + kTStages - kTLag);
+    if (++s == kTStages) {
+      s = 0;
+      phase ^= 1u;
+    }
+    /* this plane is "above" the three pending ones; the oldest of them is now complete */
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      T out[N];
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+        const T c = col[3 + r][i];
+        out[i] = h3[r][i] + P.dt * (a3[r][i] + c3 * c);
+        a3[r][i] = a2[r][i] + c2 * c;
+        a2[r][i] = a1[r][i] + c1 * c;
+        a1[r][i] = an[r][i];
+        h3[r][i] = h2[r][i];
+        h2[r][i] = h1[r][i];
+        h1[r][i] = c;
+      }
+      if (j >= 2 * kR) { // output plane z0 + j - 6
+        if (mode[r] == 1) {
+          V v;
+          memcpy(&v, out, sizeof(V));
+          *reinterpret_cast<V *>(dp[r]) = v;
+        } else if (mode[r] == 2) {
+#pragma unroll
+          for (int i = 0; i < N; ++i)
+            if (x0 + i >= P.lox && x0 + i < P.hix) dp[r][i] = out[i];
+        }
+        dp[r] += P.pitchXY;
+      }
+    }
+  }
+}
+
 template <typename T>
 __global__ void astaroth_init_kernel(T *logical0, long long pitchX, long long pitchXY, Dim3 raw, Dim3 haloOrigin, double period) {
   const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y;
@@ -172,6 +349,7 @@ __global__ void astaroth_init_kernel(T *logical0, long long pitchX, long long pi
 
 struct AstarothSim::Impl {
   std::vector<RcStream> streams;
+  std::vector<CUtensorMap *> maps[2]; // per subdomain: device array of one tensor map per field, per curr parity
   std::vector<Rect3> interior;
   std::vector<std::vector<Rect3>> exterior;
   double exchangeSeconds = 0;
@@ -191,11 +369,41 @@ AstarothSim::AstarothSim(size_t x, size_t y, size_t z, const Options &opt) : opt
   for (LocalDomain &ld : dd_->domains()) impl_->streams.emplace_back(ld.gpu());
   impl_->interior = dd_->get_interior();
   impl_->exterior = dd_->get_exterior();
+  if (std::getenv("STENCIL_ASTAROTH_NO_TMA")) opt_.useTma = false;
+  if (opt_.autoSchedule && opt_.useTma && opt_.stencil == Stencil::Star19) opt_.overlap = false;
+  if (opt_.useTma && opt_.stencil == Stencil::Star19) {
+    /* one tensor map per field and buffer: the padded buffer as (row pitch, rows, planes) */
+    for (LocalDomain &ld : dd_->domains()) {
+      DevGuard g(ld.gpu());
+      const Dim3 raw = ld.raw_size();
+      for (int parity = 0; parity < 2; ++parity) {
+        std::vector<CUtensorMap> host;
+        for (int f = 0; f < opt_.fields; ++f) {
+          char *buf = static_cast<char *>(ld.slab()) + ld.buffer_start_offset(size_t(f), parity);
+          const Dim3 pitch = ld.pitch(size_t(f));
+          host.push_back(opt_.fp64 ? tma::make_plane_map(buf, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, pitch.x, raw.y, raw.z, TmaGeom<double>::boxX, TmaGeom<double>::boxY)
+                                   : tma::make_plane_map(buf, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, pitch.x, raw.y, raw.z, TmaGeom<float>::boxX, TmaGeom<float>::boxY));
+        }
+        CUtensorMap *d = nullptr;
+        CUDA_RUNTIME(cudaMalloc(&d, host.size() * sizeof(CUtensorMap)));
+        CUDA_RUNTIME(cudaMemcpy(d, host.data(), host.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice));
+        impl_->maps[parity].push_back(d);
+      }
+      CUDA_RUNTIME(cudaFuncSetAttribute(astaroth_tma_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, TmaGeom<double>::smemBytes));
+      CUDA_RUNTIME(cudaFuncSetAttribute(astaroth_tma_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, TmaGeom<float>::smemBytes));
+    }
+  }
   init();
 }
 
 AstarothSim::~AstarothSim() {
   if (dd_) sync();
+  if (impl_ && dd_)
+    for (int parity = 0; parity < 2; ++parity)
+      for (size_t di = 0; di < impl_->maps[parity].size(); ++di) {
+        DevGuard g(dd_->domains()[di].gpu());
+        cudaFree(impl_->maps[parity][di]);
+      }
   impl_.reset();
   dd_.reset();
 }
@@ -253,11 +461,52 @@ template <typename T> static void launch_region(AstarothSim::Stencil st, LocalDo
   CUDA_RUNTIME(cudaGetLastError());
 }
 
+/* the TMA kernel on a region that is wide enough to fill its tiles */
+template <typename T> static void launch_region_tma(LocalDomain &ld, int fields, const CUtensorMap *maps, const Rect3 &reg, int tileZ, T dt, cudaStream_t stream) {
+  typedef TmaGeom<T> G;
+  TmaParams<T> P;
+  std::memset(&P, 0, sizeof(P));
+  const Dim3 pitch = ld.pitch(0), org = ld.origin();
+  const long long interiorOff = (long long)kR * (pitch.x * pitch.y + pitch.x + 1);
+  for (int f = 0; f < fields; ++f) P.dst[f] = static_cast<T *>(ld.next_data(size_t(f))) + interiorOff;
+  P.maps = maps;
+  P.pitchX = pitch.x;
+  P.pitchXY = pitch.x * pitch.y;
+  P.lox = int(reg.lo.x - org.x);
+  P.loy = int(reg.lo.y - org.y);
+  P.loz = int(reg.lo.z - org.z);
+  P.hix = int(reg.hi.x - org.x);
+  P.hiy = int(reg.hi.y - org.y);
+  P.hiz = int(reg.hi.z - org.z);
+  P.tileZ = tileZ;
+  P.tx0 = P.lox / G::tileX;
+  P.ty0 = P.loy / kTRows;
+  P.tilesX = (P.hix - 1) / G::tileX - P.tx0 + 1;
+  P.tilesY = (P.hiy - 1) / kTRows - P.ty0 + 1;
+  P.nChunks = (P.hiz - P.loz + tileZ - 1) / tileZ;
+  P.x0pad = int(ld.lead_elems(0)) + kR;
+  P.dt = dt;
+  const dim3 grid(unsigned(P.tilesX * P.tilesY * P.nChunks), unsigned(fields), 1);
+  astaroth_tma_kernel<T><<<grid, kTThreads, G::smemBytes, stream>>>(P);
+  CUDA_RUNTIME(cudaGetLastError());
+}
+
 void AstarothSim::step() {
   std::vector<LocalDomain> &doms = dd_->domains();
   auto launch = [&](size_t di, const Rect3 &reg) {
     if (reg.empty()) return;
     DevGuard g(doms[di].gpu());
+    const Dim3 ext = reg.extent();
+    const int tileX = opt_.fp64 ? TmaGeom<double>::tileX : TmaGeom<float>::tileX;
+    if (opt_.useTma && opt_.stencil == Stencil::Star19 && ext.x >= tileX / 2 && ext.y >= kTRows / 2) {
+      const CUtensorMap *maps = impl_->maps[doms[di].parity()][di];
+      if (opt_.fp64)
+        launch_region_tma<double>(doms[di], opt_.fields, maps, reg, opt_.tileZ, opt_.dt, impl_->streams[di]);
+      else
+        launch_region_tma<float>(doms[di], opt_.fields, maps, reg, opt_.tileZ, float(opt_.dt), impl_->streams[di]);
+      ++launches_;
+      return;
+    }
     if (opt_.fp64)
       launch_region<double>(opt_.stencil, doms[di], opt_.fields, reg, opt_.tileZ, opt_.dt, impl_->streams[di]);
     else

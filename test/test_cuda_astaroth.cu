@@ -15,6 +15,7 @@ double max_abs_err(const Dim3 &size, stencil::AstarothSim::Stencil st, bool fp64
   opt.fields = fields;
   opt.gpus = gpus;
   opt.overlap = overlap;
+  opt.autoSchedule = false; // test exactly the schedule asked for
   opt.tileZ = 8;
   opt.methods = methods;
   stencil::AstarothSim sim(size_t(size.x), size_t(size.y), size_t(size.z), opt);
@@ -58,6 +59,12 @@ TEST_CASE("astaroth: 19-point radius-3 stencil, fp64 and fp32, many fields and s
   REQUIRE(max_abs_err(Dim3(45, 27, 23), S::Star19, true, 3, {0, 0, 0, 0}, false, 3) < 1e-13);
   REQUIRE(max_abs_err(Dim3(48, 26, 22), S::Star19, false, 4, {0, 0}, true, 3) < 5e-6);
   REQUIRE(max_abs_err(Dim3(44, 26, 22), S::Star19, true, 2, {0, 0}, true, 3, MethodFlags::CudaMpi) < 1e-13);
+  /* wide enough for the TMA kernel in both precisions (tile = 128 fp32 / 64 fp64 cells), partial tiles in x, y and z */
+  REQUIRE(max_abs_err(Dim3(150, 37, 21), S::Star19, false, 2, {0}, true, 3) < 5e-6);
+  REQUIRE(max_abs_err(Dim3(300, 40, 19), S::Star19, false, 3, {0, 0}, true, 3) < 5e-6);
+  REQUIRE(max_abs_err(Dim3(150, 37, 21), S::Star19, true, 2, {0, 0}, true, 3) < 1e-13);
+  REQUIRE(max_abs_err(Dim3(150, 37, 21), S::Star19, true, 2, {0, 0}, false, 3) < 1e-13);
+  REQUIRE(max_abs_err(Dim3(260, 33, 18), S::Star19, false, 2, {0}, false, 3) < 5e-6);
 }
 
 TEST_CASE("astaroth: all visible GPUs", "[cuda][astaroth][multigpu]") {
