@@ -6,6 +6,7 @@
    plane; x and y neighbours are 16-byte loads that hit L1 (rows are 128-byte aligned). All fields go in one launch
    (blockIdx.z = field x z-chunk). This round the exchange is the library's direct-push exchange() overlapped with the
    interior kernel; folding the push into the exterior kernel as the Jacobi engine does is the next step. */
+#include "stencil/nvtx.hpp"
 #include "stencil/astaroth.hpp"
 
 #include <cmath>
@@ -492,6 +493,7 @@ template <typename T> static void launch_region_tma(LocalDomain &ld, int fields,
 }
 
 void AstarothSim::step() {
+  STENCIL_RANGE("AstarothSim::step");
   std::vector<LocalDomain> &doms = dd_->domains();
   auto launch = [&](size_t di, const Rect3 &reg) {
     if (reg.empty()) return;

@@ -92,8 +92,10 @@ __device__ __forceinline__ void copy_rows(const CopySeg &s, const char *__restri
       V *b = reinterpret_cast<V *>(dp + (long long)r * s.dstPitchY);
       V v[8];
 #pragma unroll
-      for (int u = 0; u < 8; ++u)
+      for (int u = 0; u < 8; ++u) { // every v[u] is defined on every path: an undefined one stays live across the whole kernel
+        v[u] = V();
         if (u < int(upr)) v[u] = ld_stream(a + u);
+      }
 #pragma unroll
       for (int u = 0; u < 8; ++u)
         if (u < int(upr)) b[u] = v[u];
@@ -109,7 +111,7 @@ __device__ __forceinline__ void copy_rows(const CopySeg &s, const char *__restri
       const bool two = r2 < nrows;
       for (unsigned u = lane; u < upr; u += 64) {
         const unsigned u2 = u + 32;
-        V v00 = ld_stream(a0 + u), v01, v10, v11;
+        V v00 = ld_stream(a0 + u), v01 = V(), v10 = V(), v11 = V();
         if (u2 < upr) v01 = ld_stream(a0 + u2);
         if (two) {
           v10 = ld_stream(a1 + u);
@@ -144,8 +146,10 @@ __device__ __forceinline__ void copy_planes(const CopySeg &s, const char *__rest
       V *b = reinterpret_cast<V *>(dp + (long long)zi * s.dstPitchZ + (long long)y * s.dstPitchY);
       V v[8];
 #pragma unroll
-      for (int u = 0; u < 8; ++u)
+      for (int u = 0; u < 8; ++u) { // every v[u] is defined on every path: an undefined one stays live across the whole kernel
+        v[u] = V();
         if (u < int(upr)) v[u] = ld_stream(a + u);
+      }
 #pragma unroll
       for (int u = 0; u < 8; ++u)
         if (u < int(upr)) b[u] = v[u];
@@ -191,7 +195,7 @@ __device__ __forceinline__ void gather_dense(const CopySeg &s, RowSrc rowSrc, ch
 }
 
 template <bool SIGNAL>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 4)
     box_copy_kernel(const CopySeg *__restrict__ segs, const CopyChunk *__restrict__ chunks, unsigned nchunks, int parity,
                     unsigned *done, SignalSet sig, unsigned epoch) {
   __shared__ CopySeg s;

@@ -26,6 +26,7 @@
    every neighbour's flag (st.release.sys). At the start of the next iteration only boundary tiles look at the
    flags (ld.acquire.sys): they are the only ones that read halo cells, and their neighbours' flags were raised
    well before the previous kernel ended, so in steady state nobody spins. */
+#include "stencil/nvtx.hpp"
 #include "stencil/jacobi.hpp"
 
 #include <algorithm>
@@ -995,6 +996,7 @@ void Jacobi3D::init() {
 }
 
 void Jacobi3D::step() {
+  STENCIL_RANGE("Jacobi3D::step");
   std::vector<LocalDomain> &doms = dd_->domains();
   const size_t nd = doms.size();
   ++impl_->iter;

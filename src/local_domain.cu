@@ -1,4 +1,5 @@
 /* LocalDomain storage and host transfers. Reference: src/local_domain.cu:1-169 (see header for the design). */
+#include "stencil/nvtx.hpp"
 #include "stencil/local_domain.cuh"
 
 #include <cstring>
@@ -131,6 +132,7 @@ void LocalDomain::compute_layout() {
 }
 
 void LocalDomain::realize() {
+  STENCIL_RANGE("LocalDomain::realize");
   if (slab_) return;
   DevGuard g(dev_);
   compute_layout();

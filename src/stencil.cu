@@ -13,6 +13,7 @@
 #include <tuple>
 
 #include "stencil/copy_plan.hpp"
+#include "stencil/nvtx.hpp"
 #include "stencil/packer.cuh"
 
 std::string method_string(MethodFlags m, const char *sep) {
@@ -313,6 +314,7 @@ public:
 
   /* ---------------- planning (realize) ---------------- */
   void prepare() {
+    STENCIL_RANGE("DistributedDomain::realize() prep transports");
     Placement *pl = dd_.placement_.get();
     const Dim3 grid = pl->dim();
     stencil::Comm &comm = *dd_.comm_;
@@ -555,6 +557,7 @@ public:
 
   /* ---------------- the per-iteration exchange ---------------- */
   void exchange() {
+    STENCIL_RANGE("DD::exchange()");
     ++epoch_;
     stencil::Comm &comm = *dd_.comm_;
     std::vector<LocalDomain> &doms = dd_.domains_;
@@ -567,6 +570,8 @@ public:
     }
 
     /* 1. longest paths first: staged sends (pack + D2H) */
+    {
+    STENCIL_RANGE("DD::exchange: remote send d2h");
     for (StagedSend &s : stagedSends_) {
       DevGuard g(doms[size_t(s.src)].gpu());
       s.packer->pack();
@@ -574,10 +579,12 @@ public:
       CUDA_RUNTIME(cudaEventRecord(s.staged, streams_[size_t(s.src)]));
       s.pending = true;
     }
+    }
     for (StagedRecv &r : stagedRecvs_) r.pending = true;
 
     /* 2. colocated sends: pack, copy into the receiver's buffer, record the shared event, notify */
     for (ColoSend &s : coloSends_) {
+      STENCIL_RANGE("DD::exchange: colo send");
       DevGuard g(doms[size_t(s.src)].gpu());
       cudaStream_t st = streams_[size_t(s.src)];
       if (s.awaitingAck) { // do not overwrite an image the receiver has not unpacked yet
@@ -595,6 +602,7 @@ public:
 
     /* 3. peer copies, phase A: pack + copy + record on the source streams */
     for (PeerCopy &pc : peerCopies_) {
+      STENCIL_RANGE("DD::exchange: peer copy send");
       DevGuard g(doms[size_t(pc.src)].gpu());
       cudaStream_t st = streams_[size_t(pc.src)];
       pc.packer->pack();
@@ -606,6 +614,7 @@ public:
     /* 4. direct pushes: wait for cross-process credits, store into the neighbours' halos, raise their flags */
     for (size_t di = 0; di < nd_; ++di) {
       if (push_[di].empty() && arriveSig_[di].n == 0) continue;
+      STENCIL_RANGE("DD::exchange: direct push");
       DevGuard g(doms[di].gpu());
       launch_wait_flags(readyWait_[di], epoch_, errWord_, timeoutNs_, streams_[di]);
       if (trace_) CUDA_RUNTIME(cudaEventRecord(trA_[di], streams_[di]));
@@ -631,6 +640,7 @@ public:
 
     /* 6. host progress loop for the host-mediated transports */
     size_t open = stagedSends_.size() + stagedRecvs_.size() + coloRecvs_.size();
+    STENCIL_RANGE("DD::exchange: poll");
     const double t0 = stencil::Comm::wtime();
     while (open) {
       for (StagedSend &s : stagedSends_) {
@@ -669,6 +679,7 @@ public:
     }
 
     /* 7. completion */
+    STENCIL_RANGE("DD::exchange: wait");
     for (size_t di = 0; di < nd_; ++di) {
       DevGuard g(doms[di].gpu());
       CUDA_RUNTIME(cudaStreamSynchronize(streams_[di]));
@@ -696,6 +707,7 @@ public:
 
   /* ---------------- plan dump + byte counters ---------------- */
   void summarize() {
+    STENCIL_RANGE("allreduce communication stats");
     std::vector<LocalDomain> &doms = dd_.domains_;
     Placement *pl = dd_.placement_.get();
     uint64_t staged = 0, colo = 0, peer = 0, kernel = 0, direct = 0;
@@ -839,18 +851,24 @@ void DistributedDomain::realize() {
   timeNodeGpus_ += comm_->allreduce_max(stencil::Comm::wtime() - t);
 
   t = stencil::Comm::wtime();
-  for (int src : gpus_)
-    for (int dst : nodeCuda) {
-      gpu_topo::enable_peer(src, dst);
-      gpu_topo::enable_peer(dst, src);
-    }
+  {
+    STENCIL_RANGE("peer_en");
+    for (int src : gpus_)
+      for (int dst : nodeCuda) {
+        gpu_topo::enable_peer(src, dst);
+        gpu_topo::enable_peer(dst, src);
+      }
+  }
   timePeerEn_ += comm_->allreduce_max(stencil::Comm::wtime() - t);
 
   t = stencil::Comm::wtime();
-  if (strategy_ == PlacementStrategy::NodeAware)
-    placement_.reset(new NodeAware(size_, *topo_, radius_, gpus_, bandwidthFn_));
-  else
-    placement_.reset(new Trivial(size_, *topo_, gpus_));
+  {
+    STENCIL_RANGE("placement");
+    if (strategy_ == PlacementStrategy::NodeAware)
+      placement_.reset(new NodeAware(size_, *topo_, radius_, gpus_, bandwidthFn_));
+    else
+      placement_.reset(new Trivial(size_, *topo_, gpus_));
+  }
   timePlacement_ += comm_->allreduce_max(stencil::Comm::wtime() - t);
 
   t = stencil::Comm::wtime();
@@ -871,6 +889,7 @@ void DistributedDomain::realize() {
   timeCreate_ += comm_->allreduce_max(stencil::Comm::wtime() - t);
 
   t = stencil::Comm::wtime();
+  STENCIL_RANGE("DistributedDomain::realize() plan messages");
   ex_.reset(new stencil::Exchanger(*this));
   ex_->prepare();
   ex_->summarize();
@@ -885,7 +904,10 @@ void DistributedDomain::swap() {
     comm_->barrier();
     t = stencil::Comm::wtime();
   }
-  for (LocalDomain &d : domains_) d.swap();
+  {
+    STENCIL_RANGE("swap");
+    for (LocalDomain &d : domains_) d.swap();
+  }
   if (exchangeStats_) timeSwap_ += comm_->allreduce_max(stencil::Comm::wtime() - t);
 }
 
@@ -949,6 +971,7 @@ std::vector<std::vector<Rect3>> DistributedDomain::get_exterior() const {
 }
 
 void DistributedDomain::write_paraview(const std::string &prefix, bool zeroNaNs) {
+  STENCIL_RANGE("write_paraview");
   for (size_t di = 0; di < domains_.size(); ++di) {
     const int64_t id = int64_t(rank_) * int64_t(domains_.size()) + int64_t(di);
     const std::string path = prefix + "_" + std::to_string(id) + ".txt";
