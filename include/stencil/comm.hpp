@@ -27,6 +27,8 @@ public:
   virtual int rank() const = 0;
   virtual int size() const = 0;
   virtual const char *name() const = 0;
+  /* true if send()/try_recv() accept DEVICE pointers (a CUDA-aware MPI underneath): enables MethodFlags::CudaAwareMpi */
+  virtual bool device_buffers() const { return false; }
 
   /* eager tagged send; returns once the payload is buffered or on the wire */
   virtual void send(int dst, int tag, const void *buf, size_t bytes) = 0;
@@ -53,6 +55,10 @@ public:
 std::unique_ptr<Comm> make_self_comm();
 /* TCP star; rank 0 listens on addr:port. Blocks until all `size` ranks joined. */
 std::unique_ptr<Comm> make_tcp_comm(int rank, int size, const std::string &addr, int port);
+
+/* MPI-backed communicator (src/mpi_comm.cpp); only in builds configured with -DUSE_MPI=ON, otherwise returns null.
+   Initialises MPI if nobody has; device_buffers() follows -DUSE_CUDA_AWARE_MPI=ON. */
+std::unique_ptr<Comm> make_mpi_comm();
 
 /* process-wide communicator. First use initialises from the environment:
    WORLD_SIZE>1 with RANK and MASTER_ADDR set -> TcpComm on STENCIL_PORT (default MASTER_PORT+17); else SelfComm. */

@@ -376,7 +376,12 @@ Comm &world() {
     const char *rk = std::getenv("RANK");
     const char *ma = std::getenv("MASTER_ADDR");
     const char *off = std::getenv("STENCIL_NO_ENV_COMM");
-    if (!off && ws && rk && ma && std::atoi(ws) > 1) {
+    /* under an MPI launcher (or when asked) and built with USE_MPI: MPI; else torchrun-style env: TCP; else alone */
+    const char *want = std::getenv("STENCIL_COMM");
+    const bool mpiLaunch = std::getenv("OMPI_COMM_WORLD_SIZE") || std::getenv("PMI_SIZE") || std::getenv("PMIX_RANK") || std::getenv("SLURM_PROCID");
+    if (!off && ((want && std::string(want) == "mpi") || (!want && mpiLaunch))) g_world = make_mpi_comm(); // null without USE_MPI
+    if (g_world) {
+    } else if (!off && ws && rk && ma && std::atoi(ws) > 1) {
       int port = 29517;
       if (const char *sp = std::getenv("STENCIL_PORT"))
         port = std::atoi(sp);

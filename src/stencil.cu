@@ -122,10 +122,13 @@ class Exchanger {
   struct StagedSend {
     int src, dstRank, tag;
     std::unique_ptr<DevicePacker> packer;
-    void *host = nullptr;
+    void *host = nullptr; // pinned staging buffer; unused when the communicator takes device pointers
     cudaEvent_t staged;
     bool pending = false;
   };
+  /* CudaAwareMpi (reference C29, tx_cuda.cuh:820-990): the packed device buffer itself is handed to the
+     communicator, no pinned host copy on either side. Needs Comm::device_buffers(). */
+  bool deviceMsgs_ = false;
   struct StagedRecv {
     int dst, srcRank, tag;
     std::unique_ptr<DeviceUnpacker> unpacker;
@@ -475,6 +478,9 @@ public:
       }
 
     /* staged: tag = (src dom, dst dom); FIFO per (rank pair, tag) keeps iterations apart */
+    deviceMsgs_ = dd_.any_methods(MethodFlags::CudaAwareMpi) && dd_.comm_->device_buffers();
+    if (dd_.any_methods(MethodFlags::CudaAwareMpi) && !deviceMsgs_ && dd_.rank_ == 0)
+      LOG_WARN("CudaAwareMpi requested but communicator '" << dd_.comm_->name() << "' does not take device pointers: staging through pinned memory");
     for (size_t di = 0; di < nd_; ++di) {
       for (auto &kv : stagedOut[di]) {
         StagedSend s;
@@ -484,7 +490,7 @@ public:
         s.packer.reset(new DevicePacker(streams_[di]));
         s.packer->prepare(&dd_.domains_[di], kv.second);
         DevGuard g(dd_.domains_[di].gpu());
-        CUDA_RUNTIME(cudaHostAlloc(&s.host, size_t(s.packer->size()), cudaHostAllocDefault));
+        if (!deviceMsgs_) CUDA_RUNTIME(cudaHostAlloc(&s.host, size_t(s.packer->size()), cudaHostAllocDefault));
         CUDA_RUNTIME(cudaEventCreateWithFlags(&s.staged, cudaEventDisableTiming));
         stagedSends_.push_back(std::move(s));
       }
@@ -496,7 +502,7 @@ public:
         r.unpacker.reset(new DeviceUnpacker(streams_[di]));
         r.unpacker->prepare(&dd_.domains_[di], kv.second);
         DevGuard g(dd_.domains_[di].gpu());
-        CUDA_RUNTIME(cudaHostAlloc(&r.host, size_t(r.unpacker->size()), cudaHostAllocDefault));
+        if (!deviceMsgs_) CUDA_RUNTIME(cudaHostAlloc(&r.host, size_t(r.unpacker->size()), cudaHostAllocDefault));
         stagedRecvs_.push_back(std::move(r));
       }
     }
@@ -575,7 +581,8 @@ public:
     for (StagedSend &s : stagedSends_) {
       DevGuard g(doms[size_t(s.src)].gpu());
       s.packer->pack();
-      CUDA_RUNTIME(cudaMemcpyAsync(s.host, s.packer->data(), size_t(s.packer->size()), cudaMemcpyDeviceToHost, streams_[size_t(s.src)]));
+      if (!deviceMsgs_)
+        CUDA_RUNTIME(cudaMemcpyAsync(s.host, s.packer->data(), size_t(s.packer->size()), cudaMemcpyDeviceToHost, streams_[size_t(s.src)]));
       CUDA_RUNTIME(cudaEventRecord(s.staged, streams_[size_t(s.src)]));
       s.pending = true;
     }
@@ -647,7 +654,7 @@ public:
         if (!s.pending) continue;
         const cudaError_t q = cudaEventQuery(s.staged);
         if (q == cudaSuccess) {
-          comm.send(s.dstRank, s.tag, s.host, size_t(s.packer->size()));
+          comm.send(s.dstRank, s.tag, deviceMsgs_ ? s.packer->data() : s.host, size_t(s.packer->size()));
           s.pending = false;
           --open;
         } else if (q != cudaErrorNotReady) {
@@ -656,9 +663,10 @@ public:
       }
       for (StagedRecv &r : stagedRecvs_) {
         if (!r.pending) continue;
-        if (comm.try_recv(r.srcRank, r.tag, r.host, size_t(r.unpacker->size()))) {
+        if (comm.try_recv(r.srcRank, r.tag, deviceMsgs_ ? r.unpacker->data() : r.host, size_t(r.unpacker->size()))) {
           DevGuard g(doms[size_t(r.dst)].gpu());
-          CUDA_RUNTIME(cudaMemcpyAsync(r.unpacker->data(), r.host, size_t(r.unpacker->size()), cudaMemcpyHostToDevice, streams_[size_t(r.dst)]));
+          if (!deviceMsgs_)
+            CUDA_RUNTIME(cudaMemcpyAsync(r.unpacker->data(), r.host, size_t(r.unpacker->size()), cudaMemcpyHostToDevice, streams_[size_t(r.dst)]));
           r.unpacker->unpack();
           r.pending = false;
           --open;
@@ -752,13 +760,16 @@ public:
       }
     }
     stencil::Comm &comm = *dd_.comm_;
-    dd_.numBytesCudaMpi_ = comm.allreduce_sum(staged);
+    /* deviceMsgs_ is a property of the communicator, so it is the same on every rank */
+    dd_.numBytesCudaMpi_ = comm.allreduce_sum(deviceMsgs_ ? 0 : staged);
+    dd_.numBytesCudaAwareMpi_ = comm.allreduce_sum(deviceMsgs_ ? staged : 0);
     dd_.numBytesCudaMpiColocated_ = comm.allreduce_sum(colo);
     dd_.numBytesCudaMemcpyPeer_ = comm.allreduce_sum(peer);
     dd_.numBytesCudaKernel_ = comm.allreduce_sum(kernel);
     dd_.numBytesNvlinkDirect_ = comm.allreduce_sum(direct);
     if (dd_.rank_ == 0) {
       LOG_INFO(dd_.numBytesCudaMpi_ << "B CudaMpi / exchange");
+      LOG_INFO(dd_.numBytesCudaAwareMpi_ << "B CudaAwareMpi / exchange");
       LOG_INFO(dd_.numBytesCudaMpiColocated_ << "B CudaMpiColocated / exchange");
       LOG_INFO(dd_.numBytesCudaMemcpyPeer_ << "B CudaMemcpyPeer / exchange");
       LOG_INFO(dd_.numBytesCudaKernel_ << "B CudaKernel / exchange");

@@ -7,11 +7,45 @@
 #include <cmath>
 #include <cstring>
 #include <fstream>
+#include <map>
 #include <sstream>
 #include <vector>
 #include "stencil/stencil.hpp"
 
+/* MpiComm compiled against the one-rank MPI stand-in, as in test_cpu_mpi_comm.cpp */
+#define STENCIL_USE_MPI 1
+#define make_mpi_comm make_mpi_comm_over_shim_cuda
+#include "../src/mpi_comm.cpp"
+#undef make_mpi_comm
+
 namespace {
+
+/* a one-rank communicator that takes DEVICE pointers, standing in for a CUDA-aware MPI */
+class DeviceLoopComm : public stencil::Comm {
+public:
+  int rank() const override { return 0; }
+  int size() const override { return 1; }
+  const char *name() const override { return "device-loop"; }
+  bool device_buffers() const override { return true; }
+  void send(int, int tag, const void *buf, size_t bytes) override {
+    std::vector<char> m(bytes);
+    CUDA_RUNTIME(cudaMemcpy(m.data(), buf, bytes, cudaMemcpyDefault));
+    box_[tag].push_back(std::move(m));
+    ++sends;
+  }
+  bool try_recv(int, int tag, void *buf, size_t bytes) override {
+    auto it = box_.find(tag);
+    if (it == box_.end() || it->second.empty()) return false;
+    if (it->second.front().size() != bytes) return false;
+    CUDA_RUNTIME(cudaMemcpy(buf, it->second.front().data(), bytes, cudaMemcpyDefault));
+    it->second.erase(it->second.begin());
+    return true;
+  }
+  size_t sends = 0;
+
+private:
+  std::map<int, std::vector<std::vector<char>>> box_;
+};
 
 /* exact, quantity-specific encodings of a global coordinate */
 float enc_f(const Dim3 &p) { return float(p.x + 64 * p.y + 4096 * p.z); }
@@ -88,8 +122,8 @@ size_t count_wrong(DistributedDomain &dd, const Radius &radius) {
 }
 
 size_t run_case(const Dim3 &size, const Radius &radius, MethodFlags methods, const std::vector<int> &gpus, PlacementStrategy strategy,
-                int rounds = 2) {
-  DistributedDomain dd(size_t(size.x), size_t(size.y), size_t(size.z));
+                int rounds = 2, stencil::Comm *comm = nullptr, uint64_t *awareBytes = nullptr, uint64_t *stagedBytes = nullptr) {
+  DistributedDomain dd(size_t(size.x), size_t(size.y), size_t(size.z), comm ? *comm : stencil::world());
   dd.set_gpus(gpus);
   dd.set_radius(radius);
   dd.set_methods(methods);
@@ -98,6 +132,8 @@ size_t run_case(const Dim3 &size, const Radius &radius, MethodFlags methods, con
   Fields q{dd.add_data<float>("f"), dd.add_data<unsigned char>("c"), dd.add_data<double>("d")};
   (void)q;
   dd.realize();
+  if (awareBytes) *awareBytes = dd.exchange_bytes_for_method(MethodFlags::CudaAwareMpi);
+  if (stagedBytes) *stagedBytes = dd.exchange_bytes_for_method(MethodFlags::CudaMpi);
   size_t wrong = 0;
   for (int r = 0; r < rounds; ++r) {
     fill(dd);
@@ -314,4 +350,30 @@ TEST_CASE("non-periodic boundaries leave the outer halos untouched", "[cuda][exc
         REQUIRE(inner != -1.f); // the internal interface is exchanged
       }
   }
+}
+
+TEST_CASE("exchange: staged transport over MpiComm, and device-pointer messages (CudaAwareMpi)", "[cuda][exchange][comm]") {
+  /* the reference forces every message, self-sends included, through MPI in test_cuda_mpi_exchange.cu */
+  std::unique_ptr<stencil::Comm> mpi = stencil::make_mpi_comm_over_shim_cuda();
+  uint64_t aware = 1, staged = 0;
+  REQUIRE(run_case(Dim3(12, 10, 9), Radius::constant(2), MethodFlags::CudaMpi, {0, 0}, PlacementStrategy::Trivial, 3, mpi.get(), &aware, &staged) == 0);
+  REQUIRE(aware == 0);
+  REQUIRE(staged > 0);
+  /* asking for CudaAwareMpi on a communicator without device pointers falls back to pinned staging */
+  REQUIRE(run_case(Dim3(12, 10, 9), Radius::constant(1), MethodFlags::CudaAwareMpi, {0, 0}, PlacementStrategy::Trivial, 2, mpi.get(), &aware, &staged) == 0);
+  REQUIRE(aware == 0);
+  REQUIRE(staged > 0);
+
+  DeviceLoopComm dev;
+  for (const Radius &r : radius_shapes()) {
+    REQUIRE(run_case(Dim3(10, 10, 10), r, MethodFlags::CudaAwareMpi, {0, 0}, PlacementStrategy::Trivial, 2, &dev, &aware, &staged) == 0);
+    REQUIRE(staged == 0);
+    REQUIRE(aware > 0);
+  }
+  REQUIRE(dev.sends > 0);
+  /* with faster methods enabled too, only what they cannot carry is left to the communicator (nothing, on one node) */
+  const size_t before = dev.sends;
+  REQUIRE(run_case(Dim3(10, 10, 10), Radius::constant(1), MethodFlags::All | MethodFlags::CudaAwareMpi, {0, 0}, PlacementStrategy::Trivial, 2, &dev, &aware, &staged) == 0);
+  REQUIRE(dev.sends == before);
+  REQUIRE(aware == 0);
 }
