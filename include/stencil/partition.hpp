@@ -17,6 +17,7 @@
    * the comm matrix accumulates when two directions reach the same neighbour. */
 #include <cassert>
 #include <cstdint>
+#include <cstdlib>
 #include <functional>
 #include <iostream>
 #include <map>
@@ -50,6 +51,29 @@ inline std::vector<int64_t> prime_factors_desc(int64_t n) {
 
 inline int64_t div_ceil(int64_t n, int64_t d) { return (n + d - 1) / d; }
 
+/* Which axis wins when the split criterion ties (cubic domains tie all the time). The reference always takes x
+   first (partition.hpp:52-58, :183-189 there). x is the contiguous axis: cutting it creates faces made of 4-12 byte
+   row fragments — one DRAM sector and one NVLink packet per row on B200 — and shortens the rows a 128-cell tile has
+   to fill. So the default here is the opposite order, z before y before x; TieBreak::X restores the reference's
+   subdomain grids (also: env STENCIL_PARTITION_TIES=x). */
+enum class TieBreak { Z, X };
+inline TieBreak &tie_break_storage() {
+  static TieBreak t = [] {
+    const char *e = std::getenv("STENCIL_PARTITION_TIES");
+    return (e && (e[0] == 'x' || e[0] == 'X')) ? TieBreak::X : TieBreak::Z;
+  }();
+  return t;
+}
+inline int pick_axis(int64_t x, int64_t y, int64_t z, bool wantLargest) {
+  const int64_t v[3] = {wantLargest ? x : -x, wantLargest ? y : -y, wantLargest ? z : -z};
+  const int order[2][3] = {{2, 1, 0}, {0, 1, 2}};
+  const int *o = order[tie_break_storage() == TieBreak::X ? 1 : 0];
+  int best = o[0];
+  for (int k = 1; k < 3; ++k)
+    if (v[o[k]] > v[best]) best = o[k];
+  return best;
+}
+
 inline int64_t linearize(const Dim3 &idx, const Dim3 &dim) {
   assert(idx.all_ge(0) && idx.all_lt(dim));
   return idx.x + dim.x * (idx.y + dim.y * idx.z);
@@ -77,6 +101,10 @@ inline Dim3 part_origin(const Dim3 &ceilSz, const Dim3 &rem, const Dim3 &idx) {
 } // namespace detail
 } // namespace stencil
 
+/* tie-breaking order of both partitioners (process-wide; set before realize()) */
+inline void set_partition_tie_break(stencil::detail::TieBreak t) { stencil::detail::tie_break_storage() = t; }
+inline stencil::detail::TieBreak partition_tie_break() { return stencil::detail::tie_break_storage(); }
+
 class RankPartition {
   Dim3 dim_;  // subdomains per axis
   Dim3 size_; // ceil subdomain size
@@ -86,11 +114,7 @@ public:
   RankPartition() : dim_(1, 1, 1) {}
   RankPartition(const Dim3 &size, int64_t n) : dim_(1, 1, 1), size_(size) {
     for (int64_t f : stencil::detail::prime_factors_desc(n)) {
-      int a = 2;
-      if (size_.x >= size_.y && size_.x >= size_.z)
-        a = 0;
-      else if (size_.y >= size_.z)
-        a = 1;
+      const int a = stencil::detail::pick_axis(size_.x, size_.y, size_.z, /*wantLargest=*/true);
       size_[a] = stencil::detail::div_ceil(size_[a], f);
       dim_[a] *= f;
     }
@@ -112,11 +136,7 @@ class NodePartition {
       const int64_t xi = size_.y * size_.z * int64_t(radius.x(1) + radius.x(-1));
       const int64_t yi = size_.x * size_.z * int64_t(radius.y(1) + radius.y(-1));
       const int64_t zi = size_.x * size_.y * int64_t(radius.z(1) + radius.z(-1));
-      int a = 2;
-      if (xi <= yi && xi <= zi)
-        a = 0;
-      else if (yi <= zi)
-        a = 1;
+      const int a = stencil::detail::pick_axis(xi, yi, zi, /*wantLargest=*/false);
       size_[a] = stencil::detail::div_ceil(size_[a], f);
       dim[a] *= f;
     }

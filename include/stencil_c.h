@@ -36,6 +36,9 @@ double stencil_comm_allreduce_max(double v);
 void stencil_comm_finalize(void);
 
 /* ---- partition, QAP and placement: pure CPU (reference: partition.hpp, qap.hpp) ---- */
+/* which axis is cut when the criterion ties: 0 = z, then y, then x (default; keeps x rows long and faces contiguous),
+   1 = x first (the reference's order). Returns the previous setting. Process-wide; set before realize(). */
+int stencil_set_partition_ties(int xFirst);
 int stencil_rank_partition(const int64_t size[3], int64_t n, int64_t dim_out[3]);
 int stencil_rank_partition_subdomain(const int64_t size[3], int64_t n, const int64_t idx[3], int64_t size_out[3],
                                      int64_t origin_out[3]);

@@ -84,6 +84,12 @@ void stencil_comm_barrier(void) { stencil::world().barrier(); }
 double stencil_comm_allreduce_max(double v) { return stencil::world().allreduce_max(v); }
 void stencil_comm_finalize(void) { stencil::finalize_world(); }
 
+int stencil_set_partition_ties(int xFirst) {
+  const int prev = partition_tie_break() == stencil::detail::TieBreak::X ? 1 : 0;
+  set_partition_tie_break(xFirst ? stencil::detail::TieBreak::X : stencil::detail::TieBreak::Z);
+  return prev;
+}
+
 int stencil_rank_partition(const int64_t size[3], int64_t n, int64_t dim_out[3]) {
   if (n < 1) return -1;
   put(dim_out, RankPartition(d3(size), n).dim());

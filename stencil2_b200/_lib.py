@@ -35,6 +35,7 @@ def _declare(l):
         "stencil_comm_barrier": (None, []),
         "stencil_comm_allreduce_max": (dbl, [dbl]),
         "stencil_comm_finalize": (None, []),
+        "stencil_set_partition_ties": (i, [i]),
         "stencil_rank_partition": (i, [I64x3, i64, I64x3]),
         "stencil_rank_partition_subdomain": (i, [I64x3, i64, I64x3, I64x3, I64x3]),
         "stencil_node_partition": (i, [I64x3, U64x27, i64, i64, I64x3, I64x3]),

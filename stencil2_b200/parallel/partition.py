@@ -2,6 +2,12 @@
 from .._lib import lib, i3, radius27, I64x3
 
 
+def set_partition_ties(x_first):
+    """Axis cut on ties: False = z, y, x (default: long x rows, contiguous faces); True = x first (reference order).
+    Returns the previous setting."""
+    return bool(lib().stencil_set_partition_ties(1 if x_first else 0))
+
+
 class RankPartition:
     """Flat split of `size` into n boxes: prime factors of n largest first, always cutting the longest axis."""
 

@@ -4,6 +4,13 @@
 #include "harness.hpp"
 #include "stencil/partition.hpp"
 
+/* the expectations below are the reference's subdomain grids: ties cut x first */
+struct ReferenceTies {
+  stencil::detail::TieBreak saved = partition_tie_break();
+  ReferenceTies() { set_partition_tie_break(stencil::detail::TieBreak::X); }
+  ~ReferenceTies() { set_partition_tie_break(saved); }
+};
+
 TEST_CASE("rank partition even", "[partition]") {
   RankPartition p(Dim3(10, 5, 5), 2);
   REQUIRE(p.dim() == Dim3(2, 1, 1));
@@ -12,6 +19,7 @@ TEST_CASE("rank partition even", "[partition]") {
 }
 
 TEST_CASE("rank partition remainders", "[partition]") {
+  ReferenceTies ties;
   RankPartition p(Dim3(10, 3, 1), 4);
   const int64_t sizes[4] = {3, 3, 2, 2}, origins[4] = {0, 3, 6, 8};
   for (int i = 0; i < 4; ++i) {
@@ -47,6 +55,7 @@ static Radius faces(size_t r) {
 }
 
 TEST_CASE("node partition weak-scaling shapes", "[partition]") {
+  ReferenceTies ties;
   /* jacobi3d weak scaling, face radius 1 */
   REQUIRE(NodePartition(Dim3(512, 512, 512), faces(1), 1, 1).dim() == Dim3(1, 1, 1));
   NodePartition p2(Dim3(645, 645, 645), faces(1), 1, 2);
@@ -64,6 +73,7 @@ TEST_CASE("node partition weak-scaling shapes", "[partition]") {
 }
 
 TEST_CASE("node partition uneven radius changes the cut order", "[partition]") {
+  ReferenceTies ties;
   Radius r = Radius::constant(1);
   r.dir(1, 0, 0) = 2; // +x=2, -x=1 => x interface weighted 3, y/z weighted 2
   REQUIRE(NodePartition(Dim3(1024, 1024, 1024), r, 1, 2).dim() == Dim3(1, 2, 1));
@@ -73,6 +83,7 @@ TEST_CASE("node partition uneven radius changes the cut order", "[partition]") {
 }
 
 TEST_CASE("node partition two levels and odd sizes", "[partition]") {
+  ReferenceTies ties;
   NodePartition p(Dim3(1024, 1024, 1024), Radius::constant(3), 2, 4);
   REQUIRE(p.sys_dim() == Dim3(2, 1, 1));
   REQUIRE(p.node_dim() == Dim3(1, 2, 2));
@@ -87,4 +98,25 @@ TEST_CASE("node partition two levels and odd sizes", "[partition]") {
   REQUIRE(s.sys_idx(0) == Dim3(0, 0, 0));
   REQUIRE(s.node_idx(4) == Dim3(1, 1, 0));
   REQUIRE(s.idx(5) == Dim3(2, 1, 0));
+}
+
+TEST_CASE("ties cut z before y before x by default, and the reference order on request", "[partition]") {
+  REQUIRE(partition_tie_break() == stencil::detail::TieBreak::Z);
+  const Radius r = Radius::constant(1);
+  /* a cube on 2, 4, 8 GPUs: the contiguous axis is cut last */
+  REQUIRE(NodePartition(Dim3(645, 645, 645), r, 1, 2).dim() == Dim3(1, 1, 2));
+  REQUIRE(NodePartition(Dim3(813, 813, 813), r, 1, 4).dim() == Dim3(1, 2, 2));
+  REQUIRE(NodePartition(Dim3(1024, 1024, 1024), r, 1, 8).dim() == Dim3(2, 2, 2));
+  REQUIRE(RankPartition(Dim3(64, 64, 64), 2).dim() == Dim3(1, 1, 2));
+  REQUIRE(RankPartition(Dim3(64, 64, 64), 4).dim() == Dim3(1, 2, 2));
+  /* no tie: the criterion decides, whatever the order */
+  REQUIRE(RankPartition(Dim3(100, 64, 64), 2).dim() == Dim3(2, 1, 1));
+  REQUIRE(NodePartition(Dim3(64, 512, 512), r, 1, 2).dim() == Dim3(1, 1, 2)); // y and z tie, x is the worst cut
+  REQUIRE(NodePartition(Dim3(512, 512, 64), r, 1, 2).dim() == Dim3(1, 2, 1)); // x and y tie, z is the worst cut
+  {
+    ReferenceTies ties;
+    REQUIRE(NodePartition(Dim3(645, 645, 645), r, 1, 2).dim() == Dim3(2, 1, 1));
+    REQUIRE(RankPartition(Dim3(64, 64, 64), 4).dim() == Dim3(2, 2, 1));
+  }
+  REQUIRE(partition_tie_break() == stencil::detail::TieBreak::Z);
 }

@@ -10,6 +10,13 @@ static std::vector<int> iota(int n) {
   return v;
 }
 
+/* the expectations below are the reference's subdomain grids: ties cut x first */
+struct ReferenceTies {
+  stencil::detail::TieBreak saved = partition_tie_break();
+  ReferenceTies() { set_partition_tie_break(stencil::detail::TieBreak::X); }
+  ~ReferenceTies() { set_partition_tie_break(saved); }
+};
+
 TEST_CASE("trivial placement assigns in linear order", "[placement]") {
   /* two ranks: 3 GPUs and 1 GPU */
   Trivial t(Dim3(40, 10, 10), std::vector<int>{3, 1}, std::vector<int>{0, 1, 2, 0});
@@ -71,6 +78,7 @@ TEST_CASE("node-aware placement keeps heavy faces on fast links", "[placement]")
 }
 
 TEST_CASE("node-aware placement across two nodes indexes the global grid", "[placement]") {
+  ReferenceTies ties;
   auto uniform = [](int a, int b) { return a == b ? 10.0 : 1.0; };
   /* 2 nodes x 2 ranks x 2 GPUs; ranks 0,1 on node 0 and 2,3 on node 1 */
   std::vector<int> cudaOf = {0, 1, 2, 3, 0, 1, 2, 3};

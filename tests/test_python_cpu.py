@@ -28,17 +28,29 @@ def test_rank_partition_matches_reference_cases(built):
 
 
 def test_node_partition_baseline_configs(built):
-    from stencil2_b200.parallel import NodePartition
+    from stencil2_b200.parallel import NodePartition, set_partition_ties
+    # default: ties cut z, then y, then x (the contiguous axis last)
     assert NodePartition((1024,) * 3, FACES1, 1, 8).dim == (2, 2, 2)
     p2 = NodePartition((645,) * 3, FACES1, 1, 2)
-    assert p2.subdomain((0, 0, 0))[0] == (323, 645, 645) and p2.subdomain((1, 0, 0))[0] == (322, 645, 645)
+    assert p2.dim == (1, 1, 2) and p2.subdomain((0, 0, 0))[0] == (645, 645, 323) and p2.subdomain((0, 0, 1))[0] == (645, 645, 322)
     p4 = NodePartition((813,) * 3, FACES1, 1, 4)
-    assert p4.dim == (2, 2, 1) and p4.subdomain((1, 1, 0))[0] == (406, 406, 813)
-    uneven = {d: 1 for d in [(x, y, z) for x in (-1, 0, 1) for y in (-1, 0, 1) for z in (-1, 0, 1)]}
-    uneven[(1, 0, 0)] = 2
-    assert NodePartition((1024,) * 3, uneven, 1, 2).dim == (1, 2, 1)
-    two = NodePartition((1024,) * 3, 3, 2, 4)
-    assert two.sys_dim == (2, 1, 1) and two.node_dim == (1, 2, 2)
+    assert p4.dim == (1, 2, 2) and p4.subdomain((0, 1, 1))[0] == (813, 406, 406)
+    # the reference's order on request
+    prev = set_partition_ties(True)
+    try:
+        assert prev is False
+        assert NodePartition((1024,) * 3, FACES1, 1, 8).dim == (2, 2, 2)
+        p2 = NodePartition((645,) * 3, FACES1, 1, 2)
+        assert p2.subdomain((0, 0, 0))[0] == (323, 645, 645) and p2.subdomain((1, 0, 0))[0] == (322, 645, 645)
+        p4 = NodePartition((813,) * 3, FACES1, 1, 4)
+        assert p4.dim == (2, 2, 1) and p4.subdomain((1, 1, 0))[0] == (406, 406, 813)
+        uneven = {d: 1 for d in [(x, y, z) for x in (-1, 0, 1) for y in (-1, 0, 1) for z in (-1, 0, 1)]}
+        uneven[(1, 0, 0)] = 2
+        assert NodePartition((1024,) * 3, uneven, 1, 2).dim == (1, 2, 1)
+        two = NodePartition((1024,) * 3, 3, 2, 4)
+        assert two.sys_dim == (2, 1, 1) and two.node_dim == (1, 2, 2)
+    finally:
+        set_partition_ties(prev)
 
 
 def test_qap_pinned_permutations(built):
@@ -56,7 +68,19 @@ def test_qap_pinned_permutations(built):
 
 def test_placement_512_cubed_on_synthetic_8gpu_topologies(built):
     """BASELINE config 1: 512^3 partition + QAP placement on synthetic 8-GPU NVLink topologies, no GPU."""
-    from stencil2_b200.parallel import place_node_aware
+    from stencil2_b200.parallel import place_node_aware, set_partition_ties
+    prev = set_partition_ties(True)  # the counts below are for the reference's 2x2x2 grid
+    try:
+        _placement_512_cases(place_node_aware)
+    finally:
+        set_partition_ties(prev)
+    # default tie order: 512x512x1024 on 8 GPUs becomes 1x2x4 (x rows stay whole); still a valid assignment
+    isl = [[100.0 if i == j else (25.0 if i % 2 == j % 2 else 1.0) for j in range(8)] for i in range(8)]
+    cuda, dim = place_node_aware((512, 512, 1024), 3, isl)
+    assert dim == (1, 2, 4) and sorted(cuda) == list(range(8))
+
+
+def _placement_512_cases(place_node_aware):
     n = 8
     uniform = [[10.0 if i == j else 1.0 for j in range(n)] for i in range(n)]
     cuda, dim = place_node_aware((512, 512, 512), 3, uniform)
