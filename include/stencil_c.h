@@ -162,6 +162,26 @@ int stencil_jacobi_step_io(stencil_jacobi_t *j, const void *params_pinned, size_
 /* host reference: one iteration on a dense periodic x*y*z fp32 array (same arithmetic as the kernel) */
 int stencil_jacobi_host_step(float *next, const float *curr, int64_t x, int64_t y, int64_t z);
 
+/* ---- AstarothSim engine (reference: bin/astaroth_sim.cu): radius 3, `fields` quantities of fp32 or fp64 ---- */
+typedef struct stencil_astaroth stencil_astaroth_t;
+#define STENCIL_ASTAROTH_AVERAGE7 0 /* the reference's stand-in compute */
+#define STENCIL_ASTAROTH_STAR19 1   /* next = curr + dt * (6th-order 19-point Laplacian) */
+/* overlap: 1 interior/exchange/exterior schedule, 0 exchange then one whole-region launch, -1 engine's choice */
+stencil_astaroth_t *stencil_astaroth_create(uint64_t x, uint64_t y, uint64_t z, int methods, int placement, int stencil_kind, int fields,
+                                            int fp64, int overlap, const int *gpus, int ngpus, double dt);
+void stencil_astaroth_destroy(stencil_astaroth_t *a);
+int stencil_astaroth_init(stencil_astaroth_t *a);
+int stencil_astaroth_step(stencil_astaroth_t *a);
+int stencil_astaroth_sync(stencil_astaroth_t *a);
+/* `iters` iterations; host wall seconds (max over ranks); *exchange_seconds (may be NULL) = time inside exchange() */
+double stencil_astaroth_run(stencil_astaroth_t *a, int iters, double *exchange_seconds);
+uint64_t stencil_astaroth_launches(const stencil_astaroth_t *a);
+/* dense [z][y][x] copy of one field as double into out[x*y*z]; cells owned by other ranks are NaN */
+int stencil_astaroth_gather(stencil_astaroth_t *a, int field, double *out, uint64_t count);
+/* host reference of one step on a dense periodic array */
+int stencil_astaroth_host_step(double *next, const double *curr, int64_t x, int64_t y, int64_t z, int stencil_kind, int fp64, double dt);
+stencil_domain_t *stencil_astaroth_domain(stencil_astaroth_t *a); /* borrowed: do not destroy */
+
 #ifdef __cplusplus
 }
 #endif

@@ -5,6 +5,7 @@
 #include <memory>
 
 #include "stencil/copy.cuh"
+#include "stencil/astaroth.hpp"
 #include "stencil/jacobi.hpp"
 #include "stencil/pack_kernel.cuh"
 #include "stencil/reduce.hpp"
@@ -21,6 +22,11 @@ struct stencil_domain {
 struct stencil_jacobi {
   std::unique_ptr<stencil::Jacobi3D> j;
   stencil_domain view; // borrowed view of j->domain()
+};
+
+struct stencil_astaroth {
+  std::unique_ptr<stencil::AstarothSim> a;
+  stencil_domain view;
 };
 
 namespace {
@@ -350,5 +356,60 @@ int stencil_jacobi_host_step(float *next, const float *curr, int64_t x, int64_t 
   std::memcpy(next, n.data(), n.size() * sizeof(float));
   return 0;
 }
+
+/* ---- AstarothSim ---- */
+stencil_astaroth_t *stencil_astaroth_create(uint64_t x, uint64_t y, uint64_t z, int methods, int placement, int stencil_kind, int fields,
+                                            int fp64, int overlap, const int *gpus, int ngpus, double dt) {
+  if (fields < 1) return nullptr;
+  stencil::AstarothSim::Options opt;
+  opt.methods = static_cast<MethodFlags>(methods);
+  opt.placement = placement == STENCIL_PLACEMENT_TRIVIAL ? PlacementStrategy::Trivial : PlacementStrategy::NodeAware;
+  opt.stencil = stencil_kind == STENCIL_ASTAROTH_STAR19 ? stencil::AstarothSim::Stencil::Star19 : stencil::AstarothSim::Stencil::Average7;
+  opt.fields = fields;
+  opt.fp64 = fp64 != 0;
+  opt.autoSchedule = overlap < 0;
+  opt.overlap = overlap != 0;
+  if (dt > 0) opt.dt = dt;
+  if (gpus && ngpus > 0) opt.gpus.assign(gpus, gpus + ngpus);
+  stencil_astaroth_t *h = new stencil_astaroth;
+  h->a.reset(new stencil::AstarothSim(x, y, z, opt));
+  h->view.dd = &h->a->domain();
+  return h;
+}
+void stencil_astaroth_destroy(stencil_astaroth_t *a) { delete a; }
+int stencil_astaroth_init(stencil_astaroth_t *a) {
+  if (!a) return -1;
+  a->a->init();
+  return 0;
+}
+int stencil_astaroth_step(stencil_astaroth_t *a) {
+  if (!a) return -1;
+  a->a->step();
+  return 0;
+}
+int stencil_astaroth_sync(stencil_astaroth_t *a) {
+  if (!a) return -1;
+  a->a->sync();
+  return 0;
+}
+double stencil_astaroth_run(stencil_astaroth_t *a, int iters, double *exchange_seconds) { return a ? a->a->run(iters, exchange_seconds) : -1.0; }
+uint64_t stencil_astaroth_launches(const stencil_astaroth_t *a) { return a ? a->a->launches() : 0; }
+int stencil_astaroth_gather(stencil_astaroth_t *a, int field, double *out, uint64_t count) {
+  if (!a || !out || field < 0 || field >= a->a->options().fields) return -1;
+  const std::vector<double> v = a->a->gather(field);
+  if (v.size() != count) return -2;
+  std::memcpy(out, v.data(), v.size() * sizeof(double));
+  return 0;
+}
+int stencil_astaroth_host_step(double *next, const double *curr, int64_t x, int64_t y, int64_t z, int stencil_kind, int fp64, double dt) {
+  if (!next || !curr || x < 1 || y < 1 || z < 1) return -1;
+  std::vector<double> c(curr, curr + x * y * z), n;
+  stencil::astaroth_host_step(n, c, Dim3(x, y, z),
+                              stencil_kind == STENCIL_ASTAROTH_STAR19 ? stencil::AstarothSim::Stencil::Star19 : stencil::AstarothSim::Stencil::Average7,
+                              fp64 != 0, dt);
+  std::memcpy(next, n.data(), n.size() * sizeof(double));
+  return 0;
+}
+stencil_domain_t *stencil_astaroth_domain(stencil_astaroth_t *a) { return a ? &a->view : nullptr; }
 
 } // extern "C"

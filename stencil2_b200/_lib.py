@@ -83,6 +83,16 @@ def _declare(l):
         "stencil_jacobi_domain": (vp, [vp]),
         "stencil_jacobi_step_io": (i, [vp, vp, sz, vp]),
         "stencil_jacobi_host_step": (i, [vp, vp, i64, i64, i64]),
+        "stencil_astaroth_create": (vp, [u64, u64, u64, i, i, i, i, i, i, P(i), i, dbl]),
+        "stencil_astaroth_destroy": (None, [vp]),
+        "stencil_astaroth_init": (i, [vp]),
+        "stencil_astaroth_step": (i, [vp]),
+        "stencil_astaroth_sync": (i, [vp]),
+        "stencil_astaroth_run": (dbl, [vp, i, P(dbl)]),
+        "stencil_astaroth_launches": (u64, [vp]),
+        "stencil_astaroth_gather": (i, [vp, i, vp, u64]),
+        "stencil_astaroth_host_step": (i, [vp, vp, i64, i64, i64, i, i, dbl]),
+        "stencil_astaroth_domain": (vp, [vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(l, name)

@@ -124,6 +124,25 @@ def test_host_jacobi_step_properties(built):
     assert b[10, 15, 26] == 1.0 and b[10, 15, 27] != 1.0
 
 
+def test_host_astaroth_step_against_numpy(built):
+    """The host reference of the 19-point radius-3 step is the 6th-order Laplacian: check it against numpy.roll."""
+    from stencil2_b200.models import astaroth_host_step
+    rng = np.random.default_rng(3)
+    a = rng.standard_normal((9, 10, 12))
+    dt = 0.01
+    b = astaroth_host_step(a, stencil=1, fp64=True, dt=dt)
+    lap = np.zeros_like(a)
+    for axis in range(3):
+        lap += 3 * (-49.0 / 18.0) * a / 3
+        for k, c in ((1, 1.5), (2, -3.0 / 20.0), (3, 1.0 / 90.0)):
+            lap += c * (np.roll(a, k, axis) + np.roll(a, -k, axis))
+    assert np.allclose(b, a + dt * lap, rtol=0, atol=1e-12)
+    # the reference's stand-in: plain 7-point average of the six face neighbours
+    c = astaroth_host_step(a, stencil=0, fp64=True)
+    avg = sum(np.roll(a, s, ax) for ax in range(3) for s in (1, -1)) / 6
+    assert np.allclose(c, avg, rtol=0, atol=1e-13)
+
+
 def test_two_process_tcp_group(built, tmp_path):
     """world_size 2 on this machine: the native Comm joins through MASTER_ADDR/MASTER_PORT like under torchrun."""
     script = tmp_path / "w.py"

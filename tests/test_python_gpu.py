@@ -30,6 +30,23 @@ def test_jacobi_modes_agree_with_host(built):
         j.close()
 
 
+def test_astaroth_engine_against_host(built):
+    from stencil2_b200.models import AstarothSim, astaroth_host_step
+    for size, fp64, tol in (((140, 24, 20), True, 1e-13), ((140, 24, 20), False, 5e-6)):
+        for overlap in (None, True):
+            sim = AstarothSim(*size, fields=2, fp64=fp64, stencil=AstarothSim.STAR19, overlap=overlap, gpus=[0, 0])
+            sim.init()
+            ref = sim.gather(1)
+            assert np.isfinite(ref).all() and ref.std() > 0.1
+            for _ in range(3):
+                sim.step()
+                ref = astaroth_host_step(ref, stencil=1, fp64=fp64, dt=sim.dt)
+            sim.sync()
+            assert np.abs(sim.gather(1) - ref).max() < tol
+            assert sim.launches > 0
+            sim.close()
+
+
 def test_ops_pack_and_reduce_against_numpy(built):
     import torch
     from stencil2_b200.ops import pack, unpack, reduce_sum_f32

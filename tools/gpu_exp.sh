@@ -2,9 +2,9 @@
 mkdir -p gpurun_out
 export STENCIL_LOG_LEVEL=1
 cd /root/repo
-timeout 900 ./build/bin/test_cuda > gpurun_out/t.log 2>&1; echo "test_cuda rc=$? $(tail -1 gpurun_out/t.log)"; grep FAIL gpurun_out/t.log | head
-echo "weak 512 r3 x4"; timeout 120 ./build/bin/weak 512 512 512 30 2>/dev/null | tail -2
-echo "bench-pack"; timeout 120 ./build/bin/bench-pack 2>/dev/null | tail -8
-echo "bench-exchange"; timeout 120 ./build/bin/bench-exchange 2>/dev/null | tail -4
-echo "astaroth"; timeout 120 ./build/bin/astaroth-sim --x 256 --y 256 --z 256 --fields 8 --double --star --iters 10 2>/dev/null
-echo "jacobi"; timeout 120 ./build/bin/jacobi3d 512 512 512 -n 30 --tile-z 16 2>/dev/null | tail -1
+A="./build/bin/jacobi3d 512 512 512 -n 40 --tile-z 16"
+for s in 0 2 4 6 7; do echo "skip=$s"; STENCIL_JACOBI_DEBUG_SKIP=$s timeout 120 $A 2>/dev/null | tail -1; done
+echo "no-fused (overlap)"; timeout 120 $A --no-fused 2>/dev/null | tail -1
+echo "no-overlap"; timeout 120 $A --no-fused --no-overlap 2>/dev/null | tail -1
+echo "tile-z 32"; timeout 120 ./build/bin/jacobi3d 512 512 512 -n 40 --tile-z 32 2>/dev/null | tail -1
+echo "tile-z 8"; timeout 120 ./build/bin/jacobi3d 512 512 512 -n 40 --tile-z 8 2>/dev/null | tail -1
