@@ -26,6 +26,7 @@
    every neighbour's flag (st.release.sys). At the start of the next iteration only boundary tiles look at the
    flags (ld.acquire.sys): they are the only ones that read halo cells, and their neighbours' flags were raised
    well before the previous kernel ended, so in steady state nobody spins. */
+#include "stencil/detail/tma.cuh"
 #include "stencil/nvtx.hpp"
 #include "stencil/jacobi.hpp"
 
@@ -279,29 +280,13 @@ template <bool FUSED> __global__ void __launch_bounds__(kThreads) jacobi7_kernel
 }
 
 
-/* ---- mbarrier / TMA primitives (PTX ISA: mbarrier, cp.async.bulk.tensor) ---- */
-__device__ __forceinline__ unsigned smem_u32(const void *p) { return unsigned(__cvta_generic_to_shared(p)); }
-__device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_arrive(unsigned long long *bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long *bar, unsigned bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity) {
-  asm volatile("{\n\t.reg .pred p;\n\tWAIT_%=:\n\t"
-               "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-               "@p bra DONE_%=;\n\tbra WAIT_%=;\n\tDONE_%=:\n\t}" ::"r"(smem_u32(bar)),
-               "r"(parity)
-               : "memory");
-}
+/* mbarrier / TMA primitives: stencil/detail/tma.cuh */
+using tma::mbar_arrive;
+using tma::mbar_arrive_expect_tx;
+using tma::mbar_init;
+using tma::mbar_wait;
 __device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *map, int cx, int cy, int cz, unsigned long long *bar) {
-  asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(
-                   smem_u32(dst)),
-               "l"(map), "r"(smem_u32(bar)), "r"(cx), "r"(cy), "r"(cz)
-               : "memory");
+  tma::load_3d(dst, map, cx, cy, cz, bar);
 }
 
 struct Cells { // four consecutive x cells of one row
@@ -729,33 +714,10 @@ Tile *upload(const std::vector<Tile> &t) {
   return d;
 }
 
-typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
-                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
-                                  CUtensorMapFloatOOBfill);
-
-/* the driver entry point is fetched through the runtime so that the library has no link dependency on libcuda */
-EncodeTiledFn encode_tiled() {
-  static EncodeTiledFn fn = [] {
-    void *p = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    CUDA_RUNTIME(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
-    if (!p || q != cudaDriverEntryPointSuccess) LOG_FATAL("cuTensorMapEncodeTiled is not available from this driver");
-    return reinterpret_cast<EncodeTiledFn>(p);
-  }();
-  return fn;
-}
-
 /* fp32 tensor over one padded buffer: dims (row pitch, rows, planes), box = one input plane of a tile */
 CUtensorMap make_plane_map(void *bufferStart, const Dim3 &pitch, const Dim3 &raw) {
-  CUtensorMap m;
-  const cuuint64_t dims[3] = {cuuint64_t(pitch.x), cuuint64_t(raw.y), cuuint64_t(raw.z)};
-  const cuuint64_t strides[2] = {cuuint64_t(pitch.x) * 4, cuuint64_t(pitch.x) * cuuint64_t(raw.y) * 4};
-  const cuuint32_t box[3] = {cuuint32_t(kTmaBoxX), cuuint32_t(kTmaBoxY), 1};
-  const cuuint32_t estr[3] = {1, 1, 1};
-  const CUresult rc = encode_tiled()(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, bufferStart, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                                     CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (rc != CUDA_SUCCESS) LOG_FATAL("cuTensorMapEncodeTiled failed with " << int(rc));
-  return m;
+  return tma::make_plane_map(bufferStart, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, sizeof(float), pitch.x, raw.y, raw.z, unsigned(kTmaBoxX),
+                             unsigned(kTmaBoxY));
 }
 
 const Dim3 kFaceDir[6] = {Dim3(-1, 0, 0), Dim3(1, 0, 0), Dim3(0, -1, 0), Dim3(0, 1, 0), Dim3(0, 0, -1), Dim3(0, 0, 1)};

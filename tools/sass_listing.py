@@ -10,7 +10,7 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "stencil2_b200", "lib", "libstencil_b200.so")
 OUT = os.path.join(ROOT, "profiles", "sass")
-KEEP = ["jacobi7_tma_kernelILb1ELi3", "jacobi7_tma_kernelILb0ELi3", "box_copy_kernelILb1", "box_copy_kernelILb0", "box_copy_batch_kernel",
+KEEP = ["jacobi7_tma_kernelILb1ELi2", "jacobi7_tma_kernelILb0ELi2", "astaroth_tma_kernelId", "astaroth_tma_kernelIf", "box_copy_kernelILb1", "box_copy_kernelILb0", "box_copy_batch_kernel",
         "wait_flags_kernel", "signal_flags_kernel", "reduce_sum_f32_kernel", "astaroth_kernelIdLb1", "astaroth_kernelIfLb0", "jacobi7_kernelILb0"]
 INTEREST = ["UTMALDG", "UTMASTG", "UBLKCP", "SYNCS", "MEMBAR", "LDG.E.128", "STG.E.128", "LDG.E.64", "STG.E.64", "LDG.E ", "STG.E ", "LDS.128", "LDS ",
             "SHFL", "ATOMG", "RED", "FFMA", "DFMA", "FADD", "DADD", "LD.E.STRONG.SYS", "ST.E.STRONG.SYS", "ERRBAR", "CCTL", "NANOSLEEP", "LDL", "STL"]
