@@ -36,11 +36,20 @@ def main(args):
         env.pop(k, None)
     iters = args.steps + max(args.warmup, 3)
     cmd = [exe, str(args.size), str(args.size), str(args.size), "-n", str(iters)]
+    sampler = None
+    try:  # clocks are sampled over the whole run of the binary (set-up included; the app exposes no hook for less)
+        sys.path.insert(0, os.path.dirname(HERE))
+        from stencil2_b200.utils.clocks import ClockSampler
+        sampler = ClockSampler(0, period_s=0.02).start()
+    except Exception:  # noqa: BLE001
+        sampler = None
     try:
         r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=3000, env=env, cwd="/tmp")
     except Exception as e:  # noqa: BLE001
         unavailable(f"reference jacobi3d failed to run: {e}")
         return
+    finally:
+        clocks = sampler.stop() if sampler else None
     line = [l for l in r.stdout.splitlines() if l.startswith("jacobi3d,")]
     if r.returncode != 0 or not line:
         unavailable("reference jacobi3d exited %d: %s" % (r.returncode, (r.stderr or r.stdout)[-300:].replace("\n", " | ")))
@@ -61,5 +70,6 @@ def main(args):
                    "build": "unmodified sources, nvcc sm_100 -O3, single-rank MPI shim (no MPI on this image), nvtx3 headers"},
         "e2e": {"value": round(cells / ttri / 1e9, 3), "unit": "Gcell/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
                 "note": "the reference app has no per-step host I/O; its timing is already host wall clock"},
+        "clocks": clocks,
         "gpu_launches": None,
     }), flush=True)

@@ -1,10 +1,7 @@
 #!/bin/bash
 mkdir -p gpurun_out
-export STENCIL_LOG_LEVEL=1
 cd /root/repo
-A="./build/bin/jacobi3d 512 512 512 -n 40 --tile-z 16"
-for s in 0 2 4 6 7; do echo "skip=$s"; STENCIL_JACOBI_DEBUG_SKIP=$s timeout 120 $A 2>/dev/null | tail -1; done
-echo "no-fused (overlap)"; timeout 120 $A --no-fused 2>/dev/null | tail -1
-echo "no-overlap"; timeout 120 $A --no-fused --no-overlap 2>/dev/null | tail -1
-echo "tile-z 32"; timeout 120 ./build/bin/jacobi3d 512 512 512 -n 40 --tile-z 32 2>/dev/null | tail -1
-echo "tile-z 8"; timeout 120 ./build/bin/jacobi3d 512 512 512 -n 40 --tile-z 8 2>/dev/null | tail -1
+timeout 900 python -m pytest tests/test_python_gpu.py tests/test_native_gpu.py -m gpu -x -q 2>&1 | tail -5
+for tz in 16 32; do echo "tile-z $tz"; timeout 300 python bench.py --steps 200 --warmup 10 --tile-z $tz 2>/dev/null | tail -1 | cut -c1-200; done
+timeout 300 python bench.py --steps 200 --warmup 10 --tile-z 16 2>/dev/null | tail -1 | python -c "import sys,json; d=json.loads(sys.stdin.read()); print(d['clocks'], d['e2e'])"
+timeout 600 python bench.py --impl reference --steps 30 --warmup 5 2>/dev/null | tail -1 | python -c "import sys,json; d=json.loads(sys.stdin.read()); print(d['value'], d['clocks'])"
