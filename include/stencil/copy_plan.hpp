@@ -74,7 +74,7 @@ struct BoxView {
   }
 };
 
-/* remote (or local) 32-bit epoch flags written with st.release.sys once every byte of the plan has been stored */
+/* remote (or local) 32-bit epoch flags written after a system-scope fence once every byte of the plan has been stored */
 struct SignalSet {
   static constexpr int kMax = 32;
   unsigned n;

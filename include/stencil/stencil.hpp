@@ -10,7 +10,7 @@
    * a new method, MethodFlags::NvlinkDirect (part of All): every message whose receiver sits on a peer-accessible
      GPU of this node — same process or another — is a segment of ONE device-initiated push per subdomain
      (src/box_copy.cu): boundary cells are stored straight into the neighbour's halo cells through NVLink, and the
-     last CTA publishes an epoch flag in the neighbour's slab (st.release.sys). No pack buffer, no cudaMemcpyPeer,
+     last CTA publishes an epoch flag in the neighbour's slab (fence.sys + store). No pack buffer, no cudaMemcpyPeer,
      no unpack kernel, no host in the data path. Receivers wait with one acquire-spin warp (other GPU) or a stream
      event (same GPU). The legacy flags keep their meaning and select legacy-equivalent paths:
        CudaKernel        same rank + same GPU        -> local segments of the push plan
@@ -153,6 +153,21 @@ public:
   /* Blocking halo exchange of all `curr` buffers: returns when every local halo is filled and every local send has
      been consumed. Launch interior work on your own streams before calling to overlap. */
   void exchange();
+
+  /* The same exchange in two halves, for callers that overlap it with their own work or never block the host:
+       exchange_async()  enqueues all device work of the exchange on the exchange streams and returns;
+       exchange_wait()   drives the host-mediated transports (staged / colocated) and waits for the streams.
+     exchange() == exchange_async(); exchange_wait();
+     If exchange_device_only() (every message travels by device stores or copies — always the case on one NVSwitch box
+     with the default methods), the host never has to wait: make your stream wait on exchange_done_event(i) before it
+     reads the halos of subdomain i, and hand the event that ends your use of subdomain i's buffers (the kernels that
+     wrote what will be sent next AND the kernels that read the halos about to be overwritten) to
+     exchange_after(i, e) before the next exchange_async(). Flag time-outs are reported by the next call. */
+  void exchange_async();
+  void exchange_wait();
+  bool exchange_device_only() const;
+  cudaEvent_t exchange_done_event(size_t i) const;
+  void exchange_after(size_t i, cudaEvent_t e);
 
   /* regions whose stencil does not read halo cells / up to six slabs that do (order +x,+y,+z,-x,-y,-z) */
   std::vector<Rect3> get_interior() const;

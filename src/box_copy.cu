@@ -48,8 +48,10 @@ __device__ __forceinline__ unsigned ld_stream(const unsigned *p) {
 __device__ __forceinline__ unsigned short ld_stream(const unsigned short *p) { return __ldg(p); }
 __device__ __forceinline__ unsigned char ld_stream(const unsigned char *p) { return __ldg(p); }
 
-__device__ __forceinline__ void st_release_sys(unsigned *p, unsigned v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+/* Flag stores are relaxed and follow ONE system-scope fence: a st.release.sys per flag is a fence each, and 26 of
+   them in a row by one thread put a ~15 us floor under every exchange. */
+__device__ __forceinline__ void st_relaxed_sys(unsigned *p, unsigned v) {
+  asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 __device__ __forceinline__ unsigned ld_acquire_sys(const unsigned *p) {
   unsigned v;
@@ -242,16 +244,18 @@ __global__ void __launch_bounds__(kThreads, 4)
     }
   }
   if (SIGNAL) {
-    /* every thread's stores -> CTA barrier -> one system-scope fence -> count this CTA as done.
-       The CTA that observes the full count owns the release stores to the (peer) flags. */
+    /* every thread's stores -> CTA barrier -> fence -> count this CTA as done.
+       The CTA that observes the full count owns the system-scope fence and the stores to the (peer) flags. */
     __syncthreads();
     if (threadIdx.x == 0) {
-      __threadfence_system();
+      /* release at GPU scope is enough here: the last CTA acquires the count at GPU scope and then releases at
+         system scope, and causality order is transitive across the two (same pattern as the fused Jacobi kernel) */
+      __threadfence();
       const unsigned prev = atomicAdd(done, 1u);
       if (prev == gridDim.x - 1) {
         *done = 0; // ready for the next launch on this stream
         __threadfence_system();
-        for (unsigned k = 0; k < sig.n; ++k) st_release_sys(sig.flag[k], epoch);
+        for (unsigned k = 0; k < sig.n; ++k) st_relaxed_sys(sig.flag[k], epoch);
       }
     }
   }
@@ -297,7 +301,7 @@ __global__ void __launch_bounds__(kThreads) box_copy_batch_kernel(const __grid_c
 __global__ void signal_flags_kernel(SignalSet sig, unsigned epoch) {
   if (threadIdx.x < sig.n) {
     __threadfence_system();
-    st_release_sys(sig.flag[threadIdx.x], epoch);
+    st_relaxed_sys(sig.flag[threadIdx.x], epoch);
   }
 }
 

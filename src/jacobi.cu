@@ -3,14 +3,14 @@
 
    Two kernel variants compute the same thing (Options::useTma picks; TMA is the default):
 
-   jacobi7_tma_kernel — the Blackwell path. A tile is 128 x 16 cells in xy, marched along z. One producer thread
-   streams the (128+8) x (16+2) input planes of the tile into a 6-deep shared-memory ring with
-   cp.async.bulk.tensor.3d (TMA; out-of-range parts of edge tiles are zero-filled by the hardware) and arms one
-   mbarrier per stage; eight consumer warps wait on the stage's mbarrier, read their centre / +-y rows as 16-byte
-   LDS, take +-x from the neighbouring lane, and hand the stage back through a second mbarrier. The centre column
-   of the last two planes and the in-plane partial sum live in registers, so every plane is read from shared
-   memory exactly once. Bytes in flight are set by the ring (6 x 9.8 KB per CTA, 3 CTAs per SM), not by registers,
-   which is what a latency-bound streaming stencil needs to reach HBM speed.
+   jacobi7_tma_kernel — the Blackwell path. A tile is 128 x 16 cells in xy, marched along z. Thread 0 streams the
+   (128+8) x (16+2) input planes of the tile into a 6-deep shared-memory ring with cp.async.bulk.tensor.3d (TMA;
+   out-of-range parts of edge tiles are zero-filled by the hardware) and arms one mbarrier per stage; the eight warps
+   wait on the stage's mbarrier, read their centre / +-y rows as 16-byte LDS, take +-x from the neighbouring lane, and
+   hand the stage back through a second mbarrier. The centre column of the last two planes and the in-plane partial
+   sum live in registers, so every plane is read from shared memory exactly once. Bytes in flight are set by the ring
+   (6 x 9.8 KB per CTA, 2 CTAs per SM), not by registers, which is what a latency-bound streaming stencil needs to
+   reach HBM speed.
 
    jacobi7_kernel — plain LDG version kept for comparison. A CTA is 32 lanes x 8 rows; a lane owns 4 consecutive x cells (one 16-byte vector), so a tile is
    128 x 8 cells in xy and is marched along z for tileZ planes with the centre column kept in registers
@@ -21,11 +21,12 @@
 
    Fusion. Tiles that own cells on a subdomain face additionally store those cells into the neighbour's `next`
    halo (peer pointer: NVLink store, or a plain local store when the axis wraps onto the same subdomain) —
-   16-byte vectors for y and z faces, one 4-byte store per row for x faces. Boundary tiles come first in the tile
-   table; each finishes with fence.sys + a counter increment, and the last one publishes the iteration number to
-   every neighbour's flag (st.release.sys). At the start of the next iteration only boundary tiles look at the
-   flags (ld.acquire.sys): they are the only ones that read halo cells, and their neighbours' flags were raised
-   well before the previous kernel ended, so in steady state nobody spins. */
+   16-byte vectors for y and z faces, one whole 32-byte sector per row (halo cell + row padding) for x faces. Tiles
+   that stored into ANOTHER GPU finish with a GPU-scope fence + a counter increment; the last of them issues one
+   system-scope fence and writes the iteration number to every such neighbour's flag. At the start of the next
+   iteration only those tiles look at the flags (ld.acquire.sys): they are the only ones that read halo cells written
+   by another GPU, and their neighbours' flags were raised well before the previous kernel ended, so in steady state
+   nobody spins. Same-GPU neighbours are ordered by the stream. */
 #include "stencil/detail/tma.cuh"
 #include "stencil/nvtx.hpp"
 #include "stencil/jacobi.hpp"
@@ -92,8 +93,9 @@ struct JacobiParams {
 /* Plain (coherent) loads on purpose: halo cells are written by OTHER GPUs while this kernel may already be running,
    and only become readable after the acquire on the neighbour's flag. ld.global.nc is outside that guarantee. */
 __device__ __forceinline__ float4 ldg4(const float *p) { return *reinterpret_cast<const float4 *>(p); }
-__device__ __forceinline__ void st_release_sys(unsigned *p, unsigned v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+/* relaxed: always issued right after one system-scope fence (a release store per flag would be a fence each) */
+__device__ __forceinline__ void st_flag_sys(unsigned *p, unsigned v) {
+  asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 __device__ __forceinline__ unsigned ld_acquire_sys(const unsigned *p) {
   unsigned v;
@@ -273,7 +275,7 @@ template <bool FUSED> __global__ void __launch_bounds__(kThreads) jacobi7_kernel
         *P.done = 0;
         __threadfence_system();
         for (int f = 0; f < 6; ++f)
-          if (P.nbFlag[f]) st_release_sys(P.nbFlag[f], P.epoch);
+          if (P.nbFlag[f]) st_flag_sys(P.nbFlag[f], P.epoch);
       }
     }
   }
@@ -372,7 +374,7 @@ __device__ __forceinline__ void signal_neighbours(const JacobiParams &P) {
       *P.done = 0;
       __threadfence_system();
       for (int f = 0; f < 6; ++f)
-        if (P.nbFlag[f]) st_release_sys(P.nbFlag[f], P.epoch);
+        if (P.nbFlag[f]) st_flag_sys(P.nbFlag[f], P.epoch);
     }
   }
 }

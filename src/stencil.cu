@@ -84,6 +84,9 @@ class Exchanger {
 
   std::vector<RcStream> streams_;
   std::vector<cudaEvent_t> pushDone_;
+  std::vector<cudaEvent_t> exDone_; // end of the enqueued exchange on each subdomain's stream (device-only plans)
+  std::vector<cudaEvent_t> after_;  // caller's events the next enqueue() waits for (not owned)
+  bool inFlight_ = false;
   /* STENCIL_EXCHANGE_TRACE=n: print per-subdomain device times of the first n exchanges (push kernel, flag wait) */
   int trace_ = 0;
   std::vector<cudaEvent_t> trA_, trB_, trC_;
@@ -264,6 +267,7 @@ public:
       cudaIpcCloseMemHandle(kv.second.ptr);
     }
     for (cudaEvent_t e : pushDone_) cudaEventDestroy(e);
+    for (cudaEvent_t e : exDone_) cudaEventDestroy(e);
     for (auto &pc : peerCopies_) cudaEventDestroy(pc.copied);
     for (auto &s : stagedSends_) {
       cudaEventDestroy(s.staged);
@@ -332,6 +336,10 @@ public:
       cudaEvent_t e;
       CUDA_RUNTIME(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
       pushDone_.push_back(e);
+      cudaEvent_t d;
+      CUDA_RUNTIME(cudaEventCreateWithFlags(&d, cudaEventDisableTiming));
+      exDone_.push_back(d);
+      after_.push_back(nullptr);
       if (trace_) {
         cudaEvent_t a, b, c;
         CUDA_RUNTIME(cudaEventCreate(&a));
@@ -410,6 +418,13 @@ public:
                 const Dim3 srcPos = dom.halo_pos(dir, false);
                 const Dim3 nbSize = pl->subdomain_size(nb.idx);
                 const Dim3 dstPos = stencil::halo_pos(dir * -1, nbSize, radius, true);
+                /* diagnostics only (results are wrong with it): STENCIL_EXCHANGE_DEBUG_DIRS is a mask of the message
+                   classes to keep in the push plan — 1 x faces, 2 y faces, 4 z faces, 8 edges, 16 corners */
+                if (const char *e = std::getenv("STENCIL_EXCHANGE_DEBUG_DIRS")) {
+                  const int nz = (dir.x != 0) + (dir.y != 0) + (dir.z != 0);
+                  const int cls = nz == 3 ? 16 : (nz == 2 ? 8 : (dir.x ? 1 : (dir.y ? 2 : 4)));
+                  if (!(std::atoi(e) & cls)) break;
+                }
                 for (size_t qi = 0; qi < nq; ++qi) {
                   if (nb.dev != me.dev && thin_for_link(dir, ext, dd_.elemSizes_[qi]))
                     push_[di].add(dom.view(qi), srcPos, mailbox_of(nb, dir * -1, qi, ext, me.dev), Dim3(0, 0, 0), ext);
@@ -564,9 +579,34 @@ public:
   /* ---------------- the per-iteration exchange ---------------- */
   void exchange() {
     STENCIL_RANGE("DD::exchange()");
+    enqueue();
+    finish();
+  }
+
+  bool device_only() const { return stagedSends_.empty() && stagedRecvs_.empty() && coloSends_.empty() && coloRecvs_.empty(); }
+  bool in_flight() const { return inFlight_; }
+  cudaEvent_t done_event(size_t di) const { return exDone_[di]; }
+  void set_after(size_t di, cudaEvent_t e) { after_[di] = e; }
+
+  /* Everything exchange() puts on the GPUs, without waiting for any of it. */
+  void enqueue() {
+    STENCIL_RANGE("DD::exchange: enqueue");
+    if (inFlight_) {
+      if (!device_only()) LOG_FATAL("exchange_async(): the previous exchange uses host-mediated transports and was not completed with exchange_wait()");
+      check_error_word();
+    }
+    inFlight_ = true;
     ++epoch_;
     stencil::Comm &comm = *dd_.comm_;
     std::vector<LocalDomain> &doms = dd_.domains_;
+
+    /* work the caller declared with exchange_after(): producers of the data to send, and consumers of the halos about to
+       be overwritten. Any local subdomain may receive from any other, so every exchange stream waits for all of them. */
+    for (size_t di = 0; di < nd_; ++di) {
+      DevGuard g(doms[di].gpu());
+      for (size_t dj = 0; dj < nd_; ++dj)
+        if (after_[dj]) CUDA_RUNTIME(cudaStreamWaitEvent(streams_[di], after_[dj], 0));
+    }
 
     /* 0. tell cross-process senders that my halos are free for this epoch (only other processes can be ahead of me) */
     for (size_t di = 0; di < nd_; ++di) {
@@ -645,6 +685,19 @@ public:
       if (trace_) CUDA_RUNTIME(cudaEventRecord(trC_[di], streams_[di]));
     }
 
+    if (device_only())
+      for (size_t di = 0; di < nd_; ++di) {
+        DevGuard g(doms[di].gpu());
+        CUDA_RUNTIME(cudaEventRecord(exDone_[di], streams_[di]));
+      }
+    for (size_t di = 0; di < nd_; ++di) after_[di] = nullptr; // one-shot
+  }
+
+  /* Host side of the exchange: progress of the host-mediated transports, then completion of the streams. */
+  void finish() {
+    if (!inFlight_) return;
+    stencil::Comm &comm = *dd_.comm_;
+    std::vector<LocalDomain> &doms = dd_.domains_;
     /* 6. host progress loop for the host-mediated transports */
     size_t open = stagedSends_.size() + stagedRecvs_.size() + coloRecvs_.size();
     STENCIL_RANGE("DD::exchange: poll");
@@ -707,6 +760,11 @@ public:
       const char ack = 1;
       comm.send(r.srcRank, ack_tag(r.tagBase), &ack, 1);
     }
+    inFlight_ = false;
+    check_error_word();
+  }
+
+  void check_error_word() const {
     if (*errWord_ != 0) {
       LOG_FATAL("exchange(): timed out waiting for a neighbour's flag (code " << *errWord_ << ", epoch " << epoch_
                                                                              << "); a peer process is gone or stuck");
@@ -921,6 +979,15 @@ void DistributedDomain::swap() {
   }
   if (exchangeStats_) timeSwap_ += comm_->allreduce_max(stencil::Comm::wtime() - t);
 }
+
+void DistributedDomain::exchange_async() { ex_->enqueue(); }
+void DistributedDomain::exchange_wait() { ex_->finish(); }
+bool DistributedDomain::exchange_device_only() const { return ex_->device_only(); }
+cudaEvent_t DistributedDomain::exchange_done_event(size_t i) const {
+  if (!ex_->device_only()) LOG_FATAL("exchange_done_event(): this plan has host-mediated transports; use exchange_wait()");
+  return ex_->done_event(i);
+}
+void DistributedDomain::exchange_after(size_t i, cudaEvent_t e) { ex_->set_after(i, e); }
 
 void DistributedDomain::exchange() {
   double t = 0;

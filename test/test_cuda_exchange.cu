@@ -377,3 +377,62 @@ TEST_CASE("exchange: staged transport over MpiComm, and device-pointer messages 
   REQUIRE(dev.sends == before);
   REQUIRE(aware == 0);
 }
+
+TEST_CASE("exchange_async / exchange_wait and the event-chained form", "[cuda][exchange][async]") {
+  const Radius radius = Radius::constant(2);
+  for (MethodFlags methods : {MethodFlags::All, MethodFlags::CudaMpi, MethodFlags::CudaMemcpyPeer | MethodFlags::CudaMpi}) {
+    DistributedDomain dd(14, 12, 10);
+    dd.set_gpus({0, 0, 0});
+    dd.set_radius(radius);
+    dd.set_methods(methods);
+    dd.set_plan_file(false);
+    Fields q{dd.add_data<float>("f"), dd.add_data<unsigned char>("c"), dd.add_data<double>("d")};
+    (void)q;
+    dd.realize();
+    /* staged messages need the host; direct stores and peer copies do not: device-only is a property of the plan */
+    REQUIRE(dd.exchange_device_only() == (methods != MethodFlags::CudaMpi));
+    for (int round = 0; round < 3; ++round) {
+      fill(dd);
+      dd.exchange_async();
+      dd.exchange_wait();
+      REQUIRE(count_wrong(dd, radius) == 0);
+      dd.swap();
+    }
+    dd.exchange_wait(); // nothing in flight: no-op
+  }
+
+  /* never waiting on the host for the exchange: user streams are chained to it by events in both directions */
+  DistributedDomain dd(16, 12, 12);
+  dd.set_gpus({0, 0});
+  dd.set_radius(radius);
+  dd.set_plan_file(false);
+  Fields q{dd.add_data<float>("f"), dd.add_data<unsigned char>("c"), dd.add_data<double>("d")};
+  (void)q;
+  dd.realize();
+  REQUIRE(dd.exchange_device_only());
+  const size_t nd = dd.domains().size();
+  std::vector<cudaStream_t> user(nd);
+  std::vector<cudaEvent_t> mine(nd);
+  for (size_t di = 0; di < nd; ++di) {
+    CUDA_RUNTIME(cudaSetDevice(dd.domains()[di].gpu()));
+    CUDA_RUNTIME(cudaStreamCreateWithFlags(&user[di], cudaStreamNonBlocking));
+    CUDA_RUNTIME(cudaEventCreateWithFlags(&mine[di], cudaEventDisableTiming));
+  }
+  for (int round = 0; round < 4; ++round) {
+    fill(dd); // synchronous host copies stand in for the user's kernels
+    for (size_t di = 0; di < nd; ++di) {
+      CUDA_RUNTIME(cudaEventRecord(mine[di], user[di]));
+      dd.exchange_after(di, mine[di]);
+    }
+    dd.exchange_async();
+    for (size_t di = 0; di < nd; ++di) CUDA_RUNTIME(cudaStreamWaitEvent(user[di], dd.exchange_done_event(di), 0));
+    for (size_t di = 0; di < nd; ++di) CUDA_RUNTIME(cudaStreamSynchronize(user[di]));
+    REQUIRE(count_wrong(dd, radius) == 0);
+    dd.swap();
+  }
+  dd.exchange_wait();
+  for (size_t di = 0; di < nd; ++di) {
+    cudaStreamDestroy(user[di]);
+    cudaEventDestroy(mine[di]);
+  }
+}
