@@ -51,12 +51,15 @@ inline std::vector<int64_t> prime_factors_desc(int64_t n) {
 
 inline int64_t div_ceil(int64_t n, int64_t d) { return (n + d - 1) / d; }
 
-/* Which axis wins when the split criterion ties (cubic domains tie all the time). The reference always takes x
-   first (partition.hpp:52-58, :183-189 there). x is the contiguous axis: cutting it creates faces made of 4-12 byte
-   row fragments — one DRAM sector and one NVLink packet per row on B200 — and shortens the rows a 128-cell tile has
-   to fill. So the default here is the opposite order, z before y before x; TieBreak::X restores the reference's
-   subdomain grids (also: env STENCIL_PARTITION_TIES=x). */
+/* How the partitioners treat the x axis. The reference takes x first whenever its criterion ties (every cubic domain;
+   partition.hpp:52-58, :183-189 there) and weighs all axes alike. x is the contiguous axis: cutting it creates faces
+   made of 4-24 byte row fragments — one DRAM sector and one NVLink packet per row on B200, measured ~3x the cost per
+   byte of a y or z face (profiles/README.md section 3) — and shortens the rows a 128-cell tile has to fill. Default
+   here (TieBreak::Z): ties go z before y before x, and a cut through x counts kXCutPenalty times its size, so
+   1024^3 on 8 GPUs becomes 1x2x4 boxes of 1024x512x256 (same halo volume as 2x2x2 cubes, no strided face on a link).
+   TieBreak::X restores the reference's subdomain grids (also: env STENCIL_PARTITION_TIES=x). */
 enum class TieBreak { Z, X };
+constexpr int64_t kXCutPenalty = 3;
 inline TieBreak &tie_break_storage() {
   static TieBreak t = [] {
     const char *e = std::getenv("STENCIL_PARTITION_TIES");
@@ -64,8 +67,13 @@ inline TieBreak &tie_break_storage() {
   }();
   return t;
 }
+/* wantLargest: the values are axis lengths and the longest is cut (RankPartition); else they are interface sizes and
+   the smallest is cut (NodePartition) */
 inline int pick_axis(int64_t x, int64_t y, int64_t z, bool wantLargest) {
-  const int64_t v[3] = {wantLargest ? x : -x, wantLargest ? y : -y, wantLargest ? z : -z};
+  const bool b200 = tie_break_storage() == TieBreak::Z;
+  /* compare x/penalty against y, z without division: scale the other two instead */
+  const int64_t px = b200 ? kXCutPenalty : 1;
+  const int64_t v[3] = {wantLargest ? x : -x * px, wantLargest ? y * px : -y, wantLargest ? z * px : -z};
   const int order[2][3] = {{2, 1, 0}, {0, 1, 2}};
   const int *o = order[tie_break_storage() == TieBreak::X ? 1 : 0];
   int best = o[0];

@@ -12,6 +12,7 @@ struct ReferenceTies {
 };
 
 TEST_CASE("rank partition even", "[partition]") {
+  ReferenceTies ties;
   RankPartition p(Dim3(10, 5, 5), 2);
   REQUIRE(p.dim() == Dim3(2, 1, 1));
   REQUIRE(p.subdomain_size(Dim3(0, 0, 0)) == Dim3(5, 5, 5));
@@ -36,6 +37,7 @@ TEST_CASE("rank partition remainders", "[partition]") {
 }
 
 TEST_CASE("rank partition 3x3 origins", "[partition]") {
+  ReferenceTies ties;
   RankPartition p(Dim3(10, 14, 2), 9);
   REQUIRE(p.dim() == Dim3(3, 3, 1));
   REQUIRE(p.subdomain_origin(Dim3(0, 0, 0)) == Dim3(0, 0, 0));
@@ -106,11 +108,18 @@ TEST_CASE("ties cut z before y before x by default, and the reference order on r
   /* a cube on 2, 4, 8 GPUs: the contiguous axis is cut last */
   REQUIRE(NodePartition(Dim3(645, 645, 645), r, 1, 2).dim() == Dim3(1, 1, 2));
   REQUIRE(NodePartition(Dim3(813, 813, 813), r, 1, 4).dim() == Dim3(1, 2, 2));
-  REQUIRE(NodePartition(Dim3(1024, 1024, 1024), r, 1, 8).dim() == Dim3(2, 2, 2));
+  /* a cut through x counts three times its size: 8 GPUs get 1x2x4 boxes (the halo volume of 2x2x2 cubes, whole rows) */
+  REQUIRE(NodePartition(Dim3(1024, 1024, 1024), r, 1, 8).dim() == Dim3(1, 2, 4));
+  REQUIRE(NodePartition(Dim3(1024, 1024, 1024), r, 1, 8).subdomain_size(Dim3(0, 1, 3)) == Dim3(1024, 512, 256));
+  REQUIRE(RankPartition(Dim3(1024, 1024, 1024), 8).dim() == Dim3(1, 2, 4));
+  /* ... but x is still cut when it is the clearly better choice */
+  REQUIRE(NodePartition(Dim3(4096, 256, 256), r, 1, 4).dim() == Dim3(4, 1, 1));
+  REQUIRE(NodePartition(Dim3(1024, 1024, 1024), r, 1, 64).dim() == Dim3(2, 4, 8));
   REQUIRE(RankPartition(Dim3(64, 64, 64), 2).dim() == Dim3(1, 1, 2));
   REQUIRE(RankPartition(Dim3(64, 64, 64), 4).dim() == Dim3(1, 2, 2));
   /* no tie: the criterion decides, whatever the order */
-  REQUIRE(RankPartition(Dim3(100, 64, 64), 2).dim() == Dim3(2, 1, 1));
+  REQUIRE(RankPartition(Dim3(200, 64, 64), 2).dim() == Dim3(2, 1, 1));
+  REQUIRE(RankPartition(Dim3(100, 64, 64), 2).dim() == Dim3(1, 1, 2)); // x is only 1.6x longer: not worth a strided face
   REQUIRE(NodePartition(Dim3(64, 512, 512), r, 1, 2).dim() == Dim3(1, 1, 2)); // y and z tie, x is the worst cut
   REQUIRE(NodePartition(Dim3(512, 512, 64), r, 1, 2).dim() == Dim3(1, 2, 1)); // x and y tie, z is the worst cut
   {

@@ -18,6 +18,7 @@ struct ReferenceTies {
 };
 
 TEST_CASE("trivial placement assigns in linear order", "[placement]") {
+  ReferenceTies ties;
   /* two ranks: 3 GPUs and 1 GPU */
   Trivial t(Dim3(40, 10, 10), std::vector<int>{3, 1}, std::vector<int>{0, 1, 2, 0});
   REQUIRE(t.dim() == Dim3(4, 1, 1));
@@ -33,6 +34,7 @@ TEST_CASE("trivial placement assigns in linear order", "[placement]") {
 }
 
 TEST_CASE("node-aware placement on a uniform NVSwitch box is the identity", "[placement]") {
+  ReferenceTies ties;
   auto uniform = [](int a, int b) { return a == b ? 10.0 : 1.0; };
   NodeAware p(Dim3(512, 512, 512), Radius::constant(3), {{0}}, 8, iota(8), uniform);
   REQUIRE(p.dim() == Dim3(2, 2, 2));
@@ -47,6 +49,7 @@ TEST_CASE("node-aware placement on a uniform NVSwitch box is the identity", "[pl
 }
 
 TEST_CASE("node-aware placement keeps heavy faces on fast links", "[placement]") {
+  ReferenceTies ties;
   /* 4 GPUs in two fast pairs {0,1} and {2,3}. 400x300x8 with face radius 2 splits 2x2x1 (x first, then y) and the
      y faces (200x8) outweigh the x faces (150x8), so in linear order the heavy pairs are (0,2) and (1,3): the
      identity placement would put both on slow links and the solver has to move them. */

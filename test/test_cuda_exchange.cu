@@ -223,6 +223,16 @@ TEST_CASE("exchange: all visible GPUs, direct NVLink stores and the legacy peer 
   }
   std::vector<int> gpus;
   for (int i = 0; i < n; ++i) gpus.push_back(i);
+  {
+    /* the reference's partition cuts x across GPUs: thin strided faces over NVLink (mailboxes + scatter) */
+    const stencil::detail::TieBreak saved = partition_tie_break();
+    set_partition_tie_break(stencil::detail::TieBreak::X);
+    size_t wrong = 0;
+    for (const Radius &r : radius_shapes()) wrong += run_case(Dim3(40, 36, 28), r, MethodFlags::All, gpus, PlacementStrategy::NodeAware);
+    wrong += run_case(Dim3(96, 20, 12), Radius::constant(3), MethodFlags::All, gpus, PlacementStrategy::NodeAware);
+    set_partition_tie_break(saved);
+    REQUIRE(wrong == 0);
+  }
   for (const Radius &r : radius_shapes()) {
     REQUIRE(run_case(Dim3(40, 36, 28), r, MethodFlags::All, gpus, PlacementStrategy::NodeAware) == 0);
     REQUIRE(run_case(Dim3(40, 36, 28), r, MethodFlags::CudaMemcpyPeer | MethodFlags::CudaKernel, gpus, PlacementStrategy::NodeAware) == 0);

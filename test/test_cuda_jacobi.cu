@@ -152,6 +152,14 @@ TEST_CASE("jacobi: every visible GPU, fused NVLink pushes", "[cuda][jacobi][mult
   std::vector<int> gpus;
   for (int i = 0; i < n; ++i) gpus.push_back(i);
   using M = stencil::Jacobi3D::Mode;
+  {
+    /* x cut across GPUs (the reference's partition): per-row sector stores over NVLink */
+    const stencil::detail::TieBreak saved = partition_tie_break();
+    set_partition_tie_break(stencil::detail::TieBreak::X);
+    const size_t bad = mismatches(Dim3(70, 40, 36), M::Fused, gpus, 8, 8);
+    set_partition_tie_break(saved);
+    REQUIRE(bad == 0);
+  }
   REQUIRE(mismatches(Dim3(70, 40, 36), M::Fused, gpus, 8, 8) == 0);
   REQUIRE(mismatches(Dim3(70, 40, 36), M::Overlap, gpus, 4, 8) == 0);
   std::vector<int> twice = gpus;

@@ -17,7 +17,15 @@ def test_version_and_loader(built):
 
 
 def test_rank_partition_matches_reference_cases(built):
-    from stencil2_b200.parallel import RankPartition
+    from stencil2_b200.parallel import RankPartition, set_partition_ties
+    prev = set_partition_ties(True)  # the reference's cases: x is treated like the other axes
+    try:
+        _rank_partition_reference_cases(RankPartition)
+    finally:
+        set_partition_ties(prev)
+
+
+def _rank_partition_reference_cases(RankPartition):
     p = RankPartition((10, 3, 1), 4)
     assert p.dim == (4, 1, 1)
     assert [p.subdomain((i, 0, 0)) for i in range(4)] == [((3, 3, 1), (0, 0, 0)), ((3, 3, 1), (3, 0, 0)), ((2, 3, 1), (6, 0, 0)), ((2, 3, 1), (8, 0, 0))]
@@ -29,8 +37,8 @@ def test_rank_partition_matches_reference_cases(built):
 
 def test_node_partition_baseline_configs(built):
     from stencil2_b200.parallel import NodePartition, set_partition_ties
-    # default: ties cut z, then y, then x (the contiguous axis last)
-    assert NodePartition((1024,) * 3, FACES1, 1, 8).dim == (2, 2, 2)
+    # default: ties cut z, then y, then x (the contiguous axis last), and an x cut counts three times its size
+    assert NodePartition((1024,) * 3, FACES1, 1, 8).dim == (1, 2, 4)
     p2 = NodePartition((645,) * 3, FACES1, 1, 2)
     assert p2.dim == (1, 1, 2) and p2.subdomain((0, 0, 0))[0] == (645, 645, 323) and p2.subdomain((0, 0, 1))[0] == (645, 645, 322)
     p4 = NodePartition((813,) * 3, FACES1, 1, 4)
