@@ -656,7 +656,15 @@ struct Jacobi3D::Impl {
     std::vector<Rect3> exterior;
     Rect3 interior;
     unsigned *doneCounter = nullptr;
-    float *dyn = nullptr; // kDynBytes of run-time parameters (hot, cold, ...)
+    float *dyn = nullptr; // 2 x kDynBytes of run-time parameters (hot, cold, ...): two slots so that an upload for
+                          // the next step never touches what the running kernel reads
+    const float *dynNow = nullptr; // the slot the next launch reads
+    /* step_io(): uploads and read-backs run on their own streams, chained to the kernels by events, so they overlap
+       the neighbouring iterations instead of sitting between two kernels on one stream */
+    RcStream ioIn, ioOut;
+    cudaEvent_t inReady[2] = {nullptr, nullptr}, kernelDone[2] = {nullptr, nullptr}, outDone[2] = {nullptr, nullptr};
+    bool kernelRecorded[2] = {false, false}, outRecorded[2] = {false, false};
+    unsigned ioSteps = 0;
     JacobiParams base[2]; // per parity: src = buffer[parity]
     CUtensorMap tmap[2];  // per parity: the curr buffer as a 3-D tensor (padded row, rows, planes)
     std::vector<int> sameDevDeps;
@@ -743,6 +751,11 @@ Jacobi3D::~Jacobi3D() {
       for (auto &p : d.tilesExterior) cudaFree(p.first);
       cudaFree(d.doneCounter);
       cudaFree(d.dyn);
+      for (int k = 0; k < 2; ++k) {
+        if (d.inReady[k]) cudaEventDestroy(d.inReady[k]);
+        if (d.kernelDone[k]) cudaEventDestroy(d.kernelDone[k]);
+        if (d.outDone[k]) cudaEventDestroy(d.outDone[k]);
+      }
     }
     if (impl_->err) cudaFreeHost(impl_->err);
   }
@@ -819,8 +832,17 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
     CUDA_RUNTIME(cudaMemset(d.doneCounter, 0, sizeof(unsigned)));
     {
       float init[kDynBytes / sizeof(float)] = {1.0f, 0.0f}; // HOT_TEMP, COLD_TEMP of the reference
-      CUDA_RUNTIME(cudaMalloc(&d.dyn, kDynBytes));
+      CUDA_RUNTIME(cudaMalloc(&d.dyn, 2 * kDynBytes));
       CUDA_RUNTIME(cudaMemcpy(d.dyn, init, kDynBytes, cudaMemcpyHostToDevice));
+      CUDA_RUNTIME(cudaMemcpy(d.dyn + kDynBytes / sizeof(float), init, kDynBytes, cudaMemcpyHostToDevice));
+      d.dynNow = d.dyn;
+      d.ioIn = RcStream(ld.gpu());
+      d.ioOut = RcStream(ld.gpu());
+      for (int k = 0; k < 2; ++k) {
+        CUDA_RUNTIME(cudaEventCreateWithFlags(&d.inReady[k], cudaEventDisableTiming));
+        CUDA_RUNTIME(cudaEventCreateWithFlags(&d.kernelDone[k], cudaEventDisableTiming));
+        CUDA_RUNTIME(cudaEventCreateWithFlags(&d.outDone[k], cudaEventDisableTiming));
+      }
     }
 
     const Dim3 sz = ld.size(), org = ld.origin(), pitch = ld.pitch(h_.id());
@@ -978,6 +1000,7 @@ void Jacobi3D::step() {
     P.hiy = int(reg.hi.y - org.y);
     P.hiz = int(reg.hi.z - org.z);
     P.epoch = impl_->iter;
+    P.dyn = d.dynNow;
     if (impl_->useTma) {
       /* the fused variant needs ~100 registers: at 3 CTAs/SM (80 registers) it spills inside the plane loop, and with
          the shared-memory-heavy carve-out those spills miss L1 (measured 4x slower); the plain variant fits in 80 */
@@ -1042,20 +1065,39 @@ void Jacobi3D::step() {
 void Jacobi3D::step_io(const void *paramsPinned, size_t nbytes, float *resultPinned) {
   std::vector<LocalDomain> &doms = dd_->domains();
   if (nbytes > kParamBytes) LOG_FATAL("Jacobi3D::step_io: parameter block larger than " << kParamBytes << " bytes");
-  /* inputs of this step: stream-ordered before the kernels that read them */
+  /* inputs of this step go into the parameter slot the previous step is NOT reading, on the upload stream; the
+     compute stream waits for the upload. The slot was last read two steps ago. */
   for (size_t di = 0; di < doms.size(); ++di) {
     DevGuard g(doms[di].gpu());
-    CUDA_RUNTIME(cudaMemcpyAsync(impl_->doms[di].dyn, paramsPinned, nbytes, cudaMemcpyHostToDevice, impl_->doms[di].stream));
+    Impl::Dom &d = impl_->doms[di];
+    const int slot = int(d.ioSteps & 1u);
+    float *dst = d.dyn + size_t(slot) * (kDynBytes / sizeof(float));
+    if (d.kernelRecorded[slot]) CUDA_RUNTIME(cudaStreamWaitEvent(d.ioIn, d.kernelDone[slot], 0));
+    CUDA_RUNTIME(cudaMemcpyAsync(dst, paramsPinned, nbytes, cudaMemcpyHostToDevice, d.ioIn));
+    CUDA_RUNTIME(cudaEventRecord(d.inReady[slot], d.ioIn));
+    CUDA_RUNTIME(cudaStreamWaitEvent(d.stream, d.inReady[slot], 0));
+    /* this step's kernel overwrites the buffer whose centre cell the read-back of two steps ago copies */
+    if (d.outRecorded[slot]) CUDA_RUNTIME(cudaStreamWaitEvent(d.stream, d.outDone[slot], 0));
+    d.dynNow = dst;
   }
   step();
-  /* result of this step: the new temperature at the centre of every local compute region */
+  /* result of this step: the new temperature at the centre of every local compute region, copied on the read-back
+     stream once this step's kernel is done (the next step only reads that buffer) */
   for (size_t di = 0; di < doms.size(); ++di) {
     LocalDomain &ld = doms[di];
     DevGuard g(ld.gpu());
+    Impl::Dom &d = impl_->doms[di];
+    const int slot = int(d.ioSteps & 1u);
+    CUDA_RUNTIME(cudaEventRecord(d.kernelDone[slot], d.stream));
+    d.kernelRecorded[slot] = true;
+    CUDA_RUNTIME(cudaStreamWaitEvent(d.ioOut, d.kernelDone[slot], 0));
     const Rect3 r = ld.get_compute_region();
     const Dim3 centre((r.lo.x + r.hi.x) / 2, (r.lo.y + r.hi.y) / 2, (r.lo.z + r.hi.z) / 2);
     Accessor<float> acc = ld.get_curr_accessor(h_);
-    CUDA_RUNTIME(cudaMemcpyAsync(resultPinned + di, &acc[centre], sizeof(float), cudaMemcpyDeviceToHost, impl_->doms[di].stream));
+    CUDA_RUNTIME(cudaMemcpyAsync(resultPinned + di, &acc[centre], sizeof(float), cudaMemcpyDeviceToHost, d.ioOut));
+    CUDA_RUNTIME(cudaEventRecord(d.outDone[slot], d.ioOut));
+    d.outRecorded[slot] = true;
+    ++d.ioSteps;
   }
 }
 
@@ -1067,6 +1109,7 @@ void Jacobi3D::sync() {
     /* fused: my halos of the final iteration are complete only when every neighbour raised its last flag */
     if (opt_.mode == Mode::Fused && impl_->iter > 0) launch_wait_flags(d.finalWait, impl_->iter, impl_->err, 5000000000ull, d.stream);
     CUDA_RUNTIME(cudaStreamSynchronize(d.stream));
+    CUDA_RUNTIME(cudaStreamSynchronize(d.ioOut));
   }
   if (*impl_->err) LOG_FATAL("Jacobi3D: timed out waiting for a neighbour (code " << *impl_->err << ", iteration " << impl_->iter << ")");
 }

@@ -166,3 +166,54 @@ TEST_CASE("jacobi: every visible GPU, fused NVLink pushes", "[cuda][jacobi][mult
   twice.insert(twice.end(), gpus.begin(), gpus.end());
   REQUIRE(mismatches(Dim3(70, 40, 36), M::Fused, twice, 8, 8) == 0);
 }
+
+TEST_CASE("jacobi: step_io uploads per-step parameters and reads back per-step results without stalling the loop", "[cuda][jacobi][io]") {
+  const Dim3 size(60, 24, 20);
+  const int iters = 7;
+  for (int nsub : {1, 2}) {
+    stencil::Jacobi3D::Options opt;
+    opt.gpus.assign(size_t(nsub), 0);
+    opt.tileZ = 8;
+    stencil::Jacobi3D j(size_t(size.x), size_t(size.y), size_t(size.z), opt);
+    float *params = nullptr, *results = nullptr;
+    CUDA_RUNTIME(cudaHostAlloc(&params, iters * 2 * sizeof(float), cudaHostAllocDefault));
+    CUDA_RUNTIME(cudaHostAlloc(&results, size_t(iters) * size_t(nsub) * sizeof(float), cudaHostAllocDefault));
+    std::vector<float> ref(size_t(size.flatten()), 0.5f), tmp;
+    std::vector<std::vector<float>> refs;
+    const int64_t R = size.x / 10, hx = size.x / 3, cx = size.x * 2 / 3, cy = size.y / 2, cz = size.z / 2;
+    for (int k = 0; k < iters; ++k) {
+      /* each step has its own slot in pinned memory, so the host may run ahead of the copies */
+      params[2 * k] = 1.0f + 0.25f * float(k);
+      params[2 * k + 1] = -0.5f * float(k);
+      j.step_io(params + 2 * k, 2 * sizeof(float), results + size_t(k) * size_t(nsub));
+      stencil::jacobi_host_step(tmp, ref, size);
+      for (int64_t z = 0; z < size.z; ++z)
+        for (int64_t y = 0; y < size.y; ++y)
+          for (int64_t x = 0; x < size.x; ++x) {
+            const int64_t base = (y - cy) * (y - cy) + (z - cz) * (z - cz);
+            float &v = tmp[size_t((z * size.y + y) * size.x + x)];
+            if (base + (x - hx) * (x - hx) < (R + 1) * (R + 1))
+              v = params[2 * k];
+            else if (base + (x - cx) * (x - cx) < (R + 1) * (R + 1))
+              v = params[2 * k + 1];
+          }
+      ref.swap(tmp);
+      refs.push_back(ref);
+    }
+    const std::vector<float> got = gather(j); // synchronises, read-back stream included
+    size_t bad = 0;
+    for (size_t i = 0; i < got.size(); ++i) bad += std::memcmp(&got[i], &ref[i], 4) != 0;
+    REQUIRE(bad == 0);
+    size_t badResults = 0;
+    for (int k = 0; k < iters; ++k)
+      for (size_t di = 0; di < j.domain().domains().size(); ++di) {
+        const Rect3 r = j.domain().domains()[di].get_compute_region();
+        const Dim3 c((r.lo.x + r.hi.x) / 2, (r.lo.y + r.hi.y) / 2, (r.lo.z + r.hi.z) / 2);
+        const float want = refs[size_t(k)][size_t((c.z * size.y + c.y) * size.x + c.x)];
+        badResults += std::memcmp(&want, &results[size_t(k) * size_t(nsub) + di], 4) != 0;
+      }
+    REQUIRE(badResults == 0);
+    cudaFreeHost(params);
+    cudaFreeHost(results);
+  }
+}
