@@ -7,13 +7,16 @@
 #include "stencil/stencil.hpp"
 
 struct MethodArgs {
-  bool staged = false, colo = false, peer = false, kernel = false, direct = false;
+  bool staged = false, colo = false, peer = false, kernel = false, direct = false, cudaAware = false;
   void add_to(argparse::Parser &p) {
     p.add_flag(kernel, "--kernel")->help("same-GPU copies (CudaKernel)");
     p.add_flag(peer, "--peer")->help("pack + cudaMemcpyPeer (CudaMemcpyPeer)");
     p.add_flag(colo, "--colo")->help("colocated CUDA IPC transport (CudaMpiColocated)");
     p.add_flag(staged, "--staged")->help("host-staged transport (CudaMpi)");
     p.add_flag(direct, "--direct")->help("device-initiated NVLink stores (NvlinkDirect)");
+    /* both spellings of the reference: weak/strong/weak-exchange say --cuda-aware, jacobi3d says --cuda-aware-mpi */
+    p.add_flag(cudaAware, "--cuda-aware")->help("device-pointer messages (CudaAwareMpi; needs a CUDA-aware MPI process group)");
+    p.add_flag(cudaAware, "--cuda-aware-mpi")->help("same as --cuda-aware");
   }
   MethodFlags flags() const {
     MethodFlags m = MethodFlags::None;
@@ -22,6 +25,7 @@ struct MethodArgs {
     if (peer) m |= MethodFlags::CudaMemcpyPeer;
     if (kernel) m |= MethodFlags::CudaKernel;
     if (direct) m |= MethodFlags::NvlinkDirect;
+    if (cudaAware) m |= MethodFlags::CudaAwareMpi;
     return m == MethodFlags::None ? MethodFlags::All : m;
   }
 };

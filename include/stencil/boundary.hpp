@@ -12,6 +12,7 @@ public:
   Boundary() : wraps_(true) {}
   bool &dir(int x, int y, int z) { return wraps_.at_dir(x, y, z); }
   const bool &dir(int x, int y, int z) const { return wraps_.at_dir(x, y, z); }
+  void set_dir(int x, int y, int z, bool wraps) noexcept { wraps_.at_dir(x, y, z) = wraps; } // reference spelling (:18)
   static Boundary periodic() { return Boundary(); }
   static Boundary none() {
     Boundary b;

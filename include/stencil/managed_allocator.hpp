@@ -28,6 +28,8 @@ public:
     }
     return static_cast<T *>(p);
   }
+  /* largest n allocate(n) could be asked for (std allocator requirement kept by the reference, :38) */
+  std::size_t max_size() const noexcept { return static_cast<std::size_t>(-1) / sizeof(T); }
   void deallocate(T *p, std::size_t) noexcept {
     if (p) cudaFree(p);
   }

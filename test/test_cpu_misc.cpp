@@ -3,6 +3,7 @@
 #include <cmath>
 #include <thread>
 #include <unistd.h>
+#include "stencil/boundary.hpp"
 #include "stencil/align.cuh"
 #include "stencil/argparse.hpp"
 #include "stencil/comm.hpp"
@@ -175,4 +176,17 @@ TEST_CASE("node topology from hostnames", "[comm]") {
   MpiTopology self(*c);
   REQUIRE(self.colocated_size() == 1);
   REQUIRE(self.colocated_rank() == 0);
+}
+
+TEST_CASE("boundary flags", "[boundary]") {
+  Boundary b;
+  REQUIRE(b == Boundary::periodic());
+  REQUIRE(b.dir(1, 0, 0));
+  b.set_dir(1, 0, 0, false);
+  b.dir(0, -1, 0) = false;
+  REQUIRE(!b.dir(1, 0, 0));
+  REQUIRE(!b.dir(0, -1, 0));
+  REQUIRE(b.dir(-1, 0, 0));
+  REQUIRE(!(b == Boundary::periodic()));
+  REQUIRE(!Boundary::none().dir(1, 1, 1));
 }

@@ -56,6 +56,8 @@ TEST_CASE("device and managed allocators", "[cuda][allocator]") {
   REQUIRE(attr.type == cudaMemoryTypeDevice);
   REQUIRE(attr.device == 0);
   da.deallocate(p, 100);
+  REQUIRE(da.max_size() == size_t(-1) / sizeof(double));
+  REQUIRE(ManagedAllocator<float>(0).max_size() == size_t(-1) / sizeof(float));
   std::vector<float, ManagedAllocator<float>> v(10, 1.5f, ManagedAllocator<float>(0));
   CUDA_RUNTIME(cudaPointerGetAttributes(&attr, v.data()));
   REQUIRE(attr.type == cudaMemoryTypeManaged);
