@@ -28,6 +28,7 @@ public:
     bool autoSchedule = true;  // let the engine drop the overlap when the TMA kernel is used: thin exterior slabs cannot
                                // fill its tiles, and exchange() + one whole-region launch measured 1.8x faster on B200
     bool freeRunning = true; // without overlap and with device-only transports: exchange_async() + events, the host never waits
+    bool fusedXFaces = true; // subdomains that wrap onto themselves in x: the kernel writes the +-x halos, exchange() skips them
     bool useTma = true; // Star19: TMA + mbarrier pipelined kernel for regions wide enough to fill its tiles
     std::vector<int> gpus;
     double period = 10;

@@ -168,6 +168,12 @@ public:
   bool exchange_device_only() const;
   cudaEvent_t exchange_done_event(size_t i) const;
   void exchange_after(size_t i, cudaEvent_t e);
+  /* For engines whose compute kernel writes the +-x face halo cells of same-GPU neighbours itself (the strided
+     faces are the expensive part of an exchange, and the kernel has those values in registers): leave those messages
+     out of exchange() from now on / put them back. Everything else — other GPUs, edges, corners, y and z faces — is
+     still exchanged. exchange_x_faces_all_local(): true if that covers every +-x face message of this rank. */
+  void exchange_skip_local_x_faces(bool on);
+  bool exchange_x_faces_all_local() const;
 
   /* regions whose stencil does not read halo cells / up to six slabs that do (order +x,+y,+z,-x,-y,-z) */
   std::vector<Rect3> get_interior() const;

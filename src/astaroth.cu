@@ -185,6 +185,8 @@ template <typename T> struct TmaParams {
   int tileZ, tilesX, tilesY, nChunks;
   int tx0, ty0;            // first tile column / row of the region (tile grid is anchored at compute cell 0)
   int x0pad;               // index of compute x = 0 inside a padded row (TMA coordinates start at the row start)
+  int wrapX;               // > 0: the subdomain is its own +-x neighbour and is wrapX cells wide; the kernel then also
+                           // writes its first / last three cells of every row into the opposite x halo of `next`
   T dt;
 };
 
@@ -235,6 +237,20 @@ template <typename T> __global__ void __launch_bounds__(kTThreads, 2) astaroth_t
     const bool in = y >= P.loy && y < P.hiy && x0 < P.hix && x0 + N > P.lox;
     mode[r] = !in ? 0 : ((x0 >= P.lox && x0 + N <= P.hix) ? 1 : 2);
     dp[r] = P.dst[field] + (long long)z0 * P.pitchXY + (long long)y * P.pitchX + x0;
+  }
+  /* Fused x faces (periodic wrap onto this subdomain): the lanes that own cells 0..2 or sx-3..sx-1 store their output
+     vector a second time, sx cells further / earlier in the same row — that is where the opposite halo lives. The extra
+     cells of the vector land in row padding. fp32 vectors are half a 32-byte sector: the other half (padding only) is
+     written as well so that no sector is left partially written. */
+  int qdelta = 0, qwide = 0;
+  if (P.wrapX > 0) {
+    if (x0 < kR) {
+      qdelta = P.wrapX;
+      qwide = (N == 4 && x0 == 0) ? N : 0;
+    } else if (x0 + N > P.wrapX - kR && x0 < P.wrapX) {
+      qdelta = -P.wrapX;
+      qwide = (N == 4 && x0 + N == P.wrapX) ? -N : 0;
+    }
   }
   const T c1 = T(1.5), c2 = T(-0.15), c3 = T(1.0 / 90.0), c0x3 = T(3) * T(-49.0 / 18.0);
   /* pending sums for the planes 1, 2, 3 behind the newest one, and the centres of those planes */
@@ -323,6 +339,10 @@ template <typename T> __global__ void __launch_bounds__(kTThreads, 2) astaroth_t
           V v;
           memcpy(&v, out, sizeof(V));
           *reinterpret_cast<V *>(dp[r]) = v;
+          if (qdelta) {
+            *reinterpret_cast<V *>(dp[r] + qdelta) = v;
+            if (qwide) *reinterpret_cast<V *>(dp[r] + qdelta + qwide) = v; // padding cells: any value will do
+          }
         } else if (mode[r] == 2) {
 #pragma unroll
           for (int i = 0; i < N; ++i)
@@ -359,6 +379,10 @@ struct AstarothSim::Impl {
   double exchangeSeconds = 0;
   /* free-running schedule: no host synchronisation inside the loop (exchange_async + events) */
   bool freeRun = false;
+  /* the kernel writes the +-x halos of `next` itself (subdomains that wrap onto themselves in x) and exchange() leaves
+     those faces out */
+  bool fusedX = false;
+  bool xHalosFromKernel = false; // the previous step's kernel filled the x halos of what is now `curr`
   std::vector<cudaEvent_t> computeDone;
   std::vector<bool> computeRecorded;
 };
@@ -387,6 +411,14 @@ AstarothSim::AstarothSim(size_t x, size_t y, size_t z, const Options &opt) : opt
   }
   if (opt_.autoSchedule && opt_.useTma && opt_.stencil == Stencil::Star19) opt_.overlap = false;
   impl_->freeRun = !opt_.overlap && opt_.freeRunning && dd_->exchange_device_only() && !std::getenv("STENCIL_ASTAROTH_HOST_SYNC");
+  {
+    /* whole-region TMA launches only, every subdomain its own x neighbour, rows that keep the second store aligned */
+    const int n = opt_.fp64 ? TmaGeom<double>::N : TmaGeom<float>::N, tileX = 32 * n;
+    bool ok = !opt_.overlap && opt_.fusedXFaces && opt_.useTma && opt_.stencil == Stencil::Star19 && dd_->subdomain_grid().x == 1 &&
+              dd_->exchange_x_faces_all_local() && !std::getenv("STENCIL_ASTAROTH_NO_FUSED_X");
+    for (LocalDomain &ld : dd_->domains()) ok = ok && ld.size().x % n == 0 && ld.size().x >= tileX / 2 && ld.size().x >= 2 * kR + n && ld.size().y >= kTRows / 2;
+    impl_->fusedX = ok;
+  }
   if (opt_.useTma && opt_.stencil == Stencil::Star19) {
     /* one tensor map per field and buffer: the padded buffer as (row pitch, rows, planes) */
     for (LocalDomain &ld : dd_->domains()) {
@@ -445,6 +477,7 @@ void AstarothSim::init() {
     }
   }
   sync();
+  impl_->xHalosFromKernel = false; // curr was just rewritten: the next exchange carries the x faces again
 }
 
 template <typename T> static void launch_region(AstarothSim::Stencil st, LocalDomain &ld, int fields, const Rect3 &reg, int tileZ, T dt, cudaStream_t stream) {
@@ -480,7 +513,9 @@ template <typename T> static void launch_region(AstarothSim::Stencil st, LocalDo
 }
 
 /* the TMA kernel on a region that is wide enough to fill its tiles */
-template <typename T> static void launch_region_tma(LocalDomain &ld, int fields, const CUtensorMap *maps, const Rect3 &reg, int tileZ, T dt, cudaStream_t stream) {
+template <typename T>
+static void launch_region_tma(LocalDomain &ld, int fields, const CUtensorMap *maps, const Rect3 &reg, int tileZ, T dt, cudaStream_t stream,
+                              bool wrapX = false) {
   typedef TmaGeom<T> G;
   TmaParams<T> P;
   std::memset(&P, 0, sizeof(P));
@@ -504,6 +539,7 @@ template <typename T> static void launch_region_tma(LocalDomain &ld, int fields,
   P.nChunks = (P.hiz - P.loz + tileZ - 1) / tileZ;
   P.x0pad = int(ld.lead_elems(0)) + kR;
   P.dt = dt;
+  P.wrapX = wrapX ? int(ld.size().x) : 0;
   const dim3 grid(unsigned(P.tilesX * P.tilesY * P.nChunks), unsigned(fields), 1);
   astaroth_tma_kernel<T><<<grid, kTThreads, G::smemBytes, stream>>>(P);
   CUDA_RUNTIME(cudaGetLastError());
@@ -520,9 +556,9 @@ void AstarothSim::step() {
     if (opt_.useTma && opt_.stencil == Stencil::Star19 && ext.x >= tileX / 2 && ext.y >= kTRows / 2) {
       const CUtensorMap *maps = impl_->maps[doms[di].parity()][di];
       if (opt_.fp64)
-        launch_region_tma<double>(doms[di], opt_.fields, maps, reg, opt_.tileZ, opt_.dt, impl_->streams[di]);
+        launch_region_tma<double>(doms[di], opt_.fields, maps, reg, opt_.tileZ, opt_.dt, impl_->streams[di], impl_->fusedX);
       else
-        launch_region_tma<float>(doms[di], opt_.fields, maps, reg, opt_.tileZ, float(opt_.dt), impl_->streams[di]);
+        launch_region_tma<float>(doms[di], opt_.fields, maps, reg, opt_.tileZ, float(opt_.dt), impl_->streams[di], impl_->fusedX);
       ++launches_;
       return;
     }
@@ -532,6 +568,9 @@ void AstarothSim::step() {
       launch_region<float>(opt_.stencil, doms[di], opt_.fields, reg, opt_.tileZ, float(opt_.dt), impl_->streams[di]);
     ++launches_;
   };
+  /* x halos of `curr`: written by the previous step's kernel if there was one, else by this exchange */
+  dd_->exchange_skip_local_x_faces(impl_->fusedX && impl_->xHalosFromKernel);
+  impl_->xHalosFromKernel = impl_->fusedX;
   if (impl_->freeRun) {
     /* exchange_async() on the exchange streams, then one whole-region launch per subdomain ordered after it by an
        event; the next exchange is ordered after these launches the same way. The host only enqueues. */

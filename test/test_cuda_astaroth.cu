@@ -65,6 +65,11 @@ TEST_CASE("astaroth: 19-point radius-3 stencil, fp64 and fp32, many fields and s
   REQUIRE(max_abs_err(Dim3(150, 37, 21), S::Star19, true, 2, {0, 0}, true, 3) < 1e-13);
   REQUIRE(max_abs_err(Dim3(150, 37, 21), S::Star19, true, 2, {0, 0}, false, 3) < 1e-13);
   REQUIRE(max_abs_err(Dim3(260, 33, 18), S::Star19, false, 2, {0}, false, 3) < 5e-6);
+  /* subdomains that wrap onto themselves in x: from the second step on the kernel writes the x halos and exchange() skips them */
+  REQUIRE(max_abs_err(Dim3(136, 24, 20), S::Star19, true, 2, {0}, false, 5) < 1e-13);
+  REQUIRE(max_abs_err(Dim3(64, 40, 64), S::Star19, true, 3, {0, 0}, false, 5) < 1e-13);
+  REQUIRE(max_abs_err(Dim3(128, 40, 64), S::Star19, false, 3, {0, 0, 0, 0}, false, 5) < 2e-5);
+  REQUIRE(max_abs_err(Dim3(132, 24, 20), S::Star19, false, 1, {0}, false, 4) < 2e-5);
 }
 
 TEST_CASE("astaroth: all visible GPUs", "[cuda][astaroth][multigpu]") {
