@@ -1,10 +1,8 @@
 #!/bin/bash
 cd /root/repo
 export STENCIL_LOG_LEVEL=1
-timeout 900 ./build/bin/test_cuda "[astaroth]" | tail -6
-timeout 900 ./build/bin/test_cuda "[exchange]" | tail -1
-A="./build/bin/astaroth-sim --x 256 --y 256 --z 256 --fields 8 --double --star --iters 20"
-echo "fused x"; timeout 120 $A 2>/dev/null | tail -1
-echo "no fused x"; STENCIL_ASTAROTH_NO_FUSED_X=1 timeout 120 $A 2>/dev/null | tail -1
-echo "fp32 x4 512^3"; timeout 120 ./build/bin/astaroth-sim --x 512 --y 512 --z 512 --fields 4 --star --iters 10 2>/dev/null | tail -1
-echo "fp32 x4 512^3 no fused x"; STENCIL_ASTAROTH_NO_FUSED_X=1 timeout 120 ./build/bin/astaroth-sim --x 512 --y 512 --z 512 --fields 4 --star --iters 10 2>/dev/null | tail -1
+timeout 900 ./build/bin/test_cuda "[jacobi]" | tail -2
+A="./build/bin/jacobi3d 512 512 512 -n 40 --tile-z 16"
+echo "fast interior path"; timeout 120 $A 2>/dev/null | tail -1
+echo "all tiles through the fused code"; STENCIL_JACOBI_DEBUG_SKIP=8 timeout 120 $A 2>/dev/null | tail -1
+timeout 300 python bench.py --steps 200 --warmup 10 2>/dev/null | tail -1 | python -c "import sys,json; d=json.loads(sys.stdin.read()); print(d['value'], d['ms_per_step'], d['e2e']['value'])"
