@@ -89,6 +89,8 @@ class CopyPlan {
   CopyChunk *dChunks_ = nullptr;
   unsigned *dDone_ = nullptr; // CTA completion counter used by the signalling variant
   int dev_ = -1;
+  std::vector<unsigned char> optional_; // per segment
+  unsigned nRequiredChunks_ = 0;
 
 public:
   CopyPlan() {}
@@ -104,6 +106,8 @@ public:
 
   /* copy box `ext` (elements) from src at srcPos to dst at dstPos; zero-volume boxes are ignored */
   void add(const BoxView &src, const Dim3 &srcPos, const BoxView &dst, const Dim3 &dstPos, const Dim3 &ext);
+  /* same, but launch_and_signal(..., withOptional = false) leaves these boxes out */
+  void add_optional(const BoxView &src, const Dim3 &srcPos, const BoxView &dst, const Dim3 &dstPos, const Dim3 &ext);
   void clear();
 
   size_t num_segments() const { return segs_.size(); }
@@ -119,9 +123,9 @@ public:
   /* one launch on `stream` (a stream of the plan's device); no host synchronisation */
   void launch(int parity, cudaStream_t stream) const;
   /* as launch(), then the last CTA to finish publishes `epoch` to every flag of `sig` (release, system scope) */
-  void launch_and_signal(int parity, const SignalSet &sig, unsigned epoch, cudaStream_t stream) const;
+  void launch_and_signal(int parity, const SignalSet &sig, unsigned epoch, cudaStream_t stream, bool withOptional = true) const;
   /* number of CTAs a launch uses */
-  unsigned grid_size() const;
+  unsigned grid_size(bool withOptional = true) const;
 };
 
 /* Spin (one warp, bounded by timeoutNs) until every flag has reached `epoch` (acquire, system scope). On timeout

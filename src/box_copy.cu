@@ -334,6 +334,8 @@ void CopyPlan::swap(CopyPlan &o) noexcept {
   std::swap(dChunks_, o.dChunks_);
   std::swap(dDone_, o.dDone_);
   std::swap(dev_, o.dev_);
+  optional_.swap(o.optional_);
+  std::swap(nRequiredChunks_, o.nRequiredChunks_);
 }
 
 void CopyPlan::clear() {
@@ -400,13 +402,25 @@ void CopyPlan::add(const BoxView &src, const Dim3 &srcPos, const BoxView &dst, c
   if (ext.x <= 0 || ext.y <= 0 || ext.z <= 0) return;
   const CopySeg s = make_seg(src, srcPos, dst, dstPos, ext);
   segs_.push_back(s);
+  optional_.push_back(0);
   bytes_ += size_t(s.rowBytes) * s.ny * s.nz;
+}
+
+void CopyPlan::add_optional(const BoxView &src, const Dim3 &srcPos, const BoxView &dst, const Dim3 &dstPos, const Dim3 &ext) {
+  const size_t before = segs_.size();
+  add(src, srcPos, dst, dstPos, ext);
+  if (segs_.size() > before) optional_.back() = 1;
 }
 
 void CopyPlan::finalize(int dev, size_t chunkBytes) {
   dev_ = dev;
   chunks_.clear();
+  nRequiredChunks_ = 0;
+  /* chunks of the optional segments go last, so that leaving them out is a shorter chunk table */
+  for (int pass = 0; pass < 2; ++pass) {
+  if (pass == 1) nRequiredChunks_ = unsigned(chunks_.size());
   for (size_t si = 0; si < segs_.size(); ++si) {
+    if (int(optional_[si]) != pass) continue;
     const CopySeg &s = segs_[si];
     /* thin rows cost a sector each way whatever their length: count at least 32 bytes per row when sizing chunks */
     const unsigned per = unsigned(std::min<size_t>(32768, std::max<size_t>(1, chunkBytes / std::max(32u, s.rowBytes))));
@@ -419,6 +433,7 @@ void CopyPlan::finalize(int dev, size_t chunkBytes) {
       for (unsigned z = 0; z < s.nz; z += planesPer)
         chunks_.push_back(CopyChunk{unsigned(si), z, 0, (unsigned short)s.ny, (unsigned short)std::min(planesPer, s.nz - z)});
     }
+  }
   }
   if (segs_.empty()) return;
   int prev = 0;
@@ -437,9 +452,9 @@ void CopyPlan::finalize(int dev, size_t chunkBytes) {
   CUDA_RUNTIME(cudaSetDevice(prev));
 }
 
-unsigned CopyPlan::grid_size() const {
+unsigned CopyPlan::grid_size(bool withOptional) const {
   /* 148 SMs x 8 resident 256-thread CTAs is a full wave on B200; small plans use one CTA per chunk */
-  return unsigned(std::min<size_t>(chunks_.size(), 148 * 8));
+  return unsigned(std::min<size_t>(withOptional ? chunks_.size() : nRequiredChunks_, 148 * 8));
 }
 
 void CopyPlan::launch(int parity, cudaStream_t stream) const {
@@ -450,13 +465,14 @@ void CopyPlan::launch(int parity, cudaStream_t stream) const {
   CUDA_RUNTIME(cudaGetLastError());
 }
 
-void CopyPlan::launch_and_signal(int parity, const SignalSet &sig, unsigned epoch, cudaStream_t stream) const {
-  if (chunks_.empty()) {
+void CopyPlan::launch_and_signal(int parity, const SignalSet &sig, unsigned epoch, cudaStream_t stream, bool withOptional) const {
+  const unsigned n = withOptional ? unsigned(chunks_.size()) : nRequiredChunks_;
+  if (n == 0) {
     /* nothing to move, but neighbours still wait for the flag */
     launch_signal_flags(sig, epoch, stream);
     return;
   }
-  box_copy_kernel<true><<<grid_size(), kThreads, 0, stream>>>(dSegs_, dChunks_, unsigned(chunks_.size()), parity, dDone_, sig, epoch);
+  box_copy_kernel<true><<<grid_size(withOptional), kThreads, 0, stream>>>(dSegs_, dChunks_, n, parity, dDone_, sig, epoch);
   CUDA_RUNTIME(cudaGetLastError());
 }
 

@@ -2,6 +2,7 @@
 #include "stencil/nvtx.hpp"
 #include "stencil/local_domain.cuh"
 
+#include <cstdlib>
 #include <cstring>
 
 #include "stencil/align.cuh"

@@ -96,9 +96,8 @@ class Exchanger {
 
   /* ---- direct push (Kernel + NvlinkDirect) ---- */
   std::vector<CopyPlan> push_;
-  /* the +-x FACE messages that stay on the sender's GPU (wrap onto itself, or an oversubscribed neighbour) are kept in
-     a plan of their own: an engine whose compute kernel writes those halo cells itself (AstarothSim) turns it off */
-  std::vector<CopyPlan> pushXLocal_;
+  /* the +-x FACE messages that stay on the sender's GPU (wrap onto itself, or an oversubscribed neighbour) are optional
+     segments of the push plan: an engine whose compute kernel writes those halo cells itself (AstarothSim) turns them off */
   bool skipXLocal_ = false;
   size_t xFaceMsgs_ = 0, xFaceLocal_ = 0;
   std::vector<CopyPlan> scatter_; // after the flags: my x-side mailboxes -> my halo cells (thin rows from other GPUs)
@@ -380,7 +379,6 @@ public:
     }
 
     push_.resize(nd_);
-    pushXLocal_.resize(nd_);
     scatter_.resize(nd_);
     arriveSig_.assign(nd_, SignalSet{0, {}});
     arriveWait_.assign(nd_, WaitSet{0, {}});
@@ -439,7 +437,7 @@ public:
                   if (nb.dev != me.dev && thin_for_link(dir, ext, dd_.elemSizes_[qi]))
                     push_[di].add(dom.view(qi), srcPos, mailbox_of(nb, dir * -1, qi, ext, me.dev), Dim3(0, 0, 0), ext);
                   else if (nb.dev == me.dev && dir.y == 0 && dir.z == 0)
-                    pushXLocal_[di].add(dom.view(qi), srcPos, view_of(nb, qi, me.dev), dstPos, ext);
+                    push_[di].add_optional(dom.view(qi), srcPos, view_of(nb, qi, me.dev), dstPos, ext);
                   else
                     push_[di].add(dom.view(qi), srcPos, view_of(nb, qi, me.dev), dstPos, ext);
                 }
@@ -485,7 +483,6 @@ public:
           }
       sameDevDeps_[di].assign(depSet.begin(), depSet.end());
       push_[di].finalize(dom.gpu());
-      pushXLocal_[di].finalize(dom.gpu());
       scatter_[di].finalize(dom.gpu());
     }
 
@@ -599,7 +596,7 @@ public:
   bool device_only() const { return stagedSends_.empty() && stagedRecvs_.empty() && coloSends_.empty() && coloRecvs_.empty(); }
   bool in_flight() const { return inFlight_; }
   void skip_local_x_faces(bool on) { skipXLocal_ = on; }
-  bool local_x_faces_only() const { // every +-x face message of every local subdomain is in pushXLocal_
+  bool local_x_faces_only() const { // every +-x face message of every local subdomain is optional
     return xFaceMsgs_ > 0 && xFaceMsgs_ == xFaceLocal_;
   }
   cudaEvent_t done_event(size_t di) const { return exDone_[di]; }
@@ -677,13 +674,12 @@ public:
 
     /* 4. direct pushes: wait for cross-process credits, store into the neighbours' halos, raise their flags */
     for (size_t di = 0; di < nd_; ++di) {
-      if (push_[di].empty() && pushXLocal_[di].empty() && arriveSig_[di].n == 0) continue;
+      if (push_[di].empty() && arriveSig_[di].n == 0) continue;
       STENCIL_RANGE("DD::exchange: direct push");
       DevGuard g(doms[di].gpu());
       launch_wait_flags(readyWait_[di], epoch_, errWord_, timeoutNs_, streams_[di]);
       if (trace_) CUDA_RUNTIME(cudaEventRecord(trA_[di], streams_[di]));
-      if (!skipXLocal_) pushXLocal_[di].launch(doms[di].parity(), streams_[di]);
-      push_[di].launch_and_signal(doms[di].parity(), arriveSig_[di], epoch_, streams_[di]);
+      push_[di].launch_and_signal(doms[di].parity(), arriveSig_[di], epoch_, streams_[di], !skipXLocal_);
       if (trace_) CUDA_RUNTIME(cudaEventRecord(trB_[di], streams_[di]));
       CUDA_RUNTIME(cudaEventRecord(pushDone_[di], streams_[di]));
     }

@@ -1,8 +1,10 @@
 #!/bin/bash
 cd /root/repo
 export STENCIL_LOG_LEVEL=1
-timeout 900 ./build/bin/test_cuda "[jacobi]" | tail -2
-A="./build/bin/jacobi3d 512 512 512 -n 40 --tile-z 16"
-echo "fast interior path"; timeout 120 $A 2>/dev/null | tail -1
-echo "all tiles through the fused code"; STENCIL_JACOBI_DEBUG_SKIP=8 timeout 120 $A 2>/dev/null | tail -1
-timeout 300 python bench.py --steps 200 --warmup 10 2>/dev/null | tail -1 | python -c "import sys,json; d=json.loads(sys.stdin.read()); print(d['value'], d['ms_per_step'], d['e2e']['value'])"
+timeout 900 ./build/bin/test_cuda "[exchange]" | tail -1
+timeout 900 ./build/bin/test_cuda "[astaroth]" | tail -1
+timeout 900 ./build/bin/test_cuda "[jacobi]" | tail -1
+timeout 900 ./build/bin/test_cuda "[pack]" | tail -1
+STENCIL_EXCHANGE_TRACE=5 timeout 120 ./build/bin/weak 512 512 512 6 2>&1 | grep "^exchange" | tail -1
+timeout 120 ./build/bin/weak 512 512 512 30 2>/dev/null | tail -1 | cut -d, -f 20-
+timeout 120 ./build/bin/astaroth-sim --x 256 --y 256 --z 256 --fields 8 --double --star --iters 20 2>/dev/null | tail -1
