@@ -243,13 +243,14 @@ template <typename T> __global__ void __launch_bounds__(kTThreads, 2) astaroth_t
      cells of the vector land in row padding. fp32 vectors are half a 32-byte sector: the other half (padding only) is
      written as well so that no sector is left partially written. */
   int qdelta = 0, qwide = 0;
+  const bool qvec = P.wrapX % N == 0;
   if (P.wrapX > 0) {
     if (x0 < kR) {
       qdelta = P.wrapX;
-      qwide = (N == 4 && x0 == 0) ? N : 0;
+      qwide = (N == 4 && x0 == 0 && qvec) ? N : 0;
     } else if (x0 + N > P.wrapX - kR && x0 < P.wrapX) {
       qdelta = -P.wrapX;
-      qwide = (N == 4 && x0 + N == P.wrapX) ? -N : 0;
+      qwide = (N == 4 && x0 + N == P.wrapX && qvec) ? -N : 0;
     }
   }
   const T c1 = T(1.5), c2 = T(-0.15), c3 = T(1.0 / 90.0), c0x3 = T(3) * T(-49.0 / 18.0);
@@ -340,13 +341,22 @@ template <typename T> __global__ void __launch_bounds__(kTThreads, 2) astaroth_t
           memcpy(&v, out, sizeof(V));
           *reinterpret_cast<V *>(dp[r]) = v;
           if (qdelta) {
-            *reinterpret_cast<V *>(dp[r] + qdelta) = v;
-            if (qwide) *reinterpret_cast<V *>(dp[r] + qdelta + qwide) = v; // padding cells: any value will do
+            if (qvec) {
+              *reinterpret_cast<V *>(dp[r] + qdelta) = v;
+              if (qwide) *reinterpret_cast<V *>(dp[r] + qdelta + qwide) = v; // padding cells: any value will do
+            } else { // row length not a multiple of the vector: element stores, face cells only
+#pragma unroll
+              for (int i = 0; i < N; ++i)
+                if (x0 + i < kR || x0 + i >= P.wrapX - kR) dp[r][qdelta + i] = out[i];
+            }
           }
         } else if (mode[r] == 2) {
 #pragma unroll
           for (int i = 0; i < N; ++i)
-            if (x0 + i >= P.lox && x0 + i < P.hix) dp[r][i] = out[i];
+            if (x0 + i >= P.lox && x0 + i < P.hix) {
+              dp[r][i] = out[i];
+              if (qdelta && (x0 + i < kR || x0 + i >= P.wrapX - kR)) dp[r][qdelta + i] = out[i];
+            }
         }
         dp[r] += P.pitchXY;
       }
@@ -416,7 +426,7 @@ AstarothSim::AstarothSim(size_t x, size_t y, size_t z, const Options &opt) : opt
     const int n = opt_.fp64 ? TmaGeom<double>::N : TmaGeom<float>::N, tileX = 32 * n;
     bool ok = !opt_.overlap && opt_.fusedXFaces && opt_.useTma && opt_.stencil == Stencil::Star19 && dd_->subdomain_grid().x == 1 &&
               dd_->exchange_x_faces_all_local() && !std::getenv("STENCIL_ASTAROTH_NO_FUSED_X");
-    for (LocalDomain &ld : dd_->domains()) ok = ok && ld.size().x % n == 0 && ld.size().x >= tileX / 2 && ld.size().x >= 2 * kR + n && ld.size().y >= kTRows / 2;
+    for (LocalDomain &ld : dd_->domains()) ok = ok && ld.size().x >= tileX / 2 && ld.size().x >= 2 * kR + n && ld.size().y >= kTRows / 2;
     impl_->fusedX = ok;
   }
   if (opt_.useTma && opt_.stencil == Stencil::Star19) {

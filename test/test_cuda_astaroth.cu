@@ -70,6 +70,10 @@ TEST_CASE("astaroth: 19-point radius-3 stencil, fp64 and fp32, many fields and s
   REQUIRE(max_abs_err(Dim3(64, 40, 64), S::Star19, true, 3, {0, 0}, false, 5) < 1e-13);
   REQUIRE(max_abs_err(Dim3(128, 40, 64), S::Star19, false, 3, {0, 0, 0, 0}, false, 5) < 2e-5);
   REQUIRE(max_abs_err(Dim3(132, 24, 20), S::Star19, false, 1, {0}, false, 4) < 2e-5);
+  /* row lengths that are not a multiple of the vector: element stores into the opposite halo */
+  REQUIRE(max_abs_err(Dim3(133, 24, 20), S::Star19, true, 2, {0}, false, 5) < 1e-13);
+  REQUIRE(max_abs_err(Dim3(131, 24, 20), S::Star19, false, 2, {0}, false, 5) < 2e-5);
+  REQUIRE(max_abs_err(Dim3(70, 21, 40), S::Star19, false, 2, {0, 0}, false, 5) < 2e-5);
 }
 
 TEST_CASE("astaroth: all visible GPUs", "[cuda][astaroth][multigpu]") {

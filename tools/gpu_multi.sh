@@ -13,11 +13,11 @@ run() { echo "## $*" >> $O; ( cd /tmp && timeout 600 "$@" 2>/dev/null | tail -6 
 run $ROOT/build/bin/jacobi3d 512 512 512 -n 30 --tile-z 16
 run python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29611 --no-python $ROOT/build/bin/jacobi3d 512 512 512 -n 30 --tile-z 16
 run $ROOT/build/bin/weak 512 512 512 30
-run $ROOT/$R/weak 512 512 512 30 --peer --kernel
+[ -n "$SKIP_REF" ] || run $ROOT/$R/weak 512 512 512 30 --peer --kernel
 run python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29631 --no-python $ROOT/build/bin/weak 512 512 512 30
 run $ROOT/build/bin/astaroth-sim --x 256 --y 256 --z 256 --fields 8 --double --star --iters 10 --weak
 echo "## bench.py under torchrun, $N ranks" >> $O
 timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29621 bench.py --gpus $N --steps 30 --warmup 5 --tile-z 16 > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err; echo "bench rc=$?" >> $O
 echo "## reference, $N GPUs" >> $O
-timeout 1200 python bench.py --impl reference --gpus $N --steps 30 --warmup 5 > gpurun_out/bench_ref_n$N.json 2> gpurun_out/bench_ref_n$N.err; echo "ref rc=$?" >> $O
+[ -n "$SKIP_REF" ] || timeout 1200 python bench.py --impl reference --gpus $N --steps 30 --warmup 5 > gpurun_out/bench_ref_n$N.json 2> gpurun_out/bench_ref_n$N.err; echo "ref rc=$?" >> $O
 cat $O; cat gpurun_out/bench_n$N.json gpurun_out/bench_ref_n$N.json | cut -c1-420; tail -n 3 gpurun_out/bench_n$N.err
