@@ -29,6 +29,8 @@ public:
                                // fill its tiles, and exchange() + one whole-region launch measured 1.8x faster on B200
     bool freeRunning = true; // without overlap and with device-only transports: exchange_async() + events, the host never waits
     bool fusedXFaces = true; // subdomains that wrap onto themselves in x: the kernel writes the +-x halos, exchange() skips them
+    bool fusedYZFaces = true; // ... and pushes its y / z face rows into the neighbours' halos (other GPUs over NVLink, flags as in
+                              // the fused Jacobi kernel): no exchange() left in steady state
     bool useTma = true; // Star19: TMA + mbarrier pipelined kernel for regions wide enough to fill its tiles
     std::vector<int> gpus;
     double period = 10;
@@ -55,6 +57,7 @@ public:
 
 private:
   struct Impl;
+  void setup_fused_faces();
   Options opt_;
   std::unique_ptr<DistributedDomain> dd_;
   std::unique_ptr<Impl> impl_;

@@ -15,7 +15,9 @@
 #include <cmath>
 #include <cstring>
 #include <limits>
+#include <set>
 
+#include "stencil/copy_plan.hpp"
 #include "stencil/detail/tma.cuh"
 
 namespace stencil {
@@ -177,6 +179,118 @@ template <typename T> struct TmaGeom {
   static constexpr int smemBytes = kTStages * stageBytes + 2 * kTStages * 8;
 };
 
+/* Fused y / z face pushes: tiles on a y or z face of the subdomain also store their rows into
+   the neighbour's `next` halo — peer pointers over NVLink, or plain stores when the neighbour shares the GPU — and
+   the kernels of neighbouring GPUs hand-shake through epoch flags exactly as the fused Jacobi kernel does
+   (src/jacobi.cu): boundary CTAs wait for the neighbours' flags of the previous iteration before reading halos,
+   count themselves done after a GPU-scope fence, and the last one raises the neighbours' flags behind one
+   system-scope fence. A 19-point star reads face halos only, so in steady state no exchange() is left. */
+enum PushFace { kYM = 0, kYP = 1, kZM = 2, kZP = 3 };
+constexpr int kFusedFlagBase = 64; // word offset of the fused-iteration flags inside a control block (as in jacobi.cu)
+
+template <typename T> struct PushParams {
+  T *nb[4][kMaxFields];      // my compute cell (x,y,z) on face f lands at nb[f][field] + z*nbPitchXY[f] + y*nbPitchX[f] + x
+  long long nbPitchX[4], nbPitchXY[4];
+  unsigned *nbFlag[4];       // neighbour's flag to raise (nullptr: ordered by streams on one GPU)
+  const unsigned *myFlag[4]; // my flag the neighbour raises
+  unsigned faceMask, flagMask;
+  unsigned nBoundary; // CTAs that take part in the hand-shake
+  unsigned *done, *err;
+  unsigned long long timeoutNs;
+  int sx, sy, sz;
+};
+
+__device__ __forceinline__ void st_flag_sys(unsigned *p, unsigned v) {
+  asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned *p) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+/* Boundary tiles only, after their plane loop: copy the rows of this tile that lie on y / z faces from my `next`
+   buffer (written a moment ago by this CTA) to the matching halo rows of the neighbours' `next` buffers.
+   One warp per row, 16-byte vectors when both sides are aligned. Loads bypass L1 (ld.global.cg). */
+template <typename T>
+__device__ __noinline__ void push_tile_faces(const PushParams<T> &Q, int field, unsigned faces, int xlo, int ylo, int z0, int z1, const T *mine,
+                                             long long pitchX, long long pitchXY) {
+  typedef typename Vec<T>::type V;
+  constexpr int N = Vec<T>::n;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = kTThreads / 32;
+  const int xhi = min(xlo + 32 * N, Q.sx), yhi = min(ylo + kTRows, Q.sy);
+  for (int f = 0; f < 4; ++f) {
+    if (!((faces >> f) & 1u)) continue;
+    int ya = ylo, yb = yhi, za = z0, zb = z1;
+    if (f == kYM) yb = min(yb, kR);
+    if (f == kYP) ya = max(ya, Q.sy - kR);
+    if (f == kZM) zb = min(zb, kR);
+    if (f == kZP) za = max(za, Q.sz - kR);
+    const int ny = yb - ya, rows = ny * (zb - za);
+    T *nb = Q.nb[f][field];
+    const long long npx = Q.nbPitchX[f], npxy = Q.nbPitchXY[f];
+    for (int r = warp; r < rows; r += nwarps) {
+      const int z = za + r / ny, y = ya + r % ny;
+      const T *src = mine + (long long)z * pitchXY + (long long)y * pitchX;
+      T *dst = nb + (long long)z * npxy + (long long)y * npx;
+      const bool vec = ((reinterpret_cast<unsigned long long>(dst + xlo) | reinterpret_cast<unsigned long long>(src + xlo)) & (sizeof(V) - 1)) == 0;
+      if (vec) {
+        const int x = xlo + lane * N;
+        if (x + N <= xhi) {
+          *reinterpret_cast<V *>(dst + x) = __ldcg(reinterpret_cast<const V *>(src + x));
+        } else {
+          for (int i = x; i < xhi; ++i) dst[i] = __ldcg(src + i);
+        }
+      } else {
+        for (int x = xlo + lane; x < xhi; x += 32) dst[x] = __ldcg(src + x);
+      }
+    }
+  }
+}
+
+template <typename T> __device__ __noinline__ void wait_neighbours(const PushParams<T> &Q, unsigned faces, unsigned epoch) {
+  if (threadIdx.x < 4 && ((faces >> threadIdx.x) & 1u)) {
+    const unsigned *f = Q.myFlag[threadIdx.x];
+    if (f) {
+      const unsigned long long t0 = globaltimer_ns();
+      while (int(ld_acquire_sys(f) - (epoch - 1)) < 0) {
+        __nanosleep(64);
+        if (globaltimer_ns() - t0 > Q.timeoutNs) {
+          atomicCAS(Q.err, 0u, 200u + threadIdx.x);
+          break;
+        }
+      }
+    }
+  }
+}
+
+template <typename T> __device__ __noinline__ void signal_neighbours(const PushParams<T> &Q, unsigned epoch) {
+  __threadfence();
+  const unsigned prev = atomicAdd(Q.done, 1u);
+  if (prev == Q.nBoundary - 1) {
+    *Q.done = 0;
+    __threadfence_system();
+    for (int f = 0; f < 4; ++f)
+      if (Q.nbFlag[f]) st_flag_sys(Q.nbFlag[f], epoch);
+  }
+}
+
+/* which y / z faces does tile (ty, z-chunk [z0,z1)) own cells on? (host and device agree through this one function) */
+__host__ __device__ inline unsigned tile_faces(int ty, int z0, int z1, int sy, int sz, unsigned faceMask) {
+  unsigned f = 0;
+  const int ylo = ty * 16, yhi = ylo + 16;
+  if (ylo < kR) f |= 1u << kYM;
+  if (yhi > sy - kR && ylo < sy) f |= 1u << kYP;
+  if (z0 < kR) f |= 1u << kZM;
+  if (z1 > sz - kR) f |= 1u << kZP;
+  return f & faceMask;
+}
+
 template <typename T> struct TmaParams {
   T *dst[kMaxFields];      // compute cell (0,0,0) of next, per field
   const CUtensorMap *maps; // device array: one map per field over the CURRENT curr buffers
@@ -185,6 +299,10 @@ template <typename T> struct TmaParams {
   int tileZ, tilesX, tilesY, nChunks;
   int tx0, ty0;            // first tile column / row of the region (tile grid is anchored at compute cell 0)
   int x0pad;               // index of compute x = 0 inside a padded row (TMA coordinates start at the row start)
+  const PushParams<T> *push; // device pointer, nullptr: no y / z pushes
+  unsigned pushFaceMask, pushFlagMask; // copies of push->faceMask / flagMask (decided before anything is loaded)
+  unsigned epoch;                      // iteration being computed (1-based)
+  int sy, sz;                          // compute extent of the subdomain (for the face tests)
   int wrapX;               // > 0: the subdomain is its own +-x neighbour and is wrapX cells wide; the kernel then also
                            // writes its first / last three cells of every row into the opposite x halo of `next`
   T dt;
@@ -210,9 +328,13 @@ template <typename T> __global__ void __launch_bounds__(kTThreads, 2) astaroth_t
     }
     tma::mbar_fence_init();
   }
+  const int z0 = P.loz + chunk * P.tileZ, z1 = min(z0 + P.tileZ, P.hiz);
+  /* y / z faces this tile pushes to neighbours; tiles that exchange with another GPU first wait for that GPU's flags of
+     the previous iteration (they are the only tiles that read halo cells it wrote) */
+  const unsigned faces = P.push ? tile_faces(ty, z0, z1, P.sy, P.sz, P.pushFaceMask) : 0u;
+  if (faces & P.pushFlagMask) wait_neighbours<T>(*P.push, faces & P.pushFlagMask, P.epoch);
   __syncthreads();
 
-  const int z0 = P.loz + chunk * P.tileZ, z1 = min(z0 + P.tileZ, P.hiz);
   const int nplanes = z1 - z0 + 2 * kR; // input planes z0-3 .. z1+2
   const CUtensorMap *map = P.maps + field;
   const int cx = P.x0pad + tx * G::tileX - kTMargin; // raw x of smem column 0
@@ -362,6 +484,16 @@ template <typename T> __global__ void __launch_bounds__(kTThreads, 2) astaroth_t
       }
     }
   }
+  if (faces) {
+    /* The plane loop above is untouched by the fusion. A boundary tile copies the face rows it has just written
+       (still in L2) into the neighbours' halos here, whole CTA, one warp per row. */
+    __syncthreads();
+    push_tile_faces<T>(*P.push, field, faces, tx * G::tileX, ty * kTRows, z0, z1, P.dst[field], P.pitchX, P.pitchXY);
+    if (faces & P.pushFlagMask) {
+      __syncthreads();
+      if (threadIdx.x == 0) signal_neighbours<T>(*P.push, P.epoch);
+    }
+  }
 }
 
 template <typename T>
@@ -393,9 +525,71 @@ struct AstarothSim::Impl {
      those faces out */
   bool fusedX = false;
   bool xHalosFromKernel = false; // the previous step's kernel filled the x halos of what is now `curr`
+  /* y / z faces pushed by the kernel too (with fusedX: no exchange() left in steady state) */
+  bool fusedYZ = false;
+  struct Push {
+    void *dev[2] = {nullptr, nullptr}; // PushParams<T> per curr parity, in device memory
+    unsigned faceMask = 0, flagMask = 0;
+    unsigned *done = nullptr;
+    std::vector<int> sameDevDeps; // local subdomains on the same GPU that push into me / I push into
+    WaitSet finalWait;
+  };
+  std::vector<Push> push;
+  unsigned iter = 0;       // iterations launched (the epoch published in the flags)
+  unsigned *err = nullptr; // host-mapped error word for flag time-outs
   std::vector<cudaEvent_t> computeDone;
   std::vector<bool> computeRecorded;
 };
+
+namespace {
+const Dim3 kPushDir[4] = {Dim3(0, -1, 0), Dim3(0, 1, 0), Dim3(0, 0, -1), Dim3(0, 0, 1)};
+
+/* one PushParams<T> (device memory) for local subdomain di with `curr` = buffer `parity` */
+template <typename T>
+void *build_push(DistributedDomain &dd, size_t di, int parity, int fields, const NeighborInfo (*nbs)[kMaxFields], unsigned faceMask, unsigned flagMask,
+                 unsigned nBoundary, unsigned *done, unsigned *err) {
+  LocalDomain &ld = dd.domains()[di];
+  PushParams<T> Q;
+  std::memset(&Q, 0, sizeof(Q));
+  const Dim3 sz = ld.size();
+  for (int f = 0; f < 4; ++f) {
+    if (!((faceMask >> f) & 1u)) continue;
+    for (int q = 0; q < fields; ++q) {
+      const NeighborInfo &n = nbs[f][q];
+      const long long npx = n.view.pitchY / (long long)sizeof(T), npxy = n.view.pitchZ / (long long)sizeof(T);
+      T *interior = reinterpret_cast<T *>(n.view.base[parity ^ 1]) + (long long)kR * (npxy + npx + 1); // its NEXT buffer
+      long long shift = 0;
+      switch (f) {
+      case kYM: shift = n.size.y * npx; break;  // my rows 0..2 -> its +y halo
+      case kYP: shift = -sz.y * npx; break;     // my last rows -> its -y halo
+      case kZM: shift = n.size.z * npxy; break;
+      case kZP: shift = -sz.z * npxy; break;
+      }
+      Q.nb[f][q] = interior + shift;
+      Q.nbPitchX[f] = npx;
+      Q.nbPitchXY[f] = npxy;
+    }
+    if ((flagMask >> f) & 1u) {
+      /* I raise the slot "from direction -dir" in the neighbour; the neighbour raises slot "from dir" in me */
+      Q.nbFlag[f] = nbs[f][0].control + kFusedFlagBase + DirectionMap<int>::slot(kPushDir[f] * -1);
+      Q.myFlag[f] = ld.arrive_flags() + kFusedFlagBase + DirectionMap<int>::slot(kPushDir[f]);
+    }
+  }
+  Q.faceMask = faceMask;
+  Q.flagMask = flagMask;
+  Q.nBoundary = nBoundary;
+  Q.done = done;
+  Q.err = err;
+  Q.timeoutNs = 5000000000ull;
+  Q.sx = int(sz.x);
+  Q.sy = int(sz.y);
+  Q.sz = int(sz.z);
+  void *d = nullptr;
+  CUDA_RUNTIME(cudaMalloc(&d, sizeof(Q)));
+  CUDA_RUNTIME(cudaMemcpy(d, &Q, sizeof(Q), cudaMemcpyHostToDevice));
+  return d;
+}
+} // namespace
 
 AstarothSim::AstarothSim(size_t x, size_t y, size_t z, const Options &opt) : opt_(opt) {
   if (opt_.fields < 1 || opt_.fields > kMaxFields) LOG_FATAL("AstarothSim supports 1.." << kMaxFields << " fields");
@@ -429,6 +623,7 @@ AstarothSim::AstarothSim(size_t x, size_t y, size_t z, const Options &opt) : opt
     for (LocalDomain &ld : dd_->domains()) ok = ok && ld.size().x >= tileX / 2 && ld.size().x >= 2 * kR + n && ld.size().y >= kTRows / 2;
     impl_->fusedX = ok;
   }
+  setup_fused_faces();
   if (opt_.useTma && opt_.stencil == Stencil::Star19) {
     /* one tensor map per field and buffer: the padded buffer as (row pitch, rows, planes) */
     for (LocalDomain &ld : dd_->domains()) {
@@ -454,8 +649,76 @@ AstarothSim::AstarothSim(size_t x, size_t y, size_t z, const Options &opt) : opt
   init();
 }
 
+void AstarothSim::setup_fused_faces() {
+  std::vector<LocalDomain> &doms = dd_->domains();
+  impl_->push.resize(doms.size());
+  bool ok = impl_->fusedX && impl_->freeRun && opt_.fusedYZFaces && !std::getenv("STENCIL_ASTAROTH_NO_FUSED_YZ");
+  std::vector<std::vector<NeighborInfo>> all(doms.size()); // [di][f * kMaxFields + q]
+  if (ok)
+    for (size_t di = 0; di < doms.size() && ok; ++di) {
+      all[di].resize(4 * kMaxFields);
+      if (doms[di].size().y < 2 * kR || doms[di].size().z < 2 * kR || opt_.tileZ < kR) ok = false;
+      for (int f = 0; f < 4 && ok; ++f)
+        for (int q = 0; q < opt_.fields; ++q) {
+          const NeighborInfo n = dd_->neighbor(di, kPushDir[f], size_t(q));
+          all[di][size_t(f * kMaxFields + q)] = n;
+          /* every face needs a neighbour we can store into; two processes on one GPU cannot hand-shake by spinning */
+          if (!n.exists || !n.reachable || (n.sameDevice && !n.sameRank) || n.size.x != doms[di].size().x) ok = false;
+        }
+    }
+  ok = dd_->comm().allreduce_sum(ok ? 0 : 1) == 0;
+  impl_->fusedYZ = ok;
+  if (!ok) return;
+  CUDA_RUNTIME(cudaHostAlloc(&impl_->err, sizeof(unsigned), cudaHostAllocMapped | cudaHostAllocPortable));
+  *impl_->err = 0;
+  const int n = opt_.fp64 ? TmaGeom<double>::N : TmaGeom<float>::N, tileX = 32 * n;
+  for (size_t di = 0; di < doms.size(); ++di) {
+    LocalDomain &ld = doms[di];
+    DevGuard g(ld.gpu());
+    Impl::Push &p = impl_->push[di];
+    NeighborInfo nbs[4][kMaxFields];
+    std::set<int> deps;
+    p.finalWait.n = 0;
+    for (int f = 0; f < 4; ++f) {
+      for (int q = 0; q < opt_.fields; ++q) nbs[f][q] = all[di][size_t(f * kMaxFields + q)];
+      const NeighborInfo &nb = nbs[f][0];
+      p.faceMask |= 1u << f;
+      if (!(nb.sameRank && nb.sameDevice)) p.flagMask |= 1u << f;
+      if (nb.sameRank && nb.sameDevice && nb.dom != int(di)) deps.insert(nb.dom);
+    }
+    p.sameDevDeps.assign(deps.begin(), deps.end());
+    /* CTAs of a whole-region launch that take part in the flag hand-shake (same classification as the kernel) */
+    const Dim3 sz = ld.size();
+    const int tilesX = int((sz.x + tileX - 1) / tileX), tilesY = int((sz.y + kTRows - 1) / kTRows);
+    const int nChunks = int((sz.z + opt_.tileZ - 1) / opt_.tileZ);
+    unsigned nBoundary = 0;
+    for (int c = 0; c < nChunks; ++c)
+      for (int ty = 0; ty < tilesY; ++ty) {
+        const int z0 = c * opt_.tileZ, z1 = std::min<int>(z0 + opt_.tileZ, int(sz.z));
+        if (tile_faces(ty, z0, z1, int(sz.y), int(sz.z), p.faceMask) & p.flagMask) nBoundary += unsigned(tilesX * opt_.fields);
+      }
+    CUDA_RUNTIME(cudaMalloc(&p.done, sizeof(unsigned)));
+    CUDA_RUNTIME(cudaMemset(p.done, 0, sizeof(unsigned)));
+    for (int parity = 0; parity < 2; ++parity)
+      p.dev[parity] = opt_.fp64 ? build_push<double>(*dd_, di, parity, opt_.fields, nbs, p.faceMask, p.flagMask, nBoundary, p.done, impl_->err)
+                                : build_push<float>(*dd_, di, parity, opt_.fields, nbs, p.faceMask, p.flagMask, nBoundary, p.done, impl_->err);
+    for (int f = 0; f < 4; ++f)
+      if ((p.flagMask >> f) & 1u) p.finalWait.flag[p.finalWait.n++] = ld.arrive_flags() + kFusedFlagBase + DirectionMap<int>::slot(kPushDir[f]);
+  }
+}
+
 AstarothSim::~AstarothSim() {
   if (dd_) sync();
+  if (impl_ && dd_) {
+    dd_->comm().barrier(); // nobody frees a slab that a neighbour's kernel may still be storing into
+    for (size_t di = 0; di < impl_->push.size(); ++di) {
+      DevGuard g(dd_->domains()[di].gpu());
+      cudaFree(impl_->push[di].dev[0]);
+      cudaFree(impl_->push[di].dev[1]);
+      cudaFree(impl_->push[di].done);
+    }
+    if (impl_->err) cudaFreeHost(impl_->err);
+  }
   if (impl_)
     for (cudaEvent_t e : impl_->computeDone) cudaEventDestroy(e);
   if (impl_ && dd_)
@@ -525,7 +788,7 @@ template <typename T> static void launch_region(AstarothSim::Stencil st, LocalDo
 /* the TMA kernel on a region that is wide enough to fill its tiles */
 template <typename T>
 static void launch_region_tma(LocalDomain &ld, int fields, const CUtensorMap *maps, const Rect3 &reg, int tileZ, T dt, cudaStream_t stream,
-                              bool wrapX = false) {
+                              bool wrapX = false, const void *push = nullptr, unsigned faceMask = 0, unsigned flagMask = 0, unsigned epoch = 0) {
   typedef TmaGeom<T> G;
   TmaParams<T> P;
   std::memset(&P, 0, sizeof(P));
@@ -550,6 +813,12 @@ static void launch_region_tma(LocalDomain &ld, int fields, const CUtensorMap *ma
   P.x0pad = int(ld.lead_elems(0)) + kR;
   P.dt = dt;
   P.wrapX = wrapX ? int(ld.size().x) : 0;
+  P.push = static_cast<const PushParams<T> *>(push);
+  P.pushFaceMask = faceMask;
+  P.pushFlagMask = flagMask;
+  P.epoch = epoch;
+  P.sy = int(ld.size().y);
+  P.sz = int(ld.size().z);
   const dim3 grid(unsigned(P.tilesX * P.tilesY * P.nChunks), unsigned(fields), 1);
   astaroth_tma_kernel<T><<<grid, kTThreads, G::smemBytes, stream>>>(P);
   CUDA_RUNTIME(cudaGetLastError());
@@ -565,10 +834,14 @@ void AstarothSim::step() {
     const int tileX = opt_.fp64 ? TmaGeom<double>::tileX : TmaGeom<float>::tileX;
     if (opt_.useTma && opt_.stencil == Stencil::Star19 && ext.x >= tileX / 2 && ext.y >= kTRows / 2) {
       const CUtensorMap *maps = impl_->maps[doms[di].parity()][di];
+      const void *pushDev = impl_->fusedYZ ? impl_->push[di].dev[doms[di].parity()] : nullptr;
+      const unsigned pushFaces = impl_->fusedYZ ? impl_->push[di].faceMask : 0u, pushFlags = impl_->fusedYZ ? impl_->push[di].flagMask : 0u;
       if (opt_.fp64)
-        launch_region_tma<double>(doms[di], opt_.fields, maps, reg, opt_.tileZ, opt_.dt, impl_->streams[di], impl_->fusedX);
+        launch_region_tma<double>(doms[di], opt_.fields, maps, reg, opt_.tileZ, opt_.dt, impl_->streams[di], impl_->fusedX, pushDev, pushFaces,
+                                  pushFlags, impl_->iter);
       else
-        launch_region_tma<float>(doms[di], opt_.fields, maps, reg, opt_.tileZ, float(opt_.dt), impl_->streams[di], impl_->fusedX);
+        launch_region_tma<float>(doms[di], opt_.fields, maps, reg, opt_.tileZ, float(opt_.dt), impl_->streams[di], impl_->fusedX, pushDev, pushFaces,
+                                 pushFlags, impl_->iter);
       ++launches_;
       return;
     }
@@ -580,16 +853,30 @@ void AstarothSim::step() {
   };
   /* x halos of `curr`: written by the previous step's kernel if there was one, else by this exchange */
   dd_->exchange_skip_local_x_faces(impl_->fusedX && impl_->xHalosFromKernel);
+  const bool steady = impl_->fusedYZ && impl_->xHalosFromKernel; // every halo of `curr` was written by the previous kernels
   impl_->xHalosFromKernel = impl_->fusedX;
+  ++impl_->iter;
   if (impl_->freeRun) {
     /* exchange_async() on the exchange streams, then one whole-region launch per subdomain ordered after it by an
-       event; the next exchange is ordered after these launches the same way. The host only enqueues. */
-    for (size_t di = 0; di < doms.size(); ++di)
-      if (impl_->computeRecorded[di]) dd_->exchange_after(di, impl_->computeDone[di]);
-    dd_->exchange_async();
+       event; the next exchange is ordered after these launches the same way. The host only enqueues.
+       With fused faces there is no exchange at all after the first step: kernels of different GPUs hand-shake through
+       flags, kernels of subdomains that share a GPU are ordered by events. */
+    if (!steady) {
+      for (size_t di = 0; di < doms.size(); ++di)
+        if (impl_->computeRecorded[di]) dd_->exchange_after(di, impl_->computeDone[di]);
+      dd_->exchange_async();
+    }
     for (size_t di = 0; di < doms.size(); ++di) {
       DevGuard g(doms[di].gpu());
-      CUDA_RUNTIME(cudaStreamWaitEvent(impl_->streams[di], dd_->exchange_done_event(di), 0));
+      if (!steady) {
+        CUDA_RUNTIME(cudaStreamWaitEvent(impl_->streams[di], dd_->exchange_done_event(di), 0));
+      } else {
+        for (int dep : impl_->push[di].sameDevDeps)
+          if (impl_->computeRecorded[size_t(dep)]) CUDA_RUNTIME(cudaStreamWaitEvent(impl_->streams[di], impl_->computeDone[size_t(dep)], 0));
+      }
+    }
+    for (size_t di = 0; di < doms.size(); ++di) {
+      DevGuard g(doms[di].gpu());
       launch(di, doms[di].get_compute_region());
       CUDA_RUNTIME(cudaEventRecord(impl_->computeDone[di], impl_->streams[di]));
       impl_->computeRecorded[di] = true;
@@ -615,9 +902,13 @@ void AstarothSim::step() {
 void AstarothSim::sync() {
   for (size_t di = 0; di < dd_->domains().size(); ++di) {
     DevGuard g(dd_->domains()[di].gpu());
+    /* fused faces: my halos of the last iteration are complete only when every neighbour GPU raised its last flag */
+    if (impl_->fusedYZ && impl_->iter > 0 && impl_->xHalosFromKernel)
+      launch_wait_flags(impl_->push[di].finalWait, impl_->iter, impl_->err, 5000000000ull, impl_->streams[di]);
     CUDA_RUNTIME(cudaStreamSynchronize(impl_->streams[di]));
   }
   dd_->exchange_wait(); // no-op unless an asynchronous exchange is still in flight
+  if (impl_->err && *impl_->err) LOG_FATAL("AstarothSim: timed out waiting for a neighbour GPU (code " << *impl_->err << ", iteration " << impl_->iter << ")");
 }
 
 double AstarothSim::run(int iters, double *exchangeSeconds) {

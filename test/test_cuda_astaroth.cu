@@ -74,6 +74,9 @@ TEST_CASE("astaroth: 19-point radius-3 stencil, fp64 and fp32, many fields and s
   REQUIRE(max_abs_err(Dim3(133, 24, 20), S::Star19, true, 2, {0}, false, 5) < 1e-13);
   REQUIRE(max_abs_err(Dim3(131, 24, 20), S::Star19, false, 2, {0}, false, 5) < 2e-5);
   REQUIRE(max_abs_err(Dim3(70, 21, 40), S::Star19, false, 2, {0, 0}, false, 5) < 2e-5);
+  /* several subdomains on one GPU: fused y / z pushes between them ordered by events, 8 steps */
+  REQUIRE(max_abs_err(Dim3(64, 40, 64), S::Star19, true, 2, {0, 0, 0, 0}, false, 8) < 1e-13);
+  REQUIRE(max_abs_err(Dim3(64, 35, 50), S::Star19, true, 2, {0, 0, 0}, false, 8) < 1e-13);
 }
 
 TEST_CASE("astaroth: all visible GPUs", "[cuda][astaroth][multigpu]") {
@@ -88,4 +91,11 @@ TEST_CASE("astaroth: all visible GPUs", "[cuda][astaroth][multigpu]") {
   using S = stencil::AstarothSim::Stencil;
   REQUIRE(max_abs_err(Dim3(60, 40, 36), S::Star19, true, 8, gpus, true, 3) < 1e-13);
   REQUIRE(max_abs_err(Dim3(60, 40, 36), S::Average7, false, 1, gpus, true, 3) == 0);
+  /* no exchange() after the first step: x halos by the kernel's wrap stores, y / z faces pushed to the other GPUs with
+     flag hand-shakes (y and z cuts only: 64-wide rows, 8 iterations so that both buffer parities are reused) */
+  REQUIRE(max_abs_err(Dim3(64, 48, 64), S::Star19, true, 3, gpus, false, 8) < 1e-13);
+  REQUIRE(max_abs_err(Dim3(128, 52, 44), S::Star19, false, 2, gpus, false, 8) < 5e-5);
+  std::vector<int> twice = gpus;
+  twice.insert(twice.end(), gpus.begin(), gpus.end());
+  REQUIRE(max_abs_err(Dim3(66, 48, 64), S::Star19, true, 2, twice, false, 7) < 1e-13);
 }
