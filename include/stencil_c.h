@@ -119,6 +119,16 @@ int stencil_domain_set_gpus(stencil_domain_t *dd, const int *cuda_ids, int n);
 int stencil_domain_set_plan_file(stencil_domain_t *dd, int on);
 int stencil_domain_realize(stencil_domain_t *dd);
 int stencil_domain_exchange(stencil_domain_t *dd);
+/* the two halves of exchange(): enqueue the device work / drive host-mediated transports and wait (see
+   DistributedDomain::exchange_async in stencil/stencil.hpp). When every message travels by device stores or copies
+   (stencil_domain_exchange_device_only() == 1) the host never has to wait: make your stream wait on
+   stencil_domain_exchange_done_event(dd, i) (a cudaEvent_t, NULL otherwise) and hand the event that ends your use of
+   subdomain i to stencil_domain_exchange_after() before the next stencil_domain_exchange_async(). */
+int stencil_domain_exchange_async(stencil_domain_t *dd);
+int stencil_domain_exchange_wait(stencil_domain_t *dd);
+int stencil_domain_exchange_device_only(const stencil_domain_t *dd);
+void *stencil_domain_exchange_done_event(const stencil_domain_t *dd, int subdomain);
+int stencil_domain_exchange_after(stencil_domain_t *dd, int subdomain, void *cuda_event);
 int stencil_domain_swap(stencil_domain_t *dd);
 int stencil_domain_num_subdomains(const stencil_domain_t *dd);
 uint64_t stencil_domain_exchange_bytes(const stencil_domain_t *dd, int methods);

@@ -233,6 +233,26 @@ int stencil_domain_exchange(stencil_domain_t *dd) {
   dd->dd->exchange();
   return 0;
 }
+int stencil_domain_exchange_async(stencil_domain_t *dd) {
+  if (!dd) return -1;
+  dd->dd->exchange_async();
+  return 0;
+}
+int stencil_domain_exchange_wait(stencil_domain_t *dd) {
+  if (!dd) return -1;
+  dd->dd->exchange_wait();
+  return 0;
+}
+int stencil_domain_exchange_device_only(const stencil_domain_t *dd) { return dd ? (dd->dd->exchange_device_only() ? 1 : 0) : -1; }
+void *stencil_domain_exchange_done_event(const stencil_domain_t *dd, int subdomain) {
+  if (!dd || subdomain < 0 || size_t(subdomain) >= dd->dd->domains().size() || !dd->dd->exchange_device_only()) return nullptr;
+  return dd->dd->exchange_done_event(size_t(subdomain));
+}
+int stencil_domain_exchange_after(stencil_domain_t *dd, int subdomain, void *cuda_event) {
+  if (!dd || subdomain < 0 || size_t(subdomain) >= dd->dd->domains().size()) return -1;
+  dd->dd->exchange_after(size_t(subdomain), static_cast<cudaEvent_t>(cuda_event));
+  return 0;
+}
 int stencil_domain_swap(stencil_domain_t *dd) {
   if (!dd) return -1;
   dd->dd->swap();

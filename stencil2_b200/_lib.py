@@ -60,6 +60,11 @@ def _declare(l):
         "stencil_domain_set_plan_file": (i, [vp, i]),
         "stencil_domain_realize": (i, [vp]),
         "stencil_domain_exchange": (i, [vp]),
+        "stencil_domain_exchange_async": (i, [vp]),
+        "stencil_domain_exchange_wait": (i, [vp]),
+        "stencil_domain_exchange_device_only": (i, [vp]),
+        "stencil_domain_exchange_done_event": (vp, [vp, i]),
+        "stencil_domain_exchange_after": (i, [vp, i, vp]),
         "stencil_domain_swap": (i, [vp]),
         "stencil_domain_num_subdomains": (i, [vp]),
         "stencil_domain_exchange_bytes": (u64, [vp, i]),

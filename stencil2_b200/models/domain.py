@@ -115,6 +115,27 @@ class DistributedDomain:
     def exchange(self):
         lib().stencil_domain_exchange(self._h)
 
+    def exchange_async(self):
+        """Enqueue the device work of an exchange and return; pair with exchange_wait()."""
+        lib().stencil_domain_exchange_async(self._h)
+
+    def exchange_wait(self):
+        lib().stencil_domain_exchange_wait(self._h)
+
+    @property
+    def exchange_device_only(self):
+        """True if no message of the plan needs the host (then torch streams can be chained to the exchange by events)."""
+        return lib().stencil_domain_exchange_device_only(self._h) == 1
+
+    def exchange_done_event(self, subdomain=0):
+        """Raw cudaEvent_t (int) recorded at the end of the last exchange_async() on that subdomain's exchange stream,
+        e.g. for torch.cuda.ExternalStream / cudaStreamWaitEvent through cuda-python. None if the plan is not device-only."""
+        return lib().stencil_domain_exchange_done_event(self._h, int(subdomain))
+
+    def exchange_after(self, subdomain, cuda_event):
+        """The next exchange_async() starts after `cuda_event` (raw cudaEvent_t handle, e.g. torch.cuda.Event().cuda_event)."""
+        lib().stencil_domain_exchange_after(self._h, int(subdomain), cuda_event)
+
     def swap(self):
         lib().stencil_domain_swap(self._h)
 

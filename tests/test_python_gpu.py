@@ -47,6 +47,49 @@ def test_astaroth_engine_against_host(built):
             sim.close()
 
 
+def test_exchange_async_chained_to_a_torch_stream(built):
+    """DistributedDomain.exchange_async(): halos of a periodic 2-subdomain field are filled while the host never waits
+    for the exchange; a torch stream is chained to it through the raw CUDA events in both directions."""
+    import torch
+    from stencil2_b200.models import DistributedDomain, Method
+    dd = DistributedDomain(16, 12, 10)
+    dd.set_radius(1)
+    q = dd.add_data(np.float32, "f")
+    dd.set_methods(Method.ALL)
+    dd.set_gpus([0, 0])
+    dd.set_plan_file(False)
+    dd.realize()
+    assert dd.exchange_device_only
+    g = np.arange(16 * 12 * 10, dtype=np.float32).reshape(10, 12, 16)
+    subs = dd.subdomains()
+    for s in subs:
+        (ox, oy, oz), (sx, sy, sz) = s.origin, s.size
+        s.from_host(q, np.full((s.raw_size[2], s.raw_size[1], s.raw_size[0]), -1, np.float32))
+        s.from_host(q, g[oz:oz + sz, oy:oy + sy, ox:ox + sx], pos=(1, 1, 1))
+    stream = torch.cuda.Stream()
+    mine = torch.cuda.Event()
+    for rounds in range(2):
+        mine.record(stream)
+        for s in subs:
+            dd.exchange_after(s.index, mine.cuda_event)
+        dd.exchange_async()
+        for s in subs:
+            ev = dd.exchange_done_event(s.index)
+            assert ev
+            from cuda import cudart
+            (err,) = cudart.cudaStreamWaitEvent(stream.cuda_stream, ev, 0)
+            assert int(err) == 0
+        stream.synchronize()
+        for s in subs:
+            (ox, oy, oz), (sx, sy, sz) = s.origin, s.size
+            got = s.to_host(q, np.float32)
+            zz, yy, xx = np.meshgrid(np.arange(-1, sz + 1), np.arange(-1, sy + 1), np.arange(-1, sx + 1), indexing="ij")
+            want = g[(oz + zz) % 10, (oy + yy) % 12, (ox + xx) % 16]
+            assert np.array_equal(got, want)
+    dd.exchange_wait()
+    dd.close()
+
+
 def test_ops_pack_and_reduce_against_numpy(built):
     import torch
     from stencil2_b200.ops import pack, unpack, reduce_sum_f32
