@@ -322,6 +322,32 @@ __device__ __noinline__ void push_cells(const JacobiParams &P, unsigned faces, i
   }
 }
 
+/* TMA kernel, boundary tiles, after the plane loop: copy the y / z face rows this tile has just written to `next`
+   (still in L2) into the neighbours' halos. Whole CTA, one warp per row, 16-byte vectors. Keeping this out of the plane
+   loop leaves the loop free of face tests and calls. */
+__device__ __noinline__ void push_tile_yz(const JacobiParams &P, unsigned faces, int xlo, int ylo, int z0, int z1) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = kTmaThreads / 32;
+  const int xhi = min(xlo + kTileX, P.sx), yhi = min(ylo + kTmaRows, P.sy);
+  const int x = xlo + lane * kVec;
+  for (int f = YM; f <= ZP; ++f) {
+    if (!((faces >> f) & 1u)) continue;
+    const bool yface = f == YM || f == YP;
+    const int fixed = (f == YM || f == ZM) ? 0 : (yface ? P.sy - 1 : P.sz - 1);
+    /* y face: one row per plane of the tile; z face: the rows of the tile in one plane */
+    const int rows = yface ? z1 - z0 : yhi - ylo;
+    for (int r = warp; r < rows; r += nwarps) {
+      const int y = yface ? fixed : ylo + r, z = yface ? z0 + r : fixed;
+      const float *src = P.dst + (long long)z * P.pitchXY + (long long)y * P.pitchX;
+      float *dst = yface ? P.nb[f] + (long long)z * P.nbPitchXY[f] : P.nb[f] + (long long)y * P.nbPitchX[f];
+      if (x + kVec <= xhi) {
+        *reinterpret_cast<float4 *>(dst + x) = __ldcg(reinterpret_cast<const float4 *>(src + x));
+      } else {
+        for (int i = x; i < xhi; ++i) dst[i] = __ldcg(src + i);
+      }
+    }
+  }
+}
+
 /* store one finished row segment (4 cells at x0.., row y, plane z) locally and, for boundary tiles, into the
    neighbours' halos. Shared by both kernel variants. */
 template <bool FUSED>
@@ -458,14 +484,13 @@ __global__ void __launch_bounds__(kTmaThreads, MINB) jacobi7_tma_kernel(const __
     int qxK = 0;
     int qxMail = -1; // >= 0: this lane's x-face cells go to xstage[qxMail] (and from there to the neighbour's mailbox)
     bool qxWide = false; // the destination halo cell starts (XM) or ends (XP) a 32-byte sector of otherwise unused cells
-    unsigned yzFaces = 0;
+    unsigned yzFaces = 0; // faces pushed from inside the plane loop through push_cells (degenerate narrow rows only)
     if (FUSED && t.faces) {
-      yzFaces = t.faces & ~((1u << XM) | (1u << XP));
-      if (P.debugSkip & 4u) yzFaces = 0;
+      /* y / z faces are copied by push_tile_yz() after the loop */
       const bool ownsXM = !(P.debugSkip & 2u) && (t.faces & (1u << XM)) && x0 == 0;
       const bool ownsXP = !(P.debugSkip & 2u) && (t.faces & (1u << XP)) && x0 <= P.sx - 1 && P.sx - 1 < x0 + kVec;
       if (ownsXM && ownsXP) {
-        yzFaces = t.faces; // a row of at most four cells: both x faces in one lane, take the generic path
+        yzFaces = t.faces & ((1u << XM) | (1u << XP)); // a row of at most four cells: both x faces in one lane, generic path
       } else if (ownsXM || ownsXP) {
         const int f = ownsXM ? XM : XP;
         qxK = ownsXM ? 0 : P.sx - 1 - x0;
@@ -493,9 +518,8 @@ __global__ void __launch_bounds__(kTmaThreads, MINB) jacobi7_tma_kernel(const __
       mode[r] = !in ? 0 : ((x0 >= P.lox && x0 + kVec <= P.hix) ? 1 : 2);
       dp[r] = P.dst + (long long)z0 * P.pitchXY + (long long)y * P.pitchX + x0;
       /* y faces are whole rows of a boundary warp; z faces are handled per plane below */
-      rowPush[r] = FUSED && yzFaces && in && ((yzFaces & 3u) || y == 0 || y == P.sy - 1);
+      rowPush[r] = FUSED && yzFaces && in;
     }
-    const bool zPush = FUSED && (yzFaces & ((1u << ZM) | (1u << ZP)));
     const long long planeStride = P.pitchXY;
     /* Register plan without copies: the centre of plane i is needed again two planes later (as "below"), so two
        register sets alternate (even / odd planes) and the loop is unrolled by two; the in-plane partial sum is
@@ -572,7 +596,7 @@ __global__ void __launch_bounds__(kTmaThreads, MINB) jacobi7_tma_kernel(const __
                 qx[r][(long long)z * qxStride] = v;
               }
             }
-            if (rowPush[r] || (zPush && mode[r] && (z == 0 || z == P.sz - 1))) push_cells(P, yzFaces, x0, y0 + r, z, o[r]);
+            if (rowPush[r]) push_cells(P, yzFaces, x0, y0 + r, z, o[r]);
           }
         }
       }
@@ -598,6 +622,10 @@ __global__ void __launch_bounds__(kTmaThreads, MINB) jacobi7_tma_kernel(const __
 
   if (FUSED && t.faces) {
     __syncthreads();
+    {
+      const unsigned yz = (P.debugSkip & 4u) ? 0u : (t.faces & ~((1u << XM) | (1u << XP)));
+      if (yz && z1 > z0) push_tile_yz(P, yz, t.tx * kTileX, t.ty * kTmaRows, z0, z1);
+    }
     /* x faces bound for another GPU: one 64-byte run (16 rows) per plane instead of one packet per row. NVLink moves a
        roughly fixed number of packets per second, so per-row stores reach a fraction of the link rate. Layout of the
        mailbox: dense [plane][row] of the neighbour's (1, sy, sz) halo box. */
