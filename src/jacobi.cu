@@ -291,37 +291,6 @@ __device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *map, i
   tma::load_3d(dst, map, cx, cy, cz, bar);
 }
 
-struct Cells { // four consecutive x cells of one row
-  float4 v;
-};
-
-/* Boundary tiles only: copy one finished row segment into the neighbours' halos. Deliberately NOT inlined: it runs for
-   a few percent of the rows, and inlining it would make the six peer pointers and pitches live across the whole
-   plane loop (108 registers instead of 72: one CTA less per SM). */
-__device__ __noinline__ void push_cells(const JacobiParams &P, unsigned faces, int x0, int y, int z, float4 o) {
-  const bool full = x0 + kVec <= P.sx;
-  const float ov[4] = {o.x, o.y, o.z, o.w};
-  /* neighbour halo addresses are pre-offset so that (y, z, x) of MY compute coordinates index them directly */
-  auto row_store = [&](float *q) {
-    if (full) {
-      *reinterpret_cast<float4 *>(q) = o;
-    } else {
-#pragma unroll
-      for (int k = 0; k < kVec; ++k)
-        if (x0 + k < P.sx) q[k] = ov[k];
-    }
-  };
-  if ((faces & (1u << YM)) && y == 0) row_store(P.nb[YM] + (long long)z * P.nbPitchXY[YM] + x0);
-  if ((faces & (1u << YP)) && y == P.sy - 1) row_store(P.nb[YP] + (long long)z * P.nbPitchXY[YP] + x0);
-  if ((faces & (1u << ZM)) && z == 0) row_store(P.nb[ZM] + (long long)y * P.nbPitchX[ZM] + x0);
-  if ((faces & (1u << ZP)) && z == P.sz - 1) row_store(P.nb[ZP] + (long long)y * P.nbPitchX[ZP] + x0);
-  if ((faces & (1u << XM)) && x0 == 0) P.nb[XM][(long long)z * P.nbPitchXY[XM] + (long long)y * P.nbPitchX[XM]] = o.x;
-  if ((faces & (1u << XP)) && x0 <= P.sx - 1 && P.sx - 1 < x0 + kVec) {
-    const int k = P.sx - 1 - x0; // which of my four cells is the last one of the row
-    P.nb[XP][(long long)z * P.nbPitchXY[XP] + (long long)y * P.nbPitchX[XP]] = k == 0 ? o.x : (k == 1 ? o.y : (k == 2 ? o.z : o.w));
-  }
-}
-
 /* TMA kernel, boundary tiles, after the plane loop: copy the y / z face rows this tile has just written to `next`
    (still in L2) into the neighbours' halos. Whole CTA, one warp per row, 16-byte vectors. Keeping this out of the plane
    loop leaves the loop free of face tests and calls. */
@@ -348,25 +317,39 @@ __device__ __noinline__ void push_tile_yz(const JacobiParams &P, unsigned faces,
   }
 }
 
-/* store one finished row segment (4 cells at x0.., row y, plane z) locally and, for boundary tiles, into the
-   neighbours' halos. Shared by both kernel variants. */
-template <bool FUSED>
-__device__ __forceinline__ void store_cells(const JacobiParams &P, const Tile &t, int x0, int y, int z, float4 o) {
-  if (!(y >= P.loy && y < P.hiy && x0 < P.hix && x0 + kVec > P.lox)) return;
-  const bool full = x0 >= P.lox && x0 + kVec <= P.hix;
-  float *dp = P.dst + (long long)z * P.pitchXY + (long long)y * P.pitchX + x0;
-  if (full) {
-    *reinterpret_cast<float4 *>(dp) = o;
-  } else {
-    const float ov[4] = {o.x, o.y, o.z, o.w};
-#pragma unroll
-    for (int k = 0; k < kVec; ++k)
-      if (x0 + k >= P.lox && x0 + k < P.hix) dp[k] = ov[k];
-  }
-  if (FUSED && t.faces) {
-    /* does this row segment touch any face at all? (cheap, mostly false even inside boundary tiles) */
-    const bool onFace = y == 0 || y == P.sy - 1 || z == 0 || z == P.sz - 1 || x0 == 0 || (x0 <= P.sx - 1 && P.sx - 1 < x0 + kVec);
-    if (onFace) push_cells(P, t.faces, x0, y, z, o);
+/* ... and the x faces: one cell per row of the tile, so one cell per thread (16 rows x 16 planes). The value is read
+   back from `next` (L2) and goes either into the neighbour's halo cell — as a whole 32-byte sector where the halo cell
+   shares its sector with row padding only (LocalDomain layout), because a 4-byte store would make the receiver's
+   memory system read-modify-write the sector — or, for a neighbour on another GPU in mailbox mode, into its dense
+   [plane][row] mailbox (64-byte runs instead of one NVLink packet per row). */
+__device__ __noinline__ void push_tile_x(const JacobiParams &P, unsigned faces, int ylo, int z0, int z1) {
+  const int n = (z1 - z0) * kTmaRows;
+  for (int f = XM; f <= XP; ++f) {
+    if (!((faces >> f) & 1u)) continue;
+    const int x = f == XM ? 0 : P.sx - 1;
+    /* start of the sector holding the destination halo cell: my x=0 lands in the neighbour's +x halo, the first cell
+       after its interior (sector = halo + 7 padding cells); my last x lands in its -x halo, the last cell before its
+       128-byte aligned interior (sector = 7 padding cells + halo) */
+    const long long sectorShift = f == XM ? 0 : -7;
+    const bool wide = ((reinterpret_cast<unsigned long long>(P.nb[f] + sectorShift) | (unsigned long long)(P.nbPitchX[f] * 4) |
+                        (unsigned long long)(P.nbPitchXY[f] * 4)) & 31ull) == 0;
+    for (int i = threadIdx.x; i < n; i += kTmaThreads) {
+      const int z = z0 + i / kTmaRows, y = ylo + i % kTmaRows;
+      if (y >= P.sy) continue;
+      const float v = __ldcg(P.dst + (long long)z * P.pitchXY + (long long)y * P.pitchX + x);
+      if (P.mbox[f]) {
+        P.mbox[f][(long long)z * P.sy + y] = v;
+      } else {
+        float *q = P.nb[f] + (long long)z * P.nbPitchXY[f] + (long long)y * P.nbPitchX[f];
+        if (wide) {
+          const float4 vv = make_float4(v, v, v, v);
+          reinterpret_cast<float4 *>(q + sectorShift)[0] = vv;
+          reinterpret_cast<float4 *>(q + sectorShift)[1] = vv;
+        } else { // neighbour's x extent is not a multiple of 8 cells: interior cells share the sector
+          *q = v;
+        }
+      }
+    }
   }
 }
 
@@ -436,8 +419,6 @@ __device__ __noinline__ void store_partial(const JacobiParams &P, float *dp, int
 template <bool FUSED, int MINB>
 __global__ void __launch_bounds__(kTmaThreads, MINB) jacobi7_tma_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ JacobiParams P) {
   extern __shared__ __align__(128) unsigned char smem[];
-  /* x-face values of this tile on their way to another GPU's mailbox: [face][plane of the tile][row] */
-  __shared__ float xstage[FUSED ? 2 : 1][FUSED ? kMaxTileZ : 1][kTmaRows];
   unsigned long long *full = reinterpret_cast<unsigned long long *>(smem + kTmaStages * kTmaStageBytes);
   unsigned long long *empty = full + kTmaStages;
   const Tile t = P.tiles[blockIdx.x];
@@ -476,49 +457,19 @@ __global__ void __launch_bounds__(kTmaThreads, MINB) jacobi7_tma_kernel(const __
     const int x0 = t.tx * kTileX + lane * kVec;
     const int y0 = t.ty * kTmaRows + r0;
     const bool nearSphere = tile_near_sphere(P, t, kTmaRows, z0, z1);
-    /* x faces: exactly one lane of a boundary warp owns the face cell of a row. Its destination pointer (row part) is
-       set up once; per plane the store is a single predicated STG — no call, no divergence worth mentioning.
-       y / z faces are whole-row vector stores and go through push_cells under a warp-uniform condition. */
-    float *qx[2] = {nullptr, nullptr};
-    long long qxStride = 0;
-    int qxK = 0;
-    int qxMail = -1; // >= 0: this lane's x-face cells go to xstage[qxMail] (and from there to the neighbour's mailbox)
-    bool qxWide = false; // the destination halo cell starts (XM) or ends (XP) a 32-byte sector of otherwise unused cells
-    unsigned yzFaces = 0; // faces pushed from inside the plane loop through push_cells (degenerate narrow rows only)
-    if (FUSED && t.faces) {
-      /* y / z faces are copied by push_tile_yz() after the loop */
-      const bool ownsXM = !(P.debugSkip & 2u) && (t.faces & (1u << XM)) && x0 == 0;
-      const bool ownsXP = !(P.debugSkip & 2u) && (t.faces & (1u << XP)) && x0 <= P.sx - 1 && P.sx - 1 < x0 + kVec;
-      if (ownsXM && ownsXP) {
-        yzFaces = t.faces & ((1u << XM) | (1u << XP)); // a row of at most four cells: both x faces in one lane, generic path
-      } else if (ownsXM || ownsXP) {
-        const int f = ownsXM ? XM : XP;
-        qxK = ownsXM ? 0 : P.sx - 1 - x0;
-        if (P.mbox[f]) qxMail = f;
-        qxStride = P.nbPitchXY[f];
-        /* start of the 32-byte sector holding the destination halo cell: my x=0 lands in the neighbour's +x halo, the
-           first cell after its interior (sector = halo + 7 padding cells); my last x lands in its -x halo, the last
-           cell before its 128-byte aligned interior (sector = 7 padding cells + halo) */
-        const long long sectorShift = ownsXM ? 0 : -7;
-        qxWide = ((reinterpret_cast<unsigned long long>(P.nb[f] + sectorShift) | (unsigned long long)(P.nbPitchX[f] * 4)) & 31ull) == 0;
-        for (int r = 0; r < 2; ++r)
-          if (y0 + r < P.sy) qx[r] = P.nb[f] + (long long)(y0 + r) * P.nbPitchX[f] + (qxWide ? sectorShift : 0);
-      }
-    }
+    /* Nothing of the fusion lives in the plane loop: face cells are copied to the neighbours by push_tile_yz() and
+       push_tile_x() after it, from what this tile has just written to `next` (still in L2). */
     /* Everything that does not change from plane to plane is decided here, so the plane loop is loads, adds and one
        store per row: where this lane's rows go (running pointers, advanced by one plane per iteration), whether the
        store is a full vector, and whether this lane has anything to push at all. */
     float *dp[2];
     int mode[2]; // 0: nothing to store, 1: full 16-byte store, 2: partial row segment (region edge)
-    bool rowPush[2];
 #pragma unroll
     for (int r = 0; r < 2; ++r) {
       const int y = y0 + r;
       const bool in = y >= P.loy && y < P.hiy && x0 < P.hix && x0 + kVec > P.lox;
       mode[r] = !in ? 0 : ((x0 >= P.lox && x0 + kVec <= P.hix) ? 1 : 2);
       dp[r] = P.dst + (long long)z0 * P.pitchXY + (long long)y * P.pitchX + x0;
-      /* y faces are whole rows of a boundary warp; z faces are handled per plane below */
-      rowPush[r] = FUSED && yzFaces && in;
     }
     const long long planeStride = P.pitchXY;
     /* Register plan without copies: the centre of plane i is needed again two planes later (as "below"), so two
@@ -578,27 +529,6 @@ __global__ void __launch_bounds__(kTmaThreads, MINB) jacobi7_tma_kernel(const __
             store_partial(P, dp[r], x0, o[r]);
           dp[r] += planeStride;
         }
-        if (FUSED && t.faces) {
-#pragma unroll
-          for (int r = 0; r < 2; ++r) {
-            if (qxMail >= 0) {
-              xstage[qxMail][z - z0][r0 + r] = qxK == 0 ? o[r].x : (qxK == 1 ? o[r].y : (qxK == 2 ? o[r].z : o[r].w));
-            } else if (qx[r]) {
-              /* The halo cell shares its 32-byte sector with row padding only (LocalDomain layout), so the whole
-                 sector is written: a 4-byte store would make the receiver's memory system read-modify-write it. */
-              const float v = qxK == 0 ? o[r].x : (qxK == 1 ? o[r].y : (qxK == 2 ? o[r].z : o[r].w));
-              if (qxWide) {
-                float4 *q = reinterpret_cast<float4 *>(qx[r] + (long long)z * qxStride);
-                const float4 vv = make_float4(v, v, v, v);
-                q[0] = vv;
-                q[1] = vv;
-              } else { // neighbour's x extent is not a multiple of 8 cells: interior cells share the sector
-                qx[r][(long long)z * qxStride] = v;
-              }
-            }
-            if (rowPush[r]) push_cells(P, yzFaces, x0, y0 + r, z, o[r]);
-          }
-        }
       }
       below[0] = c0;
       below[1] = c1;
@@ -626,17 +556,7 @@ __global__ void __launch_bounds__(kTmaThreads, MINB) jacobi7_tma_kernel(const __
       const unsigned yz = (P.debugSkip & 4u) ? 0u : (t.faces & ~((1u << XM) | (1u << XP)));
       if (yz && z1 > z0) push_tile_yz(P, yz, t.tx * kTileX, t.ty * kTmaRows, z0, z1);
     }
-    /* x faces bound for another GPU: one 64-byte run (16 rows) per plane instead of one packet per row. NVLink moves a
-       roughly fixed number of packets per second, so per-row stores reach a fraction of the link rate. Layout of the
-       mailbox: dense [plane][row] of the neighbour's (1, sy, sz) halo box. */
-    for (int f = 0; f < 2; ++f) {
-      if (!((t.faces >> f) & 1u) || !P.mbox[f]) continue;
-      const int ybase = t.ty * kTmaRows, nz = z1 - z0;
-      for (int i = threadIdx.x; i < nz * kTmaRows; i += kTmaThreads) {
-        const int zl = i / kTmaRows, r = i % kTmaRows;
-        if (ybase + r < P.sy) P.mbox[f][(long long)(z0 + zl) * P.sy + ybase + r] = xstage[f][zl][r];
-      }
-    }
+    if (!(P.debugSkip & 2u) && (t.faces & ((1u << XM) | (1u << XP))) && z1 > z0) push_tile_x(P, t.faces, t.ty * kTmaRows, z0, z1);
     /* only tiles that stored into ANOTHER GPU take part in the completion count (same-GPU neighbours are ordered by
        the stream, or are this very kernel when an axis wraps onto the subdomain itself) */
     if ((t.faces & P.flagMask) && !(P.debugSkip & 1u)) {
