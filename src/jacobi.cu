@@ -19,10 +19,12 @@
    128-byte boundaries (LocalDomain layout), so every vector access is aligned and a warp reads whole cache lines.
    HBM traffic is one read + one write of the field per iteration; the +-y / +-z re-reads are served by L1/L2.
 
-   Fusion. Tiles that own cells on a subdomain face additionally store those cells into the neighbour's `next`
-   halo (peer pointer: NVLink store, or a plain local store when the axis wraps onto the same subdomain) —
-   16-byte vectors for y and z faces, one whole 32-byte sector per row (halo cell + row padding) for x faces. Tiles
-   that stored into ANOTHER GPU finish with a GPU-scope fence + a counter increment; the last of them issues one
+   Fusion. Tiles that own cells on a subdomain face additionally put those cells into the neighbour's `next` halo
+   (peer pointer: NVLink store, or a plain local store when the axis wraps onto the same subdomain) — 16-byte vectors
+   for y and z faces, one whole 32-byte sector per row (halo cell + row padding) for x faces. In the TMA kernel this
+   is an epilogue of the tile: the plane loop is the plain kernel's loop, and the face cells are read back from `next`
+   (they are still in L2) once the loop is done; the LDG variant stores them from registers as it goes. Tiles that
+   stored into ANOTHER GPU finish with a GPU-scope fence + a counter increment; the last of them issues one
    system-scope fence and writes the iteration number to every such neighbour's flag. At the start of the next
    iteration only those tiles look at the flags (ld.acquire.sys): they are the only ones that read halo cells written
    by another GPU, and their neighbours' flags were raised well before the previous kernel ended, so in steady state
