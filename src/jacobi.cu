@@ -54,7 +54,15 @@ constexpr int kMaxTileZ = 64; // bound on Options::tileZ for the TMA variant (si
 constexpr int kTmaLag = 2; // the producer refills the slot that was consumed kTmaLag planes ago
 constexpr int kTmaPlaneBytes = kTmaBoxX * kTmaBoxY * 4;
 constexpr int kTmaStageBytes = (kTmaPlaneBytes + 127) / 128 * 128;
-constexpr int kTmaSmemBytes = kTmaStages * kTmaStageBytes + 2 * kTmaStages * 8;
+/* Subdomains that wrap onto themselves in x (always, with the default partition) do not keep x halo cells at all in
+   fused mode: a tile at the left / right end of the rows loads the four cells at the OTHER end of its rows with a
+   second, tiny TMA box per plane (4 x 16 floats) and takes its x = -1 / x = sx neighbour from there. The far-end cells
+   are being read by the tile at that end at about the same time, so this is an L2 hit; it replaces one 32-byte
+   sector store per row and its read-back. */
+constexpr int kSideBoxX = 4, kSideBytes = kSideBoxX * kTmaRows * 4; // 256 B per side and stage
+constexpr int kTmaSideOffset = kTmaStages * kTmaStageBytes;
+constexpr int kTmaBarOffset = kTmaSideOffset + 2 * kTmaStages * kSideBytes;
+constexpr int kTmaSmemBytes = kTmaBarOffset + 2 * kTmaStages * 8;
 constexpr size_t kDynBytes = Jacobi3D::kParamBytes;
 constexpr int kFusedFlagBase = 64; // word offset of the fused-iteration flags inside a control block
 
@@ -71,6 +79,7 @@ struct JacobiParams {
   int sx, sy, sz;            // compute-region size
   int lox, loy, loz, hix, hiy, hiz; // cells to update (compute coordinates, half open)
   int tileZ;
+  int wrapLoad;       // fused mode, subdomain is its own +-x neighbour: x neighbours across the wrap come from side TMA boxes
   unsigned debugSkip; // diagnostics only (STENCIL_JACOBI_DEBUG_SKIP): 1 no signal, 2 no x push, 4 no y/z push
   int tmaX0; // index of compute cell x=0 inside a padded row (TMA coordinates count from the row start)
   /* Dirichlet spheres in global coordinates */
@@ -419,9 +428,10 @@ __device__ __noinline__ void store_partial(const JacobiParams &P, float *dp, int
 }
 
 template <bool FUSED, int MINB>
-__global__ void __launch_bounds__(kTmaThreads, MINB) jacobi7_tma_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ JacobiParams P) {
+__global__ void __launch_bounds__(kTmaThreads, MINB)
+    jacobi7_tma_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmapSide, const __grid_constant__ JacobiParams P) {
   extern __shared__ __align__(128) unsigned char smem[];
-  unsigned long long *full = reinterpret_cast<unsigned long long *>(smem + kTmaStages * kTmaStageBytes);
+  unsigned long long *full = reinterpret_cast<unsigned long long *>(smem + kTmaBarOffset);
   unsigned long long *empty = full + kTmaStages;
   const Tile t = P.tiles[blockIdx.x];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -445,11 +455,19 @@ __global__ void __launch_bounds__(kTmaThreads, MINB) jacobi7_tma_kernel(const __
      `empty` barrier is almost always already satisfied. */
   const int cx = P.tmaX0 + t.tx * kTileX - 4; // 4 cells of left margin keep the centre 16-byte aligned in smem
   const int cy = t.ty * kTmaRows;             // raw row of compute row (ty*rows - 1)
+  /* x wrap by load: does this tile hold the first / the last cell of the rows? */
+  const bool sideL = FUSED && P.wrapLoad && t.tx == 0;
+  const bool sideR = FUSED && P.wrapLoad && (int(t.tx) + 1) * kTileX >= P.sx;
   auto issue = [&](int j) {                   // load input plane j (compute plane z0 - 1 + j, raw plane z0 + j)
     const int sj = j % kTmaStages;
     if (j >= kTmaStages) mbar_wait(&empty[sj], ((j / kTmaStages) - 1) & 1);
-    mbar_arrive_expect_tx(&full[sj], kTmaPlaneBytes);
+    mbar_arrive_expect_tx(&full[sj], kTmaPlaneBytes + (sideL ? kSideBytes : 0) + (sideR ? kSideBytes : 0));
     tma_load_3d(smem + sj * kTmaStageBytes, &tmap, cx, cy, z0 + j, &full[sj]);
+    /* side boxes: rows ty*16 .. +15 (raw row cy + 1); left tiles want the aligned group of four cells that holds cell
+       sx-1 (a TMA box must start on a 16-byte boundary: an unaligned start is an illegal instruction), right tiles
+       cells 0 .. 3 */
+    if (sideL) tma_load_3d(smem + kTmaSideOffset + sj * kSideBytes, &tmapSide, P.tmaX0 + ((P.sx - 1) & ~3), cy + 1, z0 + j, &full[sj]);
+    if (sideR) tma_load_3d(smem + kTmaSideOffset + (kTmaStages + sj) * kSideBytes, &tmapSide, P.tmaX0, cy + 1, z0 + j, &full[sj]);
   };
   if (threadIdx.x == 0)
     for (int j = 0; j < kTmaStages - kTmaLag && j < nplanes; ++j) issue(j);
@@ -459,6 +477,9 @@ __global__ void __launch_bounds__(kTmaThreads, MINB) jacobi7_tma_kernel(const __
     const int x0 = t.tx * kTileX + lane * kVec;
     const int y0 = t.ty * kTmaRows + r0;
     const bool nearSphere = tile_near_sphere(P, t, kTmaRows, z0, z1);
+    /* x wrap by load: which lane's vector holds cell x = sx (patchK = its index there), or is it lane 31's east read? */
+    const int patchK = (sideR && x0 <= P.sx && P.sx < x0 + kVec) ? P.sx - x0 : -1;
+    const bool eSide = sideR && x0 + kVec == P.sx;
     /* Nothing of the fusion lives in the plane loop: face cells are copied to the neighbours by push_tile_yz() and
        push_tile_x() after it, from what this tile has just written to `next` (still in L2). */
     /* Everything that does not change from plane to plane is decided here, so the plane loop is loads, adds and one
@@ -486,19 +507,28 @@ __global__ void __launch_bounds__(kTmaThreads, MINB) jacobi7_tma_kernel(const __
       const float *pl = reinterpret_cast<const float *>(smem + s * kTmaStageBytes);
       /* smem row j holds compute row ty*rows + j - 1; smem column 4 + k holds compute x = tx*128 + k */
       const float *rowC0 = pl + (r0 + 1) * kTmaBoxX + 4 + lane * kVec;
-      const float4 c0 = *reinterpret_cast<const float4 *>(rowC0);
-      const float4 c1 = *reinterpret_cast<const float4 *>(rowC0 + kTmaBoxX);
+      float4 c0 = *reinterpret_cast<const float4 *>(rowC0);
+      float4 c1 = *reinterpret_cast<const float4 *>(rowC0 + kTmaBoxX);
+      const float *sL = reinterpret_cast<const float *>(smem + kTmaSideOffset + s * kSideBytes) + r0 * kSideBoxX;
+      const float *sR = reinterpret_cast<const float *>(smem + kTmaSideOffset + (kTmaStages + s) * kSideBytes) + r0 * kSideBoxX;
+      if (patchK >= 0) { // my vector contains cell x = sx: it is cell 0 of the row
+        const float v0 = sR[0], v1 = sR[kSideBoxX];
+        if (patchK == 0) c0.x = v0, c1.x = v1;
+        else if (patchK == 1) c0.y = v0, c1.y = v1;
+        else if (patchK == 2) c0.z = v0, c1.z = v1;
+        else c0.w = v0, c1.w = v1;
+      }
       const float4 south = *reinterpret_cast<const float4 *>(rowC0 - kTmaBoxX);     // y-1 of row r0
       const float4 north = *reinterpret_cast<const float4 *>(rowC0 + 2 * kTmaBoxX); // y+1 of row r1
       float w0 = __shfl_up_sync(0xffffffffu, c0.w, 1), e0 = __shfl_down_sync(0xffffffffu, c0.x, 1);
       float w1 = __shfl_up_sync(0xffffffffu, c1.w, 1), e1 = __shfl_down_sync(0xffffffffu, c1.x, 1);
       if (lane == 0) {
-        w0 = rowC0[-1];
-        w1 = rowC0[kTmaBoxX - 1];
+        w0 = sideL ? sL[(P.sx - 1) & 3] : rowC0[-1];
+        w1 = sideL ? sL[kSideBoxX + ((P.sx - 1) & 3)] : rowC0[kTmaBoxX - 1];
       }
       if (lane == 31) {
-        e0 = rowC0[kVec];
-        e1 = rowC0[kTmaBoxX + kVec];
+        e0 = eSide ? sR[0] : rowC0[kVec];
+        e1 = eSide ? sR[kSideBoxX] : rowC0[kTmaBoxX + kVec];
       }
       /* this stage's data is in registers now: hand the slot back before doing the arithmetic and the stores */
       __syncwarp();
@@ -617,6 +647,8 @@ struct Jacobi3D::Impl {
     unsigned ioSteps = 0;
     JacobiParams base[2]; // per parity: src = buffer[parity]
     CUtensorMap tmap[2];  // per parity: the curr buffer as a 3-D tensor (padded row, rows, planes)
+    CUtensorMap tmapSide[2]; // same tensor, 4 x 16 box: the cells at the other end of the rows (x wrap by load)
+    bool wrapLoad = false;
     std::vector<int> sameDevDeps;
     WaitSet finalWait;
     CopyPlan scatter; // my x-side mailboxes -> the x halos of `next` (faces whose neighbour is on another GPU)
@@ -808,6 +840,10 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
         if (!(nbs[f].sameRank && nbs[f].sameDevice)) flagMask |= 1u << f;
         if (nbs[f].sameRank && nbs[f].sameDevice && nbs[f].dom != int(di)) deps.insert(nbs[f].dom);
       }
+    /* x wrap by load instead of x halo pushes: both x neighbours are this very subdomain */
+    d.wrapLoad = opt_.mode == Mode::Fused && impl_->useTma && !opt_.xMailbox && !std::getenv("STENCIL_JACOBI_NO_WRAP_LOAD") && nbs[XM].exists &&
+                 nbs[XP].exists && nbs[XM].sameRank && nbs[XP].sameRank && nbs[XM].dom == int(di) && nbs[XP].dom == int(di) && sz.x >= kSideBoxX;
+    if (d.wrapLoad) faceMask &= ~((1u << XM) | (1u << XP));
     d.sameDevDeps.assign(deps.begin(), deps.end());
     if (opt_.mode == Mode::Fused && impl_->useTma && opt_.xMailbox) {
       for (int f = XM; f <= XP; ++f) {
@@ -858,7 +894,12 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
         /* logical element (0,0,0) sits `lead` elements into the padded row; compute x=0 is one radius further */
         const char *bufStart = static_cast<const char *>(ld.slab()) + ld.buffer_start_offset(h_.id(), parity);
         P.tmaX0 = int(ld.lead_elems(h_.id())) + 1;
-        if (impl_->useTma) d.tmap[parity] = make_plane_map(const_cast<char *>(bufStart), pitch, ld.raw_size());
+        if (impl_->useTma) {
+          d.tmap[parity] = make_plane_map(const_cast<char *>(bufStart), pitch, ld.raw_size());
+          d.tmapSide[parity] = tma::make_plane_map(const_cast<char *>(bufStart), CU_TENSOR_MAP_DATA_TYPE_FLOAT32, sizeof(float), pitch.x,
+                                                   ld.raw_size().y, ld.raw_size().z, unsigned(kSideBoxX), unsigned(kTmaRows));
+        }
+        P.wrapLoad = d.wrapLoad ? 1 : 0;
       }
       P.ox = org.x;
       P.oy = org.y;
@@ -957,7 +998,7 @@ void Jacobi3D::step() {
       const int mb = impl_->minBlocksForced ? impl_->minBlocks : 2;
       auto *k = fused ? (mb == 3 ? &jacobi7_tma_kernel<true, 3> : &jacobi7_tma_kernel<true, 2>)
                       : (mb == 3 ? &jacobi7_tma_kernel<false, 3> : &jacobi7_tma_kernel<false, 2>);
-      (*k)<<<n, kTmaThreads, kTmaSmemBytes, d.stream>>>(d.tmap[ld.parity()], P);
+      (*k)<<<n, kTmaThreads, kTmaSmemBytes, d.stream>>>(d.tmap[ld.parity()], d.tmapSide[ld.parity()], P);
     } else if (fused) {
       jacobi7_kernel<true><<<n, kThreads, 0, d.stream>>>(P);
     } else {

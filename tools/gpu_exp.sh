@@ -1,8 +1,5 @@
 #!/bin/bash
-mkdir -p gpurun_out
 cd /root/repo
 export STENCIL_LOG_LEVEL=1
-A="./build/bin/jacobi3d 512 512 512 -n 6 --tile-z 16"
-$A > gpurun_out/ncu_plain_fused.log 2>&1 && \
-ncu --set full --clock-control none --import-source on -k regex:jacobi7 -s 3 -c 1 -f -o gpurun_out/prof_fused $A > gpurun_out/ncu_fused.log 2>&1
-echo "fused ncu rc=$?"
+timeout 500 ./build/bin/test_cuda "[jacobi]" 2>&1 | grep "FAIL\|failed in\|test cases\|error" | head -8
+timeout 300 python bench.py --steps 200 --warmup 10 2>/dev/null | tail -1 | python -c "import sys,json; d=json.loads(sys.stdin.read()); print(d['value'], d['ms_per_step'], d['e2e']['value'])"
