@@ -1,5 +1,8 @@
 #!/bin/bash
 cd /root/repo
 export STENCIL_LOG_LEVEL=1
-timeout 500 ./build/bin/test_cuda "[jacobi]" 2>&1 | grep "FAIL\|failed in\|test cases\|error" | head -8
-timeout 300 python bench.py --steps 200 --warmup 10 2>/dev/null | tail -1 | python -c "import sys,json; d=json.loads(sys.stdin.read()); print(d['value'], d['ms_per_step'], d['e2e']['value'])"
+for sz in "645 645 323" "813 407 407" "1024 512 256"; do
+A="./build/bin/jacobi3d $sz -n 40 --tile-z 16 --exact-size"
+echo "== $sz wrap by load"; timeout 120 $A 2>/dev/null | tail -1
+echo "== $sz x push"; STENCIL_JACOBI_NO_WRAP_LOAD=1 timeout 120 $A 2>/dev/null | tail -1
+done
