@@ -61,7 +61,7 @@ def test_exchange_async_chained_to_a_torch_stream(built):
     dd.realize()
     assert dd.exchange_device_only
     g = np.arange(16 * 12 * 10, dtype=np.float32).reshape(10, 12, 16)
-    subs = dd.subdomains()
+    subs = dd.subdomains
     for s in subs:
         (ox, oy, oz), (sx, sy, sz) = s.origin, s.size
         s.from_host(q, np.full((s.raw_size[2], s.raw_size[1], s.raw_size[0]), -1, np.float32))
@@ -76,7 +76,10 @@ def test_exchange_async_chained_to_a_torch_stream(built):
         for s in subs:
             ev = dd.exchange_done_event(s.index)
             assert ev
-            from cuda import cudart
+            try:
+                from cuda.bindings import runtime as cudart
+            except ImportError:
+                from cuda import cudart
             (err,) = cudart.cudaStreamWaitEvent(stream.cuda_stream, ev, 0)
             assert int(err) == 0
         stream.synchronize()
