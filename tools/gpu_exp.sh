@@ -1,8 +1,8 @@
 #!/bin/bash
+mkdir -p gpurun_out
 cd /root/repo
 export STENCIL_LOG_LEVEL=1
-for sz in "645 645 323" "813 407 407" "1024 512 256"; do
-A="./build/bin/jacobi3d $sz -n 40 --tile-z 16 --exact-size"
-echo "== $sz wrap by load"; timeout 120 $A 2>/dev/null | tail -1
-echo "== $sz x push"; STENCIL_JACOBI_NO_WRAP_LOAD=1 timeout 120 $A 2>/dev/null | tail -1
-done
+A="./build/bin/jacobi3d 512 512 512 -n 6 --tile-z 16"
+$A > gpurun_out/ncu_plain_fused.log 2>&1 && \
+ncu --set full --clock-control none --import-source on -k regex:jacobi7 -s 3 -c 1 -f -o gpurun_out/prof_fused $A > gpurun_out/ncu_fused.log 2>&1
+echo "fused ncu rc=$?"
