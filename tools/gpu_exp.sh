@@ -1,8 +1,8 @@
 #!/bin/bash
-mkdir -p gpurun_out
+# Scratch script for one-off GPU experiments (edited per experiment, run through gpurun). The kept measurement
+# scripts are gpu_tests.sh (pytest -m gpu), gpu_multi.sh N (multi-GPU validation + benches), gpu_ncu.sh (ncu captures),
+# gpu_perf.sh / gpu_apps.sh (app-level numbers).
 cd /root/repo
 export STENCIL_LOG_LEVEL=1
-A="./build/bin/jacobi3d 512 512 512 -n 6 --tile-z 16"
-$A > gpurun_out/ncu_plain_fused.log 2>&1 && \
-ncu --set full --clock-control none --import-source on -k regex:jacobi7 -s 3 -c 1 -f -o gpurun_out/prof_fused $A > gpurun_out/ncu_fused.log 2>&1
-echo "fused ncu rc=$?"
+timeout 500 ./build/bin/test_cuda "[jacobi]" 2>&1 | tail -1
+timeout 300 python bench.py --steps 100 --warmup 10 2>/dev/null | tail -1 | cut -c1-200
