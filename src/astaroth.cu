@@ -732,6 +732,7 @@ AstarothSim::~AstarothSim() {
 }
 
 void AstarothSim::init() {
+  if (impl_->iter > 0) sync(); // neighbours may still be storing the last step's faces into these buffers
   for (size_t di = 0; di < dd_->domains().size(); ++di) {
     LocalDomain &ld = dd_->domains()[di];
     DevGuard g(ld.gpu());
