@@ -129,3 +129,55 @@ TEST_CASE("ties cut z before y before x by default, and the reference order on r
   }
   REQUIRE(partition_tie_break() == stencil::detail::TieBreak::Z);
 }
+
+TEST_CASE("partitions tile the domain exactly for many sizes, counts and both tie policies", "[partition]") {
+  const Radius r = Radius::constant(2);
+  for (int policy = 0; policy < 2; ++policy) {
+    const stencil::detail::TieBreak saved = partition_tie_break();
+    set_partition_tie_break(policy ? stencil::detail::TieBreak::X : stencil::detail::TieBreak::Z);
+    size_t bad = 0;
+    const Dim3 sizes[] = {Dim3(17, 13, 11), Dim3(64, 64, 64), Dim3(645, 645, 645), Dim3(100, 7, 300), Dim3(5, 1024, 6), Dim3(813, 813, 813)};
+    for (const Dim3 &size : sizes)
+      for (int64_t n : {1, 2, 3, 4, 5, 6, 8, 12, 16, 30}) {
+        for (int kind = 0; kind < 2; ++kind) {
+          Dim3 dim;
+          std::vector<Dim3> sz, org;
+          auto collect = [&](auto &part) {
+            dim = part.dim();
+            for (int64_t z = 0; z < dim.z; ++z)
+              for (int64_t y = 0; y < dim.y; ++y)
+                for (int64_t x = 0; x < dim.x; ++x) {
+                  sz.push_back(part.subdomain_size(Dim3(x, y, z)));
+                  org.push_back(part.subdomain_origin(Dim3(x, y, z)));
+                }
+          };
+          if (kind == 0) {
+            RankPartition p(size, n);
+            collect(p);
+          } else {
+            const int64_t nodes = n % 2 == 0 ? 2 : 1;
+            NodePartition p(size, r, nodes, n / nodes);
+            collect(p);
+          }
+          if (dim.flatten() != n) ++bad;
+          int64_t cells = 0;
+          for (size_t i = 0; i < sz.size(); ++i) {
+            cells += sz[i].flatten();
+            /* boxes of a tensor-product grid: sizes along an axis differ by at most one and origins are cumulative */
+            for (int a = 0; a < 3; ++a) {
+              if (sz[i][a] < size[a] / dim[a] || sz[i][a] > size[a] / dim[a] + 1) ++bad;
+              if (org[i][a] < 0 || org[i][a] + sz[i][a] > size[a]) ++bad;
+            }
+            for (size_t j = i + 1; j < sz.size(); ++j) {
+              bool overlap = true;
+              for (int a = 0; a < 3; ++a) overlap = overlap && org[i][a] < org[j][a] + sz[j][a] && org[j][a] < org[i][a] + sz[i][a];
+              if (overlap) ++bad;
+            }
+          }
+          if (cells != size.flatten()) ++bad;
+        }
+      }
+    set_partition_tie_break(saved);
+    REQUIRE(bad == 0);
+  }
+}
