@@ -861,6 +861,18 @@ DistributedDomain::~DistributedDomain() {
   domains_.clear();
 }
 
+/* Setup timers (reference: STENCIL_SETUP_STATS, default ON, stencil.cu:31-52 there): max over ranks of each phase's
+   wall time, valid on every rank. Built with -DSETUP_STATS=OFF the reductions (one small collective per phase) are
+   skipped and the fields hold this rank's own times. */
+static double setup_phase_seconds(stencil::Comm &comm, double local) {
+#if !defined(STENCIL_SETUP_STATS) || STENCIL_SETUP_STATS == 1
+  return comm.allreduce_max(local);
+#else
+  (void)comm;
+  return local;
+#endif
+}
+
 void DistributedDomain::init(size_t x, size_t y, size_t z) {
   size_ = Dim3(int64_t(x), int64_t(y), int64_t(z));
   rank_ = comm_->rank();
@@ -868,7 +880,7 @@ void DistributedDomain::init(size_t x, size_t y, size_t z) {
 
   double t = stencil::Comm::wtime();
   topo_.reset(new MpiTopology(*comm_));
-  timeMpiTopo_ += comm_->allreduce_max(stencil::Comm::wtime() - t);
+  timeMpiTopo_ += setup_phase_seconds(*comm_, stencil::Comm::wtime() - t);
 
   int deviceCount = 0;
   CUDA_RUNTIME(cudaGetDeviceCount(&deviceCount));
@@ -931,7 +943,7 @@ void DistributedDomain::realize() {
       off += counts[size_t(r)];
     }
   }
-  timeNodeGpus_ += comm_->allreduce_max(stencil::Comm::wtime() - t);
+  timeNodeGpus_ += setup_phase_seconds(*comm_, stencil::Comm::wtime() - t);
 
   t = stencil::Comm::wtime();
   {
@@ -942,7 +954,7 @@ void DistributedDomain::realize() {
         gpu_topo::enable_peer(dst, src);
       }
   }
-  timePeerEn_ += comm_->allreduce_max(stencil::Comm::wtime() - t);
+  timePeerEn_ += setup_phase_seconds(*comm_, stencil::Comm::wtime() - t);
 
   t = stencil::Comm::wtime();
   {
@@ -952,7 +964,7 @@ void DistributedDomain::realize() {
     else
       placement_.reset(new Trivial(size_, *topo_, gpus_));
   }
-  timePlacement_ += comm_->allreduce_max(stencil::Comm::wtime() - t);
+  timePlacement_ += setup_phase_seconds(*comm_, stencil::Comm::wtime() - t);
 
   t = stencil::Comm::wtime();
   domains_.clear();
@@ -969,16 +981,16 @@ void DistributedDomain::realize() {
     domains_.push_back(std::move(ld));
   }
   for (LocalDomain &d : domains_) d.realize();
-  timeCreate_ += comm_->allreduce_max(stencil::Comm::wtime() - t);
+  timeCreate_ += setup_phase_seconds(*comm_, stencil::Comm::wtime() - t);
 
   t = stencil::Comm::wtime();
   STENCIL_RANGE("DistributedDomain::realize() plan messages");
   ex_.reset(new stencil::Exchanger(*this));
   ex_->prepare();
   ex_->summarize();
-  timePlan_ += comm_->allreduce_max(stencil::Comm::wtime() - t);
+  timePlan_ += setup_phase_seconds(*comm_, stencil::Comm::wtime() - t);
 
-  timeRealize_ += comm_->allreduce_max(stencil::Comm::wtime() - tRealize);
+  timeRealize_ += setup_phase_seconds(*comm_, stencil::Comm::wtime() - tRealize);
 }
 
 void DistributedDomain::swap() {
