@@ -50,7 +50,7 @@ constexpr int kLanes = 32, kRows = 8, kThreads = kLanes * kRows, kVec = 4, kTile
 /* TMA variant geometry */
 constexpr int kTmaRows = 16, kTmaBoxX = kTileX + 8, kTmaBoxY = kTmaRows + 2, kTmaStages = 6;
 constexpr int kTmaConsumerWarps = kTmaRows / 2, kTmaThreads = kTmaConsumerWarps * 32;
-constexpr int kMaxTileZ = 64; // bound on Options::tileZ for the TMA variant (size of the x-face staging tile)
+constexpr int kMaxTileZ = 64; // bound on Options::tileZ for the TMA variant (keeps enough tiles in flight on small domains)
 constexpr int kTmaLag = 2; // the producer refills the slot that was consumed kTmaLag planes ago
 constexpr int kTmaPlaneBytes = kTmaBoxX * kTmaBoxY * 4;
 constexpr int kTmaStageBytes = (kTmaPlaneBytes + 127) / 128 * 128;
