@@ -78,3 +78,10 @@ def test_topology_benchmarks_run(bin_dir, tmp_path):
     assert out.splitlines()[0] == "stencil" and "direct-store" in out and "All-to-all 8MiB" in out
     out = _run(bin_dir, tmp_path, "measure-buf-exchange", "--rounds", "2", "--measures", "2")
     assert "final MiB" in out and "GB/s" in out
+
+
+def test_example_heat_conserves_the_mean(bin_dir, tmp_path):
+    """examples/heat.cu: a user-written stencil with interior / exchange_async / exterior overlap."""
+    out = _run(bin_dir, tmp_path, "example-heat", "64", "48", "40", "12")
+    line = [l for l in out.splitlines() if l.startswith("mean temperature")][-1]
+    assert abs(float(line.split()[-1]) - 0.5) < 1e-3, out
