@@ -26,8 +26,9 @@ std::vector<float> gather(stencil::Jacobi3D &j) {
 }
 
 size_t mismatches(const Dim3 &size, stencil::Jacobi3D::Mode mode, const std::vector<int> &gpus, int iters, int tileZ = 32,
-                  MethodFlags methods = MethodFlags::All) {
+                  MethodFlags methods = MethodFlags::All, bool xMailbox = false) {
   stencil::Jacobi3D::Options opt;
+  opt.xMailbox = xMailbox;
   opt.mode = mode;
   opt.gpus = gpus;
   opt.tileZ = tileZ;
@@ -157,8 +158,11 @@ TEST_CASE("jacobi: every visible GPU, fused NVLink pushes", "[cuda][jacobi][mult
     const stencil::detail::TieBreak saved = partition_tie_break();
     set_partition_tie_break(stencil::detail::TieBreak::X);
     const size_t bad = mismatches(Dim3(70, 40, 36), M::Fused, gpus, 8, 8);
+    /* ... and the optional variant that sends those faces as dense runs through the neighbour's mailbox */
+    const size_t badMailbox = mismatches(Dim3(70, 40, 36), M::Fused, gpus, 8, 8, MethodFlags::All, true);
     set_partition_tie_break(saved);
     REQUIRE(bad == 0);
+    REQUIRE(badMailbox == 0);
   }
   REQUIRE(mismatches(Dim3(70, 40, 36), M::Fused, gpus, 8, 8) == 0);
   REQUIRE(mismatches(Dim3(70, 40, 36), M::Overlap, gpus, 4, 8) == 0);
