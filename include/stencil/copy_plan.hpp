@@ -92,6 +92,8 @@ class CopyPlan {
   std::vector<unsigned char> optional_; // per segment
   unsigned nRequiredChunks_ = 0;
 
+  void upload();
+
 public:
   CopyPlan() {}
   ~CopyPlan();
@@ -119,6 +121,10 @@ public:
   /* build the chunk table and upload both tables to device `dev` (the device that will run the kernel) */
   void finalize(int dev, size_t chunkBytes = 32 * 1024);
   bool finalized() const { return dSegs_ != nullptr || segs_.empty(); }
+  /* the host half of finalize(): the chunk table alone (needs no GPU; exposed for tests and tools) */
+  void build_chunks(size_t chunkBytes = 32 * 1024);
+  const std::vector<CopyChunk> &chunks() const { return chunks_; }
+  size_t num_required_chunks() const { return nRequiredChunks_; }
 
   /* one launch on `stream` (a stream of the plan's device); no host synchronisation */
   void launch(int parity, cudaStream_t stream) const;

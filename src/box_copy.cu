@@ -414,6 +414,11 @@ void CopyPlan::add_optional(const BoxView &src, const Dim3 &srcPos, const BoxVie
 
 void CopyPlan::finalize(int dev, size_t chunkBytes) {
   dev_ = dev;
+  build_chunks(chunkBytes);
+  upload();
+}
+
+void CopyPlan::build_chunks(size_t chunkBytes) {
   chunks_.clear();
   nRequiredChunks_ = 0;
   /* chunks of the optional segments go last, so that leaving them out is a shorter chunk table */
@@ -435,6 +440,9 @@ void CopyPlan::finalize(int dev, size_t chunkBytes) {
     }
   }
   }
+}
+
+void CopyPlan::upload() {
   if (segs_.empty()) return;
   int prev = 0;
   CUDA_RUNTIME(cudaGetDevice(&prev));
