@@ -11,5 +11,6 @@ for n in 1 2 4 8; do
   launch="python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $((29700 + n)) --no-python"
   $launch ./build/bin/jacobi3d 512 512 512 -n 100 | tee -a "$OUT/jacobi3d.csv"
   $launch ./build/bin/weak 512 512 512 30 | tee -a "$OUT/weak.csv"
-  $launch ./build/bin/astaroth-sim --x 256 --y 256 --z 256 --fields 8 --double --star --weak --iters 20 | tee -a "$OUT/astaroth.csv"
+  # through a wrapper: torchrun's own parser takes "--star" for an abbreviation of --start-method
+  EXTRA=--weak ITERS=20 $launch tools/astaroth_target.sh | tee -a "$OUT/astaroth.csv"
 done
