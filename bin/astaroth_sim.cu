@@ -35,6 +35,7 @@ int main(int argc, char **argv) {
   p.add_option(fields, "--fields");
   p.add_flag(fp64, "--double");
   p.add_flag(star, "--star");
+  p.add_flag(star, "--star19")->help("same as --star (torchrun's parser mistakes --star for an abbreviation of its --start-method)");
   p.add_flag(noOverlap, "--no-overlap");
   p.add_flag(forceOverlap, "--overlap")->help("keep the interior/exterior schedule even where the engine would drop it");
   p.add_flag(weak, "--weak");
