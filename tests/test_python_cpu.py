@@ -173,3 +173,24 @@ def test_two_process_tcp_group(built, tmp_path):
     outs = [p.communicate(timeout=120)[0] for p in procs]
     assert all(p.returncode == 0 for p in procs), outs
     assert "ok 0" in outs[0] and "ok 1" in outs[1]
+
+
+def test_c_abi_header_library_and_binding_agree(built):
+    """Every function declared in include/stencil_c.h is exported by the library, and everything the ctypes layer
+    declares exists in the header (so the three cannot drift apart silently)."""
+    import re
+    import subprocess
+    from stencil2_b200 import library_path
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    header = open(os.path.join(root, "include", "stencil_c.h")).read()
+    header = re.sub(r"/\*.*?\*/", "", header, flags=re.S)
+    declared = set(re.findall(r"\b(stencil_[a-z0-9_]+)\s*\(", header))
+    nm = subprocess.run(["nm", "-D", "--defined-only", library_path()], stdout=subprocess.PIPE, text=True, check=True).stdout
+    exported = {l.split()[-1] for l in nm.splitlines() if " T " in l and "stencil_" in l}
+    missing = sorted(d for d in declared if d not in exported)
+    assert not missing, f"declared in stencil_c.h but not exported: {missing}"
+    binding = open(os.path.join(root, "stencil2_b200", "_lib.py")).read()
+    bound = set(re.findall(r'"(stencil_[a-z0-9_]+)"\s*:', binding))
+    unknown = sorted(b for b in bound if b not in declared)
+    assert not unknown, f"bound in _lib.py but not in stencil_c.h: {unknown}"
+    assert len(bound) > 40
