@@ -28,6 +28,7 @@ APPS = {  # target -> (sources relative to the reference root, extra defines)
     "weak": (["bin/weak.cu"], ["-DSTENCIL_EXCHANGE_STATS=1"]),
     "strong": (["bin/strong.cu"], ["-DSTENCIL_EXCHANGE_STATS=1"]),
     "weak-exchange": (["bin/weak_exchange.cu"], ["-DSTENCIL_EXCHANGE_STATS=1"]),
+    "bench-qap": (["bin/bench_qap.cu"], []),  # CPU only: placement solver timings (BASELINE config 1)
 }
 LIB = ["src/gpu_topology.cpp", "src/local_domain.cu", "src/rcstream.cpp", "src/stencil.cu"]
 
