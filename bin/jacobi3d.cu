@@ -1,6 +1,6 @@
 /* jacobi3d: 7-point Jacobi heat solver, weak-scaled by the number of subdomains.
    CLI and CSV line follow the reference's bin/jacobi3d.cu:110-128,378-379:
-     jacobi3d X Y Z [--iters/-n N] [--staged --colo --peer --kernel --direct] [--trivial] [--no-overlap]
+     jacobi3d X Y Z [--iters/-n N] [--staged --colo --peer --kernel --direct --cuda-aware-mpi] [--trivial] [--no-overlap]
               [--paraview --prefix P --period/-q Q]
    prints on rank 0:  jacobi3d,<methods>,<ranks>,<devCount>,<x>,<y>,<z>,<min iter s>,<trimean iter s>
    Additions: --direct (MethodFlags::NvlinkDirect), --no-fused (use the reference's exchange() schedule instead of
@@ -8,28 +8,26 @@
 #include <cmath>
 #include <iostream>
 
-#include "stencil/argparse.hpp"
+#include "common.hpp"
 #include "stencil/jacobi.hpp"
 #include "stencil/statistics.hpp"
 
 int main(int argc, char **argv) {
-  bool useStaged = false, useColo = false, usePeer = false, useKernel = false, useDirect = false;
-  bool trivial = false, noOverlap = false, paraview = false, noFused = false, exactSize = false, ldg = false, boundaryFirst = false;
+  MethodArgs methodArgs;
+  bool trivial = false, noOverlap = false, paraview = false, noFused = false, exactSize = false, ldg = false, naturalOrder = false;
+  bool deviceTime = false;
   size_t x = 512, y = 512, z = 512;
   std::string prefix;
   int iters = 30, period = -1, tileZ = 32;
 
   argparse::Parser parser("7-point Jacobi on a periodic box with a hot and a cold sphere");
-  parser.add_flag(useStaged, "--staged")->help("enable the host-staged transport (CudaMpi)");
-  parser.add_flag(useColo, "--colo")->help("enable the colocated IPC transport (CudaMpiColocated)");
-  parser.add_flag(usePeer, "--peer")->help("enable pack + cudaMemcpyPeer (CudaMemcpyPeer)");
-  parser.add_flag(useKernel, "--kernel")->help("enable same-GPU copies (CudaKernel)");
-  parser.add_flag(useDirect, "--direct")->help("enable device-initiated NVLink stores (NvlinkDirect)");
+  methodArgs.add_to(parser);
   parser.add_flag(trivial, "--trivial")->help("skip node-aware placement");
   parser.add_flag(noOverlap, "--no-overlap")->help("don't overlap communication and computation");
   parser.add_flag(noFused, "--no-fused")->help("use exchange() + separate kernels instead of the fused kernel");
   parser.add_flag(ldg, "--ldg")->help("use the plain-load kernel variant instead of the TMA pipeline");
-  parser.add_flag(boundaryFirst, "--boundary-first")->help("schedule pushing tiles before interior tiles");
+  parser.add_flag(naturalOrder, "--natural-order")->help("do not schedule the tiles that push to other GPUs first");
+  parser.add_flag(deviceTime, "--device-time")->help("also print the free-running device time per iteration (no host sync in the loop)");
   parser.add_flag(exactSize, "--exact-size")->help("use X Y Z as the whole domain (no weak scaling)");
   parser.add_option(prefix, "--prefix")->help("prefix for paraview files");
   parser.add_flag(paraview, "--paraview")->help("dump paraview files");
@@ -66,13 +64,7 @@ int main(int argc, char **argv) {
     z = size_t(double(z) * s + 0.5);
   }
 
-  MethodFlags methods = MethodFlags::None;
-  if (useStaged) methods |= MethodFlags::CudaMpi;
-  if (useColo) methods |= MethodFlags::CudaMpiColocated;
-  if (usePeer) methods |= MethodFlags::CudaMemcpyPeer;
-  if (useKernel) methods |= MethodFlags::CudaKernel;
-  if (useDirect) methods |= MethodFlags::NvlinkDirect;
-  if (methods == MethodFlags::None) methods = MethodFlags::All;
+  const MethodFlags methods = methodArgs.flags();
 
   Statistics iterTime;
   {
@@ -82,7 +74,7 @@ int main(int argc, char **argv) {
     opt.mode = noOverlap ? stencil::Jacobi3D::Mode::NoOverlap : (noFused ? stencil::Jacobi3D::Mode::Overlap : stencil::Jacobi3D::Mode::Fused);
     opt.tileZ = tileZ;
     opt.useTma = !ldg;
-    opt.boundaryFirst = boundaryFirst;
+    opt.flaggedFirst = !naturalOrder;
     opt.planFile = true;
     stencil::Jacobi3D solver(x, y, z, opt);
     comm.barrier();
@@ -96,6 +88,10 @@ int main(int argc, char **argv) {
       if (paraview && iter % period == 0) solver.domain().write_paraview(prefix + "jacobi3d_" + std::to_string(iter));
     }
     if (paraview) solver.domain().write_paraview(prefix + "jacobi3d_final");
+    if (deviceTime) {
+      const double secs = solver.run(iters);
+      if (rank == 0) std::cout << "jacobi3d-device," << size << "," << devCount << "," << x << "," << y << "," << z << "," << secs / iters << "\n";
+    }
   }
   if (rank == 0)
     std::cout << "jacobi3d," << method_string(methods) << "," << size << "," << devCount << "," << x << "," << y << "," << z << ","

@@ -144,6 +144,9 @@ struct WaitSet {
 };
 void launch_wait_flags(const WaitSet &ws, unsigned epoch, unsigned *errWord, unsigned long long timeoutNs,
                        cudaStream_t stream);
+/* how long a device-side flag wait may last before it reports through the error word: STENCIL_FLAG_TIMEOUT_MS
+   (default 5000). One helper for the Exchanger and both engines, so that debuggers / MPS / slow peers need one knob. */
+unsigned long long flag_timeout_ns();
 /* publish `epoch` to every flag (release, system scope) once all prior work of `stream` is done */
 void launch_signal_flags(const SignalSet &sig, unsigned epoch, cudaStream_t stream);
 

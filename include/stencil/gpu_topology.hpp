@@ -22,6 +22,11 @@ Mat2D<double> bandwidth_matrix(int n);
 
 /* enable src->dst peer access if the hardware allows; remembers the outcome */
 void enable_peer(int src, int dst);
+/* Record whether src could reach dst without enabling anything: for a dst that belongs to ANOTHER process.
+   Its memory is only ever reached through cudaIpcOpenMemHandle(..., cudaIpcMemLazyEnablePeerAccess), which sets up
+   what it needs; cudaDeviceEnablePeerAccess() here would create a context on that GPU in this process too (with one
+   process per GPU: 64 contexts on an 8-GPU box, and 13 s of the 14 s realize() took). */
+void note_peer(int src, int dst);
 /* was peer access from src to dst enabled by enable_peer() (true for src == dst once registered) */
 bool peer(int src, int dst);
 /* true if every active NVLink of `dev` ends at an NVSwitch */

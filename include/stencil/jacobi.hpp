@@ -32,9 +32,8 @@ public:
     std::vector<int> gpus; // empty: the rank's default devices
     int tileZ = 32;        // z-extent of a tile (planes marched per CTA)
     bool useTma = true;    // TMA + mbarrier pipelined kernel (false: plain LDG variant, kept for comparison)
-    bool xMailbox = false;      // send x faces to other GPUs as dense runs through their mailboxes (+ a scatter kernel per
-                                // iteration) instead of one 32-byte sector per row; measured slower on 2 B200, kept for study
-    bool boundaryFirst = false; // schedule the tiles that push to neighbours before the interior tiles
+    bool flaggedFirst = true; // schedule the tiles that push to ANOTHER GPU first, so each face is announced early
+    bool narrowTiles = true;  // cover the remainder of rows that are not a multiple of 128 cells with 32 x 64 tiles
     bool planFile = false;
   };
 

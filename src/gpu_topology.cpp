@@ -202,6 +202,14 @@ void enable_peer(int src, int dst) {
   g_peer[{src, dst}] = ok;
 }
 
+void note_peer(int src, int dst) {
+  int can = src == dst ? 1 : 0;
+  if (src != dst) CUDA_RUNTIME(cudaDeviceCanAccessPeer(&can, src, dst));
+  LOG_DEBUG(src << " -> " << dst << " peer access " << (can ? "possible (enabled lazily by the IPC mapping)" : "unavailable"));
+  std::lock_guard<std::mutex> lk(g_mu);
+  g_peer[{src, dst}] = can != 0;
+}
+
 bool peer(int src, int dst) {
   std::lock_guard<std::mutex> lk(g_mu);
   auto it = g_peer.find({src, dst});

@@ -47,29 +47,48 @@ namespace stencil {
 namespace {
 
 constexpr int kLanes = 32, kRows = 8, kThreads = kLanes * kRows, kVec = 4, kTileX = kLanes * kVec;
-/* TMA variant geometry */
-constexpr int kTmaRows = 16, kTmaBoxX = kTileX + 8, kTmaBoxY = kTmaRows + 2, kTmaStages = 6;
+/* TMA variant geometry. Two tile shapes share one kernel, picked per tile (uniform per CTA):
+     wide   128 cells x 16 rows: a warp is one pair of rows, a lane owns 4 cells of each;
+     narrow  32 cells x 64 rows: a warp is four pairs of rows, 8 lanes per row. Same 2048 cells per plane, same loop.
+   Narrow tiles cover what is left of a row after the last full 128-cell tile: the weak-scaling rule produces rows of
+   645 and 813 cells, and a wide tile on the remaining 5 / 45 cells costs as much as one on 128 (the kernel is as much
+   issue bound as DRAM bound). 645 -> 5 wide + 1 narrow column = 5.25 tile columns instead of 6. */
+constexpr int kTmaRows = 16, kTmaStages = 6;
 constexpr int kTmaConsumerWarps = kTmaRows / 2, kTmaThreads = kTmaConsumerWarps * 32;
 constexpr int kMaxTileZ = 64; // bound on Options::tileZ for the TMA variant (keeps enough tiles in flight on small domains)
 constexpr int kTmaLag = 2; // the producer refills the slot that was consumed kTmaLag planes ago
-constexpr int kTmaPlaneBytes = kTmaBoxX * kTmaBoxY * 4;
-constexpr int kTmaStageBytes = (kTmaPlaneBytes + 127) / 128 * 128;
 /* Subdomains that wrap onto themselves in x (always, with the default partition) do not keep x halo cells at all in
    fused mode: a tile at the left / right end of the rows loads the four cells at the OTHER end of its rows with a
-   second, tiny TMA box per plane (4 x 16 floats) and takes its x = -1 / x = sx neighbour from there. The far-end cells
-   are being read by the tile at that end at about the same time, so this is an L2 hit; it replaces one 32-byte
+   second, tiny TMA box per plane (4 cells x tile rows) and takes its x = -1 / x = sx neighbour from there. The far-end
+   cells are being read by the tile at that end at about the same time, so this is an L2 hit; it replaces one 32-byte
    sector store per row and its read-back. */
-constexpr int kSideBoxX = 4, kSideBytes = kSideBoxX * kTmaRows * 4; // 256 B per side and stage
-constexpr int kTmaSideOffset = kTmaStages * kTmaStageBytes;
-constexpr int kTmaBarOffset = kTmaSideOffset + 2 * kTmaStages * kSideBytes;
-constexpr int kTmaSmemBytes = kTmaBarOffset + 2 * kTmaStages * 8;
+constexpr int kSideBoxX = 4;
+template <int LW> struct Geo { // LW = lanes per row: 32 (wide) or 8 (narrow)
+  static constexpr int kSub = 32 / LW;         // row pairs per warp
+  static constexpr int kW = LW * kVec;         // tile width in cells
+  static constexpr int kR = kTmaRows * kSub;   // tile rows
+  static constexpr int kBoxX = kW + 8, kBoxY = kR + 2;
+  static constexpr int kPlaneBytes = kBoxX * kBoxY * 4;
+  static constexpr int kStageBytes = (kPlaneBytes + 127) / 128 * 128;
+  static constexpr int kSideBytes = kSideBoxX * kR * 4; // per side and stage
+  static constexpr int kSideOffset = kTmaStages * kStageBytes;
+  static constexpr int kBarOffset = kSideOffset + 2 * kTmaStages * kSideBytes;
+  static constexpr int kSmemBytes = kBarOffset + 2 * kTmaStages * 8;
+};
+using Wide = Geo<32>;
+using Narrow = Geo<8>;
+constexpr int kNarrowMaxRemainder = 96; // a remainder wider than this is cheaper as one wide tile than as four narrow ones
+constexpr int kTmaSmemBytes = Narrow::kSmemBytes > Wide::kSmemBytes ? Narrow::kSmemBytes : Wide::kSmemBytes;
 constexpr size_t kDynBytes = Jacobi3D::kParamBytes;
 constexpr int kFusedFlagBase = 64; // word offset of the fused-iteration flags inside a control block
 
 enum Face { XM = 0, XP = 1, YM = 2, YP = 3, ZM = 4, ZP = 5 };
 
 struct Tile {
-  unsigned short tx, ty, tz, faces; // faces: bit f set when the tile owns cells on face f that must be pushed
+  int x0, y0;           // first cell / first row of the tile (compute coordinates)
+  unsigned short tz;    // z index in units of tileZ
+  unsigned char faces;  // bit f set when the tile owns cells on face f that must be pushed
+  unsigned char narrow; // TMA variant: 1 = 32 x 64 tile, 0 = 128 x 16
 };
 
 struct JacobiParams {
@@ -90,13 +109,12 @@ struct JacobiParams {
   /* fused push */
   float *nb[6];            // neighbour's next buffer: address of ITS halo cell that receives my face cell (0,0) ...
   long long nbPitchX[6], nbPitchXY[6];
-  float *mbox[2];          // XM / XP: the neighbour's dense x-side mailbox (nullptr: store straight into its halo)
   unsigned *nbFlag[6];     // neighbour flag to raise (nullptr: ordered by the stream / same kernel)
   const unsigned *myFlag[6]; // my flag the neighbour raises (nullptr: no wait)
   unsigned flagMask;       // faces whose neighbour is synchronised through a flag (another GPU); 0 on a single GPU
   unsigned epoch;          // iteration number being computed (1-based)
-  unsigned nBoundary;      // number of tiles that push
-  unsigned *done;          // boundary tile counter
+  unsigned nFace[6];       // per face: number of tiles that push through it to another GPU
+  unsigned *done;          // six per-face counters of finished tiles
   unsigned *err;           // host-mapped error word
   unsigned long long timeoutNs;
 };
@@ -152,30 +170,62 @@ __device__ __forceinline__ float sphere_or(const JacobiParams &P, long long gx, 
   return v;
 }
 
+/* Tiles on a flagged face read halo cells another GPU writes: wait until that neighbour has delivered the previous
+   iteration through THAT face (threads 0..5, one per face; the caller follows with a CTA barrier). A tile waits only
+   on the faces it touches, so a neighbour that is late on one face holds up only the tiles along that face. */
+__device__ __forceinline__ void wait_faces(const JacobiParams &P, unsigned faces) {
+  if (threadIdx.x < 6 && ((faces >> threadIdx.x) & 1u)) {
+    const unsigned *f = P.myFlag[threadIdx.x];
+    const unsigned long long t0 = globaltimer_ns();
+    while (int(ld_acquire_sys(f) - (P.epoch - 1)) < 0) {
+      __nanosleep(64);
+      if (globaltimer_ns() - t0 > P.timeoutNs) {
+        atomicCAS(P.err, 0u, 100u + threadIdx.x);
+        break;
+      }
+    }
+  }
+}
+
+/* Tiles that stored into ANOTHER GPU: count this CTA as done on each of those faces; whoever completes a face's count
+   raises that neighbour's flag — per face, so a face whose tiles are scheduled early (see make_tiles) is announced
+   early and the neighbour never finds it missing when its next kernel starts.
+   Ordering chain: every thread's (peer) stores -> CTA barrier -> thread 0: fence at GPU scope + counter increments ->
+   the CTA that sees a full count: system-scope fence -> relaxed stores of the flags. Causality is transitive
+   across the scopes, so only the final fence has to be system-wide; a system fence per boundary CTA measured
+   ~20 us per 512^3 iteration on B200. */
+__device__ __forceinline__ void signal_faces(const JacobiParams &P, unsigned faces) {
+  if (threadIdx.x == 0) {
+    __threadfence();
+    unsigned ready = 0;
+#pragma unroll
+    for (int f = 0; f < 6; ++f)
+      if ((faces >> f) & 1u) {
+        if (atomicAdd(P.done + f, 1u) == P.nFace[f] - 1) {
+          P.done[f] = 0;
+          ready |= 1u << f;
+        }
+      }
+    if (ready) {
+      __threadfence_system();
+#pragma unroll
+      for (int f = 0; f < 6; ++f)
+        if ((ready >> f) & 1u) st_flag_sys(P.nbFlag[f], P.epoch);
+    }
+  }
+}
+
 template <bool FUSED> __global__ void __launch_bounds__(kThreads) jacobi7_kernel(const __grid_constant__ JacobiParams P) {
   const Tile t = P.tiles[blockIdx.x];
   const int lane = threadIdx.x & (kLanes - 1), row = threadIdx.x / kLanes;
 
   if (FUSED && (t.faces & P.flagMask)) {
-    /* boundary tiles read halo cells: wait until every neighbour has delivered iteration epoch-1 */
-    if (threadIdx.x < 6) {
-      const unsigned *f = P.myFlag[threadIdx.x];
-      if (f) {
-        const unsigned long long t0 = globaltimer_ns();
-        while (int(ld_acquire_sys(f) - (P.epoch - 1)) < 0) {
-          __nanosleep(64);
-          if (globaltimer_ns() - t0 > P.timeoutNs) {
-            atomicCAS(P.err, 0u, 100u + threadIdx.x);
-            break;
-          }
-        }
-      }
-    }
+    wait_faces(P, t.faces & P.flagMask);
     __syncthreads();
   }
 
-  const int x0 = t.tx * kTileX + lane * kVec;
-  const int y = t.ty * kRows + row;
+  const int x0 = t.x0 + lane * kVec;
+  const int y = t.y0 + row;
   const int z0 = max(int(t.tz) * P.tileZ, P.loz), z1 = min(int(t.tz + 1) * P.tileZ, P.hiz);
   /* a warp is one row, so the row test is warp-uniform; the x test is per lane (partial tiles) */
   const bool rowActive = y >= P.loy && y < P.hiy;
@@ -184,9 +234,9 @@ template <bool FUSED> __global__ void __launch_bounds__(kThreads) jacobi7_kernel
   /* does this tile come near either sphere? (uniform per CTA) */
   bool nearSphere;
   {
-    const long long gy0 = P.oy + t.ty * kRows, gy1 = gy0 + kRows - 1;
+    const long long gy0 = P.oy + t.y0, gy1 = gy0 + kRows - 1;
     const long long gz0 = P.oz + z0, gz1 = P.oz + z1 - 1;
-    const long long gx0 = P.ox + t.tx * kTileX, gx1 = gx0 + kTileX - 1;
+    const long long gx0 = P.ox + t.x0, gx1 = gx0 + kTileX - 1;
     auto gap = [](long long a0, long long a1, long long c) { return c < a0 ? a0 - c : (c > a1 ? c - a1 : 0); };
     const long long dy = gap(gy0, gy1, P.cy), dz = gap(gz0, gz1, P.cz);
     const long long dh = gap(gx0, gx1, P.hcx), dc = gap(gx0, gx1, P.ccx);
@@ -279,16 +329,7 @@ template <bool FUSED> __global__ void __launch_bounds__(kThreads) jacobi7_kernel
 
   if (FUSED && (t.faces & P.flagMask)) {
     __syncthreads();
-    if (threadIdx.x == 0) {
-      __threadfence();
-      const unsigned prev = atomicAdd(P.done, 1u);
-      if (prev == P.nBoundary - 1) {
-        *P.done = 0;
-        __threadfence_system();
-        for (int f = 0; f < 6; ++f)
-          if (P.nbFlag[f]) st_flag_sys(P.nbFlag[f], P.epoch);
-      }
-    }
+    signal_faces(P, t.faces & P.flagMask);
   }
 }
 
@@ -304,11 +345,10 @@ __device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *map, i
 
 /* TMA kernel, boundary tiles, after the plane loop: copy the y / z face rows this tile has just written to `next`
    (still in L2) into the neighbours' halos. Whole CTA, one warp per row, 16-byte vectors. Keeping this out of the plane
-   loop leaves the loop free of face tests and calls. */
-__device__ __noinline__ void push_tile_yz(const JacobiParams &P, unsigned faces, int xlo, int ylo, int z0, int z1) {
+   loop leaves the loop free of face tests and calls. tw x tr = the tile's shape. */
+__device__ __noinline__ void push_tile_yz(const JacobiParams &P, unsigned faces, int xlo, int ylo, int tw, int tr, int z0, int z1) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = kTmaThreads / 32;
-  const int xhi = min(xlo + kTileX, P.sx), yhi = min(ylo + kTmaRows, P.sy);
-  const int x = xlo + lane * kVec;
+  const int xhi = min(xlo + tw, P.sx), yhi = min(ylo + tr, P.sy);
   for (int f = YM; f <= ZP; ++f) {
     if (!((faces >> f) & 1u)) continue;
     const bool yface = f == YM || f == YP;
@@ -319,22 +359,23 @@ __device__ __noinline__ void push_tile_yz(const JacobiParams &P, unsigned faces,
       const int y = yface ? fixed : ylo + r, z = yface ? z0 + r : fixed;
       const float *src = P.dst + (long long)z * P.pitchXY + (long long)y * P.pitchX;
       float *dst = yface ? P.nb[f] + (long long)z * P.nbPitchXY[f] : P.nb[f] + (long long)y * P.nbPitchX[f];
-      if (x + kVec <= xhi) {
-        *reinterpret_cast<float4 *>(dst + x) = __ldcg(reinterpret_cast<const float4 *>(src + x));
-      } else {
-        for (int i = x; i < xhi; ++i) dst[i] = __ldcg(src + i);
+      for (int x = xlo + lane * kVec; x < xhi; x += 32 * kVec) {
+        if (x + kVec <= xhi) {
+          *reinterpret_cast<float4 *>(dst + x) = __ldcg(reinterpret_cast<const float4 *>(src + x));
+        } else {
+          for (int i = x; i < xhi; ++i) dst[i] = __ldcg(src + i);
+        }
       }
     }
   }
 }
 
-/* ... and the x faces: one cell per row of the tile, so one cell per thread (16 rows x 16 planes). The value is read
-   back from `next` (L2) and goes either into the neighbour's halo cell — as a whole 32-byte sector where the halo cell
-   shares its sector with row padding only (LocalDomain layout), because a 4-byte store would make the receiver's
-   memory system read-modify-write the sector — or, for a neighbour on another GPU in mailbox mode, into its dense
-   [plane][row] mailbox (64-byte runs instead of one NVLink packet per row). */
-__device__ __noinline__ void push_tile_x(const JacobiParams &P, unsigned faces, int ylo, int z0, int z1) {
-  const int n = (z1 - z0) * kTmaRows;
+/* ... and the x faces (subdomains whose x neighbour is not themselves): one cell per row of the tile, so one cell per
+   thread. The value is read back from `next` (L2) and goes into the neighbour's halo cell — as a whole 32-byte sector
+   where the halo cell shares its sector with row padding only (LocalDomain layout), because a 4-byte store would make
+   the receiver's memory system read-modify-write the sector. */
+__device__ __noinline__ void push_tile_x(const JacobiParams &P, unsigned faces, int ylo, int tr, int z0, int z1) {
+  const int n = (z1 - z0) * tr;
   for (int f = XM; f <= XP; ++f) {
     if (!((faces >> f) & 1u)) continue;
     const int x = f == XM ? 0 : P.sx - 1;
@@ -345,64 +386,25 @@ __device__ __noinline__ void push_tile_x(const JacobiParams &P, unsigned faces, 
     const bool wide = ((reinterpret_cast<unsigned long long>(P.nb[f] + sectorShift) | (unsigned long long)(P.nbPitchX[f] * 4) |
                         (unsigned long long)(P.nbPitchXY[f] * 4)) & 31ull) == 0;
     for (int i = threadIdx.x; i < n; i += kTmaThreads) {
-      const int z = z0 + i / kTmaRows, y = ylo + i % kTmaRows;
+      const int z = z0 + i / tr, y = ylo + i % tr;
       if (y >= P.sy) continue;
       const float v = __ldcg(P.dst + (long long)z * P.pitchXY + (long long)y * P.pitchX + x);
-      if (P.mbox[f]) {
-        P.mbox[f][(long long)z * P.sy + y] = v;
-      } else {
-        float *q = P.nb[f] + (long long)z * P.nbPitchXY[f] + (long long)y * P.nbPitchX[f];
-        if (wide) {
-          const float4 vv = make_float4(v, v, v, v);
-          reinterpret_cast<float4 *>(q + sectorShift)[0] = vv;
-          reinterpret_cast<float4 *>(q + sectorShift)[1] = vv;
-        } else { // neighbour's x extent is not a multiple of 8 cells: interior cells share the sector
-          *q = v;
-        }
+      float *q = P.nb[f] + (long long)z * P.nbPitchXY[f] + (long long)y * P.nbPitchX[f];
+      if (wide) {
+        const float4 vv = make_float4(v, v, v, v);
+        reinterpret_cast<float4 *>(q + sectorShift)[0] = vv;
+        reinterpret_cast<float4 *>(q + sectorShift)[1] = vv;
+      } else { // neighbour's x extent is not a multiple of 8 cells: interior cells share the sector
+        *q = v;
       }
     }
   }
 }
 
-/* boundary tiles: wait until every neighbour has delivered the previous iteration (threads 0..5, then CTA barrier) */
-__device__ __forceinline__ void wait_neighbours(const JacobiParams &P) {
-  if (threadIdx.x < 6) {
-    const unsigned *f = P.myFlag[threadIdx.x];
-    if (f) {
-      const unsigned long long t0 = globaltimer_ns();
-      while (int(ld_acquire_sys(f) - (P.epoch - 1)) < 0) {
-        __nanosleep(64);
-        if (globaltimer_ns() - t0 > P.timeoutNs) {
-          atomicCAS(P.err, 0u, 100u + threadIdx.x);
-          break;
-        }
-      }
-    }
-  }
-}
-
-/* boundary tiles: count this CTA as done; the last one raises the neighbours' flags.
-   Ordering chain: every thread's (peer) stores -> CTA barrier -> thread 0: fence at GPU scope + counter increment ->
-   the CTA that sees the full count: system-scope fence -> release stores of the flags. Causality is transitive
-   across the scopes, so only the one final fence has to be system-wide; a system fence per boundary CTA measured
-   ~20 us per 512^3 iteration on B200. */
-__device__ __forceinline__ void signal_neighbours(const JacobiParams &P) {
-  if (threadIdx.x == 0) {
-    __threadfence();
-    const unsigned prev = atomicAdd(P.done, 1u);
-    if (prev == P.nBoundary - 1) {
-      *P.done = 0;
-      __threadfence_system();
-      for (int f = 0; f < 6; ++f)
-        if (P.nbFlag[f]) st_flag_sys(P.nbFlag[f], P.epoch);
-    }
-  }
-}
-
-__device__ __forceinline__ bool tile_near_sphere(const JacobiParams &P, const Tile &t, int rows, int z0, int z1) {
-  const long long gy0 = P.oy + t.ty * rows, gy1 = gy0 + rows - 1;
+__device__ __forceinline__ bool tile_near_sphere(const JacobiParams &P, const Tile &t, int tw, int tr, int z0, int z1) {
+  const long long gy0 = P.oy + t.y0, gy1 = gy0 + tr - 1;
   const long long gz0 = P.oz + z0, gz1 = P.oz + z1 - 1;
-  const long long gx0 = P.ox + t.tx * kTileX, gx1 = gx0 + kTileX - 1;
+  const long long gx0 = P.ox + t.x0, gx1 = gx0 + tw - 1;
   auto gap = [](long long a0, long long a1, long long c) { return c < a0 ? a0 - c : (c > a1 ? c - a1 : 0); };
   const long long dy = gap(gy0, gy1, P.cy), dz = gap(gz0, gz1, P.cz);
   const long long dh = gap(gx0, gx1, P.hcx), dc = gap(gx0, gx1, P.ccx);
@@ -427,14 +429,14 @@ __device__ __noinline__ void store_partial(const JacobiParams &P, float *dp, int
     if (x0 + k >= P.lox && x0 + k < P.hix) dp[k] = ov[k];
 }
 
-template <bool FUSED, int MINB>
-__global__ void __launch_bounds__(kTmaThreads, MINB)
-    jacobi7_tma_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmapSide, const __grid_constant__ JacobiParams P) {
-  extern __shared__ __align__(128) unsigned char smem[];
-  unsigned long long *full = reinterpret_cast<unsigned long long *>(smem + kTmaBarOffset);
+/* one tile of the TMA kernel; G = Wide or Narrow (uniform per CTA) */
+template <bool FUSED, class G>
+__device__ __forceinline__ void tma_tile(unsigned char *smem, const CUtensorMap *tmap, const CUtensorMap *tmapSide, const JacobiParams &P, const Tile &t) {
+  constexpr int LW = 32 / G::kSub;
+  unsigned long long *full = reinterpret_cast<unsigned long long *>(smem + G::kBarOffset);
   unsigned long long *empty = full + kTmaStages;
-  const Tile t = P.tiles[blockIdx.x];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int xl = lane & (LW - 1), sub = lane / LW; // position in the row, which of the warp's row pairs
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kTmaStages; ++s) {
@@ -443,8 +445,12 @@ __global__ void __launch_bounds__(kTmaThreads, MINB)
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (FUSED && (t.faces & P.flagMask)) wait_neighbours(P);
+  if (FUSED && (t.faces & P.flagMask)) wait_faces(P, t.faces & P.flagMask);
   __syncthreads();
+  /* The halo cells this tile is about to fetch were written by another GPU with ordinary (generic-proxy) stores and
+     made visible by the acquire above; the fetch is a TMA (async-proxy) read issued by thread 0, so that thread orders
+     the two proxies explicitly. */
+  if (FUSED && (t.faces & P.flagMask) && threadIdx.x == 0) asm volatile("fence.proxy.async.global;" ::: "memory");
 
   const int z0 = max(int(t.tz) * P.tileZ, P.loz), z1 = min(int(t.tz + 1) * P.tileZ, P.hiz);
   const int nplanes = z1 > z0 ? z1 - z0 + 2 : 0; // input planes z0-1 .. z1
@@ -453,31 +459,31 @@ __global__ void __launch_bounds__(kTmaThreads, MINB)
      pairs) and with it a resident CTA. Thread 0 issues the TMA loads itself — a prologue of kTmaStages - kTmaLag
      planes, then one refill per iteration into the slot every warp released kTmaLag planes ago, so its wait on the
      `empty` barrier is almost always already satisfied. */
-  const int cx = P.tmaX0 + t.tx * kTileX - 4; // 4 cells of left margin keep the centre 16-byte aligned in smem
-  const int cy = t.ty * kTmaRows;             // raw row of compute row (ty*rows - 1)
+  const int cx = P.tmaX0 + t.x0 - 4; // 4 cells of left margin keep the centre 16-byte aligned in smem
+  const int cy = t.y0;               // raw row of compute row (y0 - 1)
   /* x wrap by load: does this tile hold the first / the last cell of the rows? */
-  const bool sideL = FUSED && P.wrapLoad && t.tx == 0;
-  const bool sideR = FUSED && P.wrapLoad && (int(t.tx) + 1) * kTileX >= P.sx;
-  auto issue = [&](int j) {                   // load input plane j (compute plane z0 - 1 + j, raw plane z0 + j)
+  const bool sideL = FUSED && P.wrapLoad && t.x0 == 0;
+  const bool sideR = FUSED && P.wrapLoad && t.x0 + G::kW >= P.sx;
+  auto issue = [&](int j) {          // load input plane j (compute plane z0 - 1 + j, raw plane z0 + j)
     const int sj = j % kTmaStages;
     if (j >= kTmaStages) mbar_wait(&empty[sj], ((j / kTmaStages) - 1) & 1);
-    mbar_arrive_expect_tx(&full[sj], kTmaPlaneBytes + (sideL ? kSideBytes : 0) + (sideR ? kSideBytes : 0));
-    tma_load_3d(smem + sj * kTmaStageBytes, &tmap, cx, cy, z0 + j, &full[sj]);
-    /* side boxes: rows ty*16 .. +15 (raw row cy + 1); left tiles want the aligned group of four cells that holds cell
+    mbar_arrive_expect_tx(&full[sj], G::kPlaneBytes + (sideL ? G::kSideBytes : 0) + (sideR ? G::kSideBytes : 0));
+    tma_load_3d(smem + sj * G::kStageBytes, tmap, cx, cy, z0 + j, &full[sj]);
+    /* side boxes: the tile's rows (raw row cy + 1); left tiles want the aligned group of four cells that holds cell
        sx-1 (a TMA box must start on a 16-byte boundary: an unaligned start is an illegal instruction), right tiles
        cells 0 .. 3 */
-    if (sideL) tma_load_3d(smem + kTmaSideOffset + sj * kSideBytes, &tmapSide, P.tmaX0 + ((P.sx - 1) & ~3), cy + 1, z0 + j, &full[sj]);
-    if (sideR) tma_load_3d(smem + kTmaSideOffset + (kTmaStages + sj) * kSideBytes, &tmapSide, P.tmaX0, cy + 1, z0 + j, &full[sj]);
+    if (sideL) tma_load_3d(smem + G::kSideOffset + sj * G::kSideBytes, tmapSide, P.tmaX0 + ((P.sx - 1) & ~3), cy + 1, z0 + j, &full[sj]);
+    if (sideR) tma_load_3d(smem + G::kSideOffset + (kTmaStages + sj) * G::kSideBytes, tmapSide, P.tmaX0, cy + 1, z0 + j, &full[sj]);
   };
   if (threadIdx.x == 0)
     for (int j = 0; j < kTmaStages - kTmaLag && j < nplanes; ++j) issue(j);
   {
-    /* ---- consumers: warp w owns tile rows 2w and 2w+1, a lane owns 4 cells of each ---- */
-    const int r0 = 2 * warp;
-    const int x0 = t.tx * kTileX + lane * kVec;
-    const int y0 = t.ty * kTmaRows + r0;
-    const bool nearSphere = tile_near_sphere(P, t, kTmaRows, z0, z1);
-    /* x wrap by load: which lane's vector holds cell x = sx (patchK = its index there), or is it lane 31's east read? */
+    /* ---- consumers: a warp owns G::kSub pairs of tile rows, a lane 4 cells of each row of its pair ---- */
+    const int r0 = 2 * (warp * G::kSub + sub);
+    const int x0 = t.x0 + xl * kVec;
+    const int y0 = t.y0 + r0;
+    const bool nearSphere = tile_near_sphere(P, t, G::kW, G::kR, z0, z1);
+    /* x wrap by load: which lane's vector holds cell x = sx (patchK = its index there), or is it the last lane's east read? */
     const int patchK = (sideR && x0 <= P.sx && P.sx < x0 + kVec) ? P.sx - x0 : -1;
     const bool eSide = sideR && x0 + kVec == P.sx;
     /* Nothing of the fusion lives in the plane loop: face cells are copied to the neighbours by push_tile_yz() and
@@ -504,13 +510,13 @@ __global__ void __launch_bounds__(kTmaThreads, MINB)
     unsigned phase = 0;
     auto plane = [&](const int i, float4 (&below)[2]) { // `below` holds plane i-2 on entry and plane i on exit
       mbar_wait(&full[s], phase);
-      const float *pl = reinterpret_cast<const float *>(smem + s * kTmaStageBytes);
-      /* smem row j holds compute row ty*rows + j - 1; smem column 4 + k holds compute x = tx*128 + k */
-      const float *rowC0 = pl + (r0 + 1) * kTmaBoxX + 4 + lane * kVec;
+      const float *pl = reinterpret_cast<const float *>(smem + s * G::kStageBytes);
+      /* smem row j holds compute row t.y0 + j - 1; smem column 4 + k holds compute x = t.x0 + k */
+      const float *rowC0 = pl + (r0 + 1) * G::kBoxX + 4 + xl * kVec;
       float4 c0 = *reinterpret_cast<const float4 *>(rowC0);
-      float4 c1 = *reinterpret_cast<const float4 *>(rowC0 + kTmaBoxX);
-      const float *sL = reinterpret_cast<const float *>(smem + kTmaSideOffset + s * kSideBytes) + r0 * kSideBoxX;
-      const float *sR = reinterpret_cast<const float *>(smem + kTmaSideOffset + (kTmaStages + s) * kSideBytes) + r0 * kSideBoxX;
+      float4 c1 = *reinterpret_cast<const float4 *>(rowC0 + G::kBoxX);
+      const float *sL = reinterpret_cast<const float *>(smem + G::kSideOffset + s * G::kSideBytes) + r0 * kSideBoxX;
+      const float *sR = reinterpret_cast<const float *>(smem + G::kSideOffset + (kTmaStages + s) * G::kSideBytes) + r0 * kSideBoxX;
       if (patchK >= 0) { // my vector contains cell x = sx: it is cell 0 of the row
         const float v0 = sR[0], v1 = sR[kSideBoxX];
         if (patchK == 0) c0.x = v0, c1.x = v1;
@@ -518,17 +524,17 @@ __global__ void __launch_bounds__(kTmaThreads, MINB)
         else if (patchK == 2) c0.z = v0, c1.z = v1;
         else c0.w = v0, c1.w = v1;
       }
-      const float4 south = *reinterpret_cast<const float4 *>(rowC0 - kTmaBoxX);     // y-1 of row r0
-      const float4 north = *reinterpret_cast<const float4 *>(rowC0 + 2 * kTmaBoxX); // y+1 of row r1
-      float w0 = __shfl_up_sync(0xffffffffu, c0.w, 1), e0 = __shfl_down_sync(0xffffffffu, c0.x, 1);
-      float w1 = __shfl_up_sync(0xffffffffu, c1.w, 1), e1 = __shfl_down_sync(0xffffffffu, c1.x, 1);
-      if (lane == 0) {
+      const float4 south = *reinterpret_cast<const float4 *>(rowC0 - G::kBoxX);     // y-1 of row r0
+      const float4 north = *reinterpret_cast<const float4 *>(rowC0 + 2 * G::kBoxX); // y+1 of row r1
+      float w0 = __shfl_up_sync(0xffffffffu, c0.w, 1, LW), e0 = __shfl_down_sync(0xffffffffu, c0.x, 1, LW);
+      float w1 = __shfl_up_sync(0xffffffffu, c1.w, 1, LW), e1 = __shfl_down_sync(0xffffffffu, c1.x, 1, LW);
+      if (xl == 0) {
         w0 = sideL ? sL[(P.sx - 1) & 3] : rowC0[-1];
-        w1 = sideL ? sL[kSideBoxX + ((P.sx - 1) & 3)] : rowC0[kTmaBoxX - 1];
+        w1 = sideL ? sL[kSideBoxX + ((P.sx - 1) & 3)] : rowC0[G::kBoxX - 1];
       }
-      if (lane == 31) {
+      if (xl == LW - 1) {
         e0 = eSide ? sR[0] : rowC0[kVec];
-        e1 = eSide ? sR[kSideBoxX] : rowC0[kTmaBoxX + kVec];
+        e1 = eSide ? sR[kSideBoxX] : rowC0[G::kBoxX + kVec];
       }
       /* this stage's data is in registers now: hand the slot back before doing the arithmetic and the stores */
       __syncwarp();
@@ -586,16 +592,29 @@ __global__ void __launch_bounds__(kTmaThreads, MINB)
     __syncthreads();
     {
       const unsigned yz = (P.debugSkip & 4u) ? 0u : (t.faces & ~((1u << XM) | (1u << XP)));
-      if (yz && z1 > z0) push_tile_yz(P, yz, t.tx * kTileX, t.ty * kTmaRows, z0, z1);
+      if (yz && z1 > z0) push_tile_yz(P, yz, t.x0, t.y0, G::kW, G::kR, z0, z1);
     }
-    if (!(P.debugSkip & 2u) && (t.faces & ((1u << XM) | (1u << XP))) && z1 > z0) push_tile_x(P, t.faces, t.ty * kTmaRows, z0, z1);
-    /* only tiles that stored into ANOTHER GPU take part in the completion count (same-GPU neighbours are ordered by
+    if (!(P.debugSkip & 2u) && (t.faces & ((1u << XM) | (1u << XP))) && z1 > z0) push_tile_x(P, t.faces, t.y0, G::kR, z0, z1);
+    /* only tiles that stored into ANOTHER GPU take part in the completion counts (same-GPU neighbours are ordered by
        the stream, or are this very kernel when an axis wraps onto the subdomain itself) */
     if ((t.faces & P.flagMask) && !(P.debugSkip & 1u)) {
       __syncthreads();
-      signal_neighbours(P);
+      signal_faces(P, t.faces & P.flagMask);
     }
   }
+}
+
+template <bool FUSED, int MINB>
+__global__ void __launch_bounds__(kTmaThreads, MINB)
+    jacobi7_tma_kernel(const __grid_constant__ CUtensorMap tmapWide, const __grid_constant__ CUtensorMap tmapNarrow,
+                       const __grid_constant__ CUtensorMap tmapSideWide, const __grid_constant__ CUtensorMap tmapSideNarrow,
+                       const __grid_constant__ JacobiParams P) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  const Tile t = P.tiles[blockIdx.x];
+  if (t.narrow)
+    tma_tile<FUSED, Narrow>(smem, &tmapNarrow, &tmapSideNarrow, P, t);
+  else
+    tma_tile<FUSED, Wide>(smem, &tmapWide, &tmapSideWide, P, t);
 }
 
 __global__ void div6_check_kernel(const float *in, unsigned *mismatches, int n) {
@@ -628,8 +647,8 @@ struct Jacobi3D::Impl {
   struct Dom {
     RcStream stream;
     cudaEvent_t done = nullptr, t0 = nullptr, t1 = nullptr;
-    Tile *tilesAll = nullptr; // whole compute region, boundary tiles first
-    unsigned nAll = 0, nBoundary = 0;
+    Tile *tilesAll = nullptr; // whole compute region, tiles that push to another GPU first
+    unsigned nAll = 0, nFace[6] = {0, 0, 0, 0, 0, 0};
     Tile *tilesInterior = nullptr;
     unsigned nInterior = 0;
     std::vector<std::pair<Tile *, unsigned>> tilesExterior;
@@ -646,12 +665,12 @@ struct Jacobi3D::Impl {
     bool kernelRecorded[2] = {false, false}, outRecorded[2] = {false, false};
     unsigned ioSteps = 0;
     JacobiParams base[2]; // per parity: src = buffer[parity]
-    CUtensorMap tmap[2];  // per parity: the curr buffer as a 3-D tensor (padded row, rows, planes)
-    CUtensorMap tmapSide[2]; // same tensor, 4 x 16 box: the cells at the other end of the rows (x wrap by load)
+    /* per parity: the curr buffer as a 3-D tensor (padded row, rows, planes) with the box of a wide tile, of a narrow
+       tile, and the 4-cell-wide boxes at the other end of the rows (x wrap by load) for both shapes */
+    CUtensorMap tmap[2], tmapNarrow[2], tmapSide[2], tmapSideNarrow[2];
     bool wrapLoad = false;
     std::vector<int> sameDevDeps;
     WaitSet finalWait;
-    CopyPlan scatter; // my x-side mailboxes -> the x halos of `next` (faces whose neighbour is on another GPU)
   };
   std::vector<Dom> doms;
   unsigned iter = 0;
@@ -665,37 +684,67 @@ struct Jacobi3D::Impl {
 
 namespace {
 
-/* tiles covering region [lo,hi) (compute coordinates) of a subdomain of size sz; faceMask selects which subdomain
-   faces push (0 for non-fused launches). Boundary tiles are emitted first. */
-std::vector<Tile> make_tiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int rows, int tileZ, unsigned faceMask, unsigned *nBoundary,
-                             bool boundaryFirst = false, unsigned countMask = 0) {
-  std::vector<Tile> boundary, inner;
-  unsigned nb = 0;
-  if (hi.x <= lo.x || hi.y <= lo.y || hi.z <= lo.z) {
-    if (nBoundary) *nBoundary = 0;
-    return inner;
+/* Tiles covering region [lo,hi) (compute coordinates) of a subdomain of size sz. faceMask selects which subdomain
+   faces push (0 for non-fused launches); countMask the faces whose neighbour is another GPU, nFace[f] receives the
+   number of tiles that push through face f to such a neighbour. With `narrow` (TMA variant) the part of a row that is
+   left after the last full 128-cell tile is covered by 32 x 64 tiles when it is at most kNarrowMaxRemainder cells.
+
+   Order. Natural (z, y, x) order keeps tiles that share halo rows / planes / margins resident together, so those
+   re-reads hit L2 (putting ALL pushing tiles first, x faces included, measured +160 MB of DRAM reads per 512^3
+   iteration). Tiles that push to another GPU are moved to the front all the same — z faces (whole layers, which keep
+   their locality) first, then the y / x face tiles of the other layers in z order: a face is announced to its
+   neighbour as soon as its last tile retires, i.e. within the first fifth of the kernel, so the neighbour's next
+   kernel — whose first tiles are exactly the ones that need that face — never waits for the END of this one, and the
+   GPUs may drift by most of an iteration without anybody spinning. Cost: two planes per z face and one row per y-face
+   tile lose their L2 hit (< 1 % of the traffic). */
+std::vector<Tile> make_tiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int rows, int tileZ, unsigned faceMask, unsigned *nFace,
+                             bool narrow, bool flaggedFirst = true, unsigned countMask = 0) {
+  std::vector<Tile> out;
+  if (nFace)
+    for (int f = 0; f < 6; ++f) nFace[f] = 0;
+  if (hi.x <= lo.x || hi.y <= lo.y || hi.z <= lo.z) return out;
+  /* columns of tiles: (x0, narrow?) */
+  std::vector<std::pair<int64_t, bool>> cols;
+  for (int64_t x = lo.x / kTileX * kTileX; x < hi.x;) {
+    const int64_t left = std::min<int64_t>(hi.x, sz.x) - x;
+    if (narrow && left <= kNarrowMaxRemainder) {
+      /* skip 32-cell columns that lie wholly before lo.x (regions that start inside a tile) */
+      if (x + Narrow::kW > lo.x) cols.emplace_back(x, true);
+      x += Narrow::kW;
+    } else {
+      cols.emplace_back(x, false);
+      x += kTileX;
+    }
   }
-  for (int64_t tz = lo.z / tileZ; tz * tileZ < hi.z; ++tz)
-    for (int64_t ty = lo.y / rows; ty * rows < hi.y; ++ty)
-      for (int64_t tx = lo.x / kTileX; tx * kTileX < hi.x; ++tx) {
-        unsigned f = 0;
-        if (tx == 0) f |= 1u << XM;
-        if (tx * kTileX <= sz.x - 1 && sz.x - 1 < (tx + 1) * kTileX) f |= 1u << XP;
-        if (ty == 0) f |= 1u << YM;
-        if (ty * rows <= sz.y - 1 && sz.y - 1 < (ty + 1) * rows) f |= 1u << YP;
-        if (tz == 0) f |= 1u << ZM;
-        if (tz * tileZ <= sz.z - 1 && sz.z - 1 < (tz + 1) * tileZ) f |= 1u << ZP;
-        f &= faceMask;
-        const Tile t{(unsigned short)tx, (unsigned short)ty, (unsigned short)tz, (unsigned short)f};
-        if (f & countMask) ++nb; // tiles that store into another GPU and therefore take part in the completion count
-        /* Natural (z, y, x) order keeps tiles that share halo rows / planes / margins resident together, so those
-           re-reads hit L2. Scheduling the pushing tiles first costs that locality (measured on B200: +160 MB of DRAM
-           reads and +50 us per 512^3 iteration) and buys nothing while all GPUs run in step. */
-        (f && boundaryFirst ? boundary : inner).push_back(t);
-      }
-  if (nBoundary) *nBoundary = nb;
-  boundary.insert(boundary.end(), inner.begin(), inner.end());
-  return boundary;
+  auto emit = [&](int64_t tz, int64_t x0, int64_t y0, int64_t w, int64_t r, bool nar) {
+    unsigned f = 0;
+    if (x0 == 0) f |= 1u << XM;
+    if (x0 <= sz.x - 1 && sz.x - 1 < x0 + w) f |= 1u << XP;
+    if (y0 == 0) f |= 1u << YM;
+    if (y0 <= sz.y - 1 && sz.y - 1 < y0 + r) f |= 1u << YP;
+    if (tz == 0) f |= 1u << ZM;
+    if (tz * tileZ <= sz.z - 1 && sz.z - 1 < (tz + 1) * tileZ) f |= 1u << ZP;
+    f &= faceMask;
+    if (nFace)
+      for (int k = 0; k < 6; ++k)
+        if ((f & countMask) >> k & 1u) ++nFace[k];
+    out.push_back(Tile{int(x0), int(y0), (unsigned short)tz, (unsigned char)f, (unsigned char)(nar ? 1 : 0)});
+  };
+  for (int64_t tz = lo.z / tileZ; tz * tileZ < hi.z; ++tz) {
+    /* wide columns row block by row block, then the narrow columns (their row blocks are four times as tall) */
+    for (int64_t y0 = lo.y / rows * rows; y0 < hi.y; y0 += rows)
+      for (const auto &c : cols)
+        if (!c.second) emit(tz, c.first, y0, kTileX, rows, false);
+    for (int64_t y0 = lo.y / Narrow::kR * Narrow::kR; y0 < hi.y; y0 += Narrow::kR)
+      for (const auto &c : cols)
+        if (c.second) emit(tz, c.first, y0, Narrow::kW, Narrow::kR, true);
+  }
+  if (flaggedFirst && countMask) {
+    const unsigned zbits = (1u << ZM) | (1u << ZP);
+    auto prio = [&](const Tile &t) { return (t.faces & countMask & zbits) ? 0 : ((t.faces & countMask) ? 1 : 2); };
+    std::stable_sort(out.begin(), out.end(), [&](const Tile &a, const Tile &b) { return prio(a) < prio(b); });
+  }
+  return out;
 }
 
 Tile *upload(const std::vector<Tile> &t) {
@@ -706,10 +755,9 @@ Tile *upload(const std::vector<Tile> &t) {
   return d;
 }
 
-/* fp32 tensor over one padded buffer: dims (row pitch, rows, planes), box = one input plane of a tile */
-CUtensorMap make_plane_map(void *bufferStart, const Dim3 &pitch, const Dim3 &raw) {
-  return tma::make_plane_map(bufferStart, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, sizeof(float), pitch.x, raw.y, raw.z, unsigned(kTmaBoxX),
-                             unsigned(kTmaBoxY));
+/* fp32 tensor over one padded buffer: dims (row pitch, rows, planes), box = boxX x boxY cells of one plane */
+CUtensorMap make_plane_map(void *bufferStart, const Dim3 &pitch, const Dim3 &raw, int boxX, int boxY) {
+  return tma::make_plane_map(bufferStart, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, sizeof(float), pitch.x, raw.y, raw.z, unsigned(boxX), unsigned(boxY));
 }
 
 const Dim3 kFaceDir[6] = {Dim3(-1, 0, 0), Dim3(1, 0, 0), Dim3(0, -1, 0), Dim3(0, 1, 0), Dim3(0, 0, -1), Dim3(0, 0, 1)};
@@ -721,6 +769,12 @@ Jacobi3D::Jacobi3D(size_t x, size_t y, size_t z, const Options &opt, Comm &comm)
 
 Jacobi3D::~Jacobi3D() {
   if (impl_) {
+    /* a neighbour's last iteration may still be storing into my `next` halo and flags: wait for its final flags and
+       let every rank arrive before any IPC-exported slab is freed */
+    if (dd_) {
+      if (*impl_->err == 0) sync();
+      dd_->comm().barrier();
+    }
     for (size_t di = 0; di < impl_->doms.size(); ++di) {
       Impl::Dom &d = impl_->doms[di];
       DevGuard g(dd_->domains()[di].gpu());
@@ -748,7 +802,8 @@ Jacobi3D::~Jacobi3D() {
 void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
   if (opt_.tileZ < 1) opt_.tileZ = 32;
   if (opt_.useTma && opt_.tileZ > kMaxTileZ) opt_.tileZ = kMaxTileZ;
-  if (std::getenv("STENCIL_JACOBI_XMAILBOX")) opt_.xMailbox = true;
+  if (std::getenv("STENCIL_JACOBI_NATURAL_ORDER")) opt_.flaggedFirst = false;
+  if (std::getenv("STENCIL_JACOBI_NO_NARROW")) opt_.narrowTiles = false;
   dd_.reset(comm ? new DistributedDomain(x, y, z, *comm) : new DistributedDomain(x, y, z));
   if (!opt_.gpus.empty()) dd_->set_gpus(opt_.gpus);
   Radius radius = Radius::constant(0);
@@ -810,8 +865,8 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
     CUDA_RUNTIME(cudaEventCreateWithFlags(&d.done, cudaEventDisableTiming));
     CUDA_RUNTIME(cudaEventCreate(&d.t0));
     CUDA_RUNTIME(cudaEventCreate(&d.t1));
-    CUDA_RUNTIME(cudaMalloc(&d.doneCounter, sizeof(unsigned)));
-    CUDA_RUNTIME(cudaMemset(d.doneCounter, 0, sizeof(unsigned)));
+    CUDA_RUNTIME(cudaMalloc(&d.doneCounter, 8 * sizeof(unsigned)));
+    CUDA_RUNTIME(cudaMemset(d.doneCounter, 0, 8 * sizeof(unsigned)));
     {
       float init[kDynBytes / sizeof(float)] = {1.0f, 0.0f}; // HOT_TEMP, COLD_TEMP of the reference
       CUDA_RUNTIME(cudaMalloc(&d.dyn, 2 * kDynBytes));
@@ -841,35 +896,22 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
         if (nbs[f].sameRank && nbs[f].sameDevice && nbs[f].dom != int(di)) deps.insert(nbs[f].dom);
       }
     /* x wrap by load instead of x halo pushes: both x neighbours are this very subdomain */
-    d.wrapLoad = opt_.mode == Mode::Fused && impl_->useTma && !opt_.xMailbox && !std::getenv("STENCIL_JACOBI_NO_WRAP_LOAD") && nbs[XM].exists &&
+    d.wrapLoad = opt_.mode == Mode::Fused && impl_->useTma && !std::getenv("STENCIL_JACOBI_NO_WRAP_LOAD") && nbs[XM].exists &&
                  nbs[XP].exists && nbs[XM].sameRank && nbs[XP].sameRank && nbs[XM].dom == int(di) && nbs[XP].dom == int(di) && sz.x >= kSideBoxX;
     if (d.wrapLoad) faceMask &= ~((1u << XM) | (1u << XP));
     d.sameDevDeps.assign(deps.begin(), deps.end());
-    if (opt_.mode == Mode::Fused && impl_->useTma && opt_.xMailbox) {
-      for (int f = XM; f <= XP; ++f) {
-        if (!nbs[f].exists || nbs[f].sameDevice) continue;
-        /* what the neighbour on side f put into my mailbox belongs in the x halo of `next` on that side */
-        const Dim3 side = kFaceDir[f], ext = ld.halo_extent(side);
-        BoxView src = BoxView::dense(static_cast<char *>(ld.slab()) + ld.mailbox_offset(side, h_.id(), 0), ext, sizeof(float));
-        src.base[1] = static_cast<char *>(ld.slab()) + ld.mailbox_offset(side, h_.id(), 1);
-        BoxView dst = ld.view(h_.id());
-        std::swap(dst.base[0], dst.base[1]); // parity p selects curr = buffer p; the target is next = buffer p^1
-        d.scatter.add(src, Dim3(0, 0, 0), dst, ld.halo_pos(side, true), ext);
-      }
-      d.scatter.finalize(ld.gpu());
-    }
-
     const int rows = impl_->rows;
-    const std::vector<Tile> all = make_tiles(Dim3(0, 0, 0), sz, sz, rows, opt_.tileZ, faceMask, &d.nBoundary, opt_.boundaryFirst, flagMask);
+    const bool narrow = impl_->useTma && opt_.narrowTiles;
+    const std::vector<Tile> all = make_tiles(Dim3(0, 0, 0), sz, sz, rows, opt_.tileZ, faceMask, d.nFace, narrow, opt_.flaggedFirst, flagMask);
     d.tilesAll = upload(all);
     d.nAll = unsigned(all.size());
     d.interior = interiors[di];
     d.exterior = exteriors[di];
-    const std::vector<Tile> in = make_tiles(d.interior.lo - org, d.interior.hi - org, sz, rows, opt_.tileZ, 0, nullptr);
+    const std::vector<Tile> in = make_tiles(d.interior.lo - org, d.interior.hi - org, sz, rows, opt_.tileZ, 0, nullptr, narrow);
     d.tilesInterior = upload(in);
     d.nInterior = unsigned(in.size());
     for (const Rect3 &r : d.exterior) {
-      const std::vector<Tile> ex = make_tiles(r.lo - org, r.hi - org, sz, rows, opt_.tileZ, 0, nullptr);
+      const std::vector<Tile> ex = make_tiles(r.lo - org, r.hi - org, sz, rows, opt_.tileZ, 0, nullptr, narrow);
       d.tilesExterior.emplace_back(upload(ex), unsigned(ex.size()));
     }
 
@@ -895,9 +937,11 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
         const char *bufStart = static_cast<const char *>(ld.slab()) + ld.buffer_start_offset(h_.id(), parity);
         P.tmaX0 = int(ld.lead_elems(h_.id())) + 1;
         if (impl_->useTma) {
-          d.tmap[parity] = make_plane_map(const_cast<char *>(bufStart), pitch, ld.raw_size());
-          d.tmapSide[parity] = tma::make_plane_map(const_cast<char *>(bufStart), CU_TENSOR_MAP_DATA_TYPE_FLOAT32, sizeof(float), pitch.x,
-                                                   ld.raw_size().y, ld.raw_size().z, unsigned(kSideBoxX), unsigned(kTmaRows));
+          char *b = const_cast<char *>(bufStart);
+          d.tmap[parity] = make_plane_map(b, pitch, ld.raw_size(), Wide::kBoxX, Wide::kBoxY);
+          d.tmapNarrow[parity] = make_plane_map(b, pitch, ld.raw_size(), Narrow::kBoxX, Narrow::kBoxY);
+          d.tmapSide[parity] = make_plane_map(b, pitch, ld.raw_size(), kSideBoxX, Wide::kR);
+          d.tmapSideNarrow[parity] = make_plane_map(b, pitch, ld.raw_size(), kSideBoxX, Narrow::kR);
         }
         P.wrapLoad = d.wrapLoad ? 1 : 0;
       }
@@ -912,10 +956,10 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
       P.r2 = (R + 1) * (R + 1);
       P.tiles = d.tilesAll;
       P.dyn = d.dyn;
-      P.nBoundary = d.nBoundary;
+      for (int f = 0; f < 6; ++f) P.nFace[f] = d.nFace[f];
       P.done = d.doneCounter;
       P.err = impl_->err;
-      P.timeoutNs = 5000000000ull;
+      P.timeoutNs = flag_timeout_ns();
       for (int f = 0; f < 6; ++f) {
         if (!(faceMask & (1u << f))) continue;
         const NeighborInfo &n = nbs[f];
@@ -936,11 +980,6 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
         P.nb[f] = nbase + (rz * npxy + ry * npx + rx);
         P.nbPitchX[f] = npx;
         P.nbPitchXY[f] = npxy;
-        if ((f == XM || f == XP) && impl_->useTma && opt_.xMailbox && !n.sameDevice) {
-          /* my x = 0 cells are the neighbour's +x halo, my last x its -x halo; mailbox parity = buffer parity */
-          const Dim3 side = kFaceDir[f] * -1;
-          P.mbox[f] = reinterpret_cast<float *>(n.slab + n.layout->mailbox_offset(side, h_.id(), parity));
-        }
         const bool viaFlag = !(n.sameRank && n.sameDevice);
         if (viaFlag) {
           P.flagMask |= 1u << f;
@@ -998,7 +1037,8 @@ void Jacobi3D::step() {
       const int mb = impl_->minBlocksForced ? impl_->minBlocks : 2;
       auto *k = fused ? (mb == 3 ? &jacobi7_tma_kernel<true, 3> : &jacobi7_tma_kernel<true, 2>)
                       : (mb == 3 ? &jacobi7_tma_kernel<false, 3> : &jacobi7_tma_kernel<false, 2>);
-      (*k)<<<n, kTmaThreads, kTmaSmemBytes, d.stream>>>(d.tmap[ld.parity()], d.tmapSide[ld.parity()], P);
+      const int pa = ld.parity();
+      (*k)<<<n, kTmaThreads, kTmaSmemBytes, d.stream>>>(d.tmap[pa], d.tmapNarrow[pa], d.tmapSide[pa], d.tmapSideNarrow[pa], P);
     } else if (fused) {
       jacobi7_kernel<true><<<n, kThreads, 0, d.stream>>>(P);
     } else {
@@ -1019,12 +1059,6 @@ void Jacobi3D::step() {
       DevGuard g(doms[di].gpu());
       Impl::Dom &d = impl_->doms[di];
       launch(di, d.tilesAll, d.nAll, doms[di].get_compute_region(), true);
-      if (!d.scatter.empty()) {
-        /* x faces from other GPUs arrive in my mailbox: once their flags are up, move them into the halo of `next` */
-        launch_wait_flags(d.finalWait, impl_->iter, impl_->err, 5000000000ull, d.stream);
-        d.scatter.launch(doms[di].parity(), d.stream);
-        launches_ += 2;
-      }
       if (!d.sameDevDeps.empty() || nd > 1) CUDA_RUNTIME(cudaEventRecord(d.done, d.stream));
     }
     dd_->swap();
@@ -1098,7 +1132,7 @@ void Jacobi3D::sync() {
     DevGuard g(doms[di].gpu());
     Impl::Dom &d = impl_->doms[di];
     /* fused: my halos of the final iteration are complete only when every neighbour raised its last flag */
-    if (opt_.mode == Mode::Fused && impl_->iter > 0) launch_wait_flags(d.finalWait, impl_->iter, impl_->err, 5000000000ull, d.stream);
+    if (opt_.mode == Mode::Fused && impl_->iter > 0) launch_wait_flags(d.finalWait, impl_->iter, impl_->err, flag_timeout_ns(), d.stream);
     CUDA_RUNTIME(cudaStreamSynchronize(d.stream));
     CUDA_RUNTIME(cudaStreamSynchronize(d.ioOut));
   }

@@ -68,13 +68,13 @@ struct Where {
 int staged_tag(int srcDom, int dstDom) { return (1 << 24) | ((srcDom & 0xFF) << 8) | (dstDom & 0xFF); }
 int ack_tag(int payload) { return (2 << 24) | (payload & 0xFFFF); }
 
+} // namespace
+
 unsigned long long flag_timeout_ns() {
   const char *e = std::getenv("STENCIL_FLAG_TIMEOUT_MS");
   const double ms = e ? std::atof(e) : 5000.0;
-  return (unsigned long long)(ms * 1e6);
+  return (unsigned long long)((ms > 0 ? ms : 5000.0) * 1e6);
 }
-
-} // namespace
 
 /* ------------------------------------------------------------------------------------------------------------ */
 
@@ -948,10 +948,14 @@ void DistributedDomain::realize() {
   t = stencil::Comm::wtime();
   {
     STENCIL_RANGE("peer_en");
+    /* peer access between the GPUs of THIS process (both directions: the loop visits every ordered pair); GPUs of
+       other processes are only noted as reachable — their slabs arrive as IPC mappings that enable access lazily */
     for (int src : gpus_)
       for (int dst : nodeCuda) {
-        gpu_topo::enable_peer(src, dst);
-        gpu_topo::enable_peer(dst, src);
+        if (std::find(gpus_.begin(), gpus_.end(), dst) != gpus_.end())
+          gpu_topo::enable_peer(src, dst);
+        else
+          gpu_topo::note_peer(src, dst);
       }
   }
   timePeerEn_ += setup_phase_seconds(*comm_, stencil::Comm::wtime() - t);

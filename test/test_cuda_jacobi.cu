@@ -26,9 +26,10 @@ std::vector<float> gather(stencil::Jacobi3D &j) {
 }
 
 size_t mismatches(const Dim3 &size, stencil::Jacobi3D::Mode mode, const std::vector<int> &gpus, int iters, int tileZ = 32,
-                  MethodFlags methods = MethodFlags::All, bool xMailbox = false) {
+                  MethodFlags methods = MethodFlags::All, bool narrowTiles = true, bool flaggedFirst = true) {
   stencil::Jacobi3D::Options opt;
-  opt.xMailbox = xMailbox;
+  opt.narrowTiles = narrowTiles;
+  opt.flaggedFirst = flaggedFirst;
   opt.mode = mode;
   opt.gpus = gpus;
   opt.tileZ = tileZ;
@@ -109,6 +110,25 @@ TEST_CASE("jacobi: one subdomain, all schedules, bit exact", "[cuda][jacobi]") {
   }
 }
 
+TEST_CASE("jacobi: rows that are not a multiple of the 128-cell tile use 32 x 64 remainder tiles", "[cuda][jacobi][narrow]") {
+  using M = stencil::Jacobi3D::Mode;
+  for (M m : {M::Fused, M::Overlap, M::NoOverlap}) {
+    REQUIRE(mismatches(Dim3(133, 70, 20), m, {0}, 4, 8) == 0);    // one wide column + one narrow column, two narrow row blocks
+    REQUIRE(mismatches(Dim3(70, 130, 12), m, {0}, 4, 4) == 0);    // narrow columns only (0, 32, 64), three row blocks
+    REQUIRE(mismatches(Dim3(200, 65, 10), m, {0, 0}, 4, 8) == 0); // remainder 72: three narrow columns; y cut across subdomains
+    REQUIRE(mismatches(Dim3(230, 20, 18), m, {0}, 3, 8) == 0);    // remainder 102 > 96: a second wide column instead
+    REQUIRE(mismatches(Dim3(132, 64, 9), m, {0}, 3, 4) == 0);     // remainder is exactly one vector
+  }
+  /* same sizes with the remainder tiles switched off agree as well */
+  REQUIRE(mismatches(Dim3(133, 70, 20), M::Fused, {0}, 4, 8, MethodFlags::All, false) == 0);
+  /* x cut across subdomains (no wrap by load: x halos are pushed by narrow tiles too) */
+  const stencil::detail::TieBreak saved = partition_tie_break();
+  set_partition_tie_break(stencil::detail::TieBreak::X);
+  const size_t bad = mismatches(Dim3(330, 70, 12), M::Fused, {0, 0}, 5, 4);
+  set_partition_tie_break(saved);
+  REQUIRE(bad == 0);
+}
+
 TEST_CASE("jacobi: 2, 3, 4 and 8 subdomains on GPU 0", "[cuda][jacobi]") {
   using M = stencil::Jacobi3D::Mode;
   for (M m : {M::Fused, M::Overlap, M::NoOverlap}) {
@@ -158,13 +178,14 @@ TEST_CASE("jacobi: every visible GPU, fused NVLink pushes", "[cuda][jacobi][mult
     const stencil::detail::TieBreak saved = partition_tie_break();
     set_partition_tie_break(stencil::detail::TieBreak::X);
     const size_t bad = mismatches(Dim3(70, 40, 36), M::Fused, gpus, 8, 8);
-    /* ... and the optional variant that sends those faces as dense runs through the neighbour's mailbox */
-    const size_t badMailbox = mismatches(Dim3(70, 40, 36), M::Fused, gpus, 8, 8, MethodFlags::All, true);
+    /* ... and with wide tiles only, in natural tile order */
+    const size_t badWide = mismatches(Dim3(70, 40, 36), M::Fused, gpus, 8, 8, MethodFlags::All, false, false);
     set_partition_tie_break(saved);
     REQUIRE(bad == 0);
-    REQUIRE(badMailbox == 0);
+    REQUIRE(badWide == 0);
   }
   REQUIRE(mismatches(Dim3(70, 40, 36), M::Fused, gpus, 8, 8) == 0);
+  REQUIRE(mismatches(Dim3(333, 150, 90), M::Fused, gpus, 12, 8) == 0); // wide + narrow tile columns, several row blocks
   REQUIRE(mismatches(Dim3(70, 40, 36), M::Overlap, gpus, 4, 8) == 0);
   std::vector<int> twice = gpus;
   twice.insert(twice.end(), gpus.begin(), gpus.end());
