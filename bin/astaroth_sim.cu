@@ -2,7 +2,7 @@
    CLI follows the reference's bin/astaroth_sim.cu:87-101 (--x --y --z default 512 = size per run, --remote
    --cuda-aware-mpi --colocated --peer --kernel --trivial, -f/--file accepted and unused). The reference runs exactly
    one fp32 field, 5 iterations and prints no timing; defaults here reproduce that workload, and the options
-   --fields N, --double, --star (real 19-point radius-3 stencil), --iters, --no-overlap, --weak (scale the size by
+   --fields N, --double, --star (real 19-point radius-3 stencil), --cross (that stencil plus cross-derivative terms), --iters, --no-overlap, --weak (scale the size by
    numGpus^0.33333 like the other apps) cover BASELINE's "8 fp64 fields, radius 3, 256^3 per GPU" config.
    Adds one CSV line on rank 0:
      astaroth-sim,<methods>,<ranks>,<devCount>,x,y,z,<fields>,<fp32|fp64>,<avg7|star19>,<iters>,<s per iter>,<exchange s per iter>,<Gcell/s> */
@@ -17,7 +17,7 @@ int main(int argc, char **argv) {
   size_t x = 512, y = 512, z = 512;
   int iters = 5, fields = 1;
   bool remote = false, cudaAware = false, colocated = false, peer = false, kernel = false, direct = false, trivial = false;
-  bool fp64 = false, star = false, noOverlap = false, forceOverlap = false, weak = false, check = false;
+  bool fp64 = false, star = false, cross = false, noOverlap = false, forceOverlap = false, weak = false, check = false;
   std::string file;
   argparse::Parser p("radius-3 multi-field stencil (Astaroth stand-in)");
   p.add_option(x, "--x");
@@ -36,6 +36,7 @@ int main(int argc, char **argv) {
   p.add_flag(fp64, "--double");
   p.add_flag(star, "--star");
   p.add_flag(star, "--star19")->help("same as --star (torchrun's parser mistakes --star for an abbreviation of its --start-method)");
+  p.add_flag(cross, "--cross")->help("19-point stencil plus cross-derivative terms: reads edge and corner halos too");
   p.add_flag(noOverlap, "--no-overlap");
   p.add_flag(forceOverlap, "--overlap")->help("keep the interior/exterior schedule even where the engine would drop it");
   p.add_flag(weak, "--weak");
@@ -72,7 +73,7 @@ int main(int argc, char **argv) {
     opt.placement = trivial ? PlacementStrategy::Trivial : PlacementStrategy::NodeAware;
     opt.fields = fields;
     opt.fp64 = fp64;
-    opt.stencil = star ? stencil::AstarothSim::Stencil::Star19 : stencil::AstarothSim::Stencil::Average7;
+    opt.stencil = cross ? stencil::AstarothSim::Stencil::Star19Cross : (star ? stencil::AstarothSim::Stencil::Star19 : stencil::AstarothSim::Stencil::Average7);
     opt.overlap = !noOverlap;
     opt.autoSchedule = !forceOverlap;
     opt.planFile = true;
@@ -93,7 +94,7 @@ int main(int argc, char **argv) {
           if (first[i] == first[i]) ref[i] = first[i]; // my cells: bit-identical start (device sin differs in the last ulp)
         for (int it = 0; it < iters; ++it) {
           sim.step();
-          stencil::astaroth_host_step(tmp, ref, size, opt.stencil, fp64, opt.dt);
+          stencil::astaroth_host_step(tmp, ref, size, opt.stencil, fp64, opt.dt, opt.crossWeight);
           ref.swap(tmp);
         }
         const std::vector<double> got = sim.gather(f);
@@ -118,7 +119,7 @@ int main(int argc, char **argv) {
   }
   if (job.rank == 0)
     std::cout << "astaroth-sim," << method_string(methods) << "," << job.size << "," << job.devCount << "," << x << "," << y << "," << z << ","
-              << fields << "," << (fp64 ? "fp64" : "fp32") << "," << (star ? "star19" : "avg7") << "," << iters << "," << perIter << ","
+              << fields << "," << (fp64 ? "fp64" : "fp32") << "," << (cross ? "star19cross" : (star ? "star19" : "avg7")) << "," << iters << "," << perIter << ","
               << exPerIter << "," << double(x) * double(y) * double(z) / perIter / 1e9 << "\n";
   stencil::finalize_world();
   return 0;

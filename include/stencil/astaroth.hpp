@@ -17,7 +17,10 @@ namespace stencil {
 
 class AstarothSim {
 public:
-  enum class Stencil { Average7, Star19 };
+  /* Star19Cross = Star19 plus cross-derivative terms (6th-order d2/dxdy, d2/dxdz, d2/dydz along the diagonals and a
+     d3/dxdydz corner term, weighted by Options::crossWeight): reads all 26 halo directions, as the mixed derivatives of
+     a real Astaroth right-hand side do */
+  enum class Stencil { Average7, Star19, Star19Cross };
   struct Options {
     MethodFlags methods = MethodFlags::All;
     PlacementStrategy placement = PlacementStrategy::NodeAware;
@@ -29,8 +32,12 @@ public:
                                // fill its tiles, and exchange() + one whole-region launch measured 1.8x faster on B200
     bool freeRunning = true; // without overlap and with device-only transports: exchange_async() + events, the host never waits
     bool fusedXFaces = true; // subdomains that wrap onto themselves in x: the kernel writes the +-x halos, exchange() skips them
-    bool fusedYZFaces = true; // ... and pushes its y / z face rows into the neighbours' halos (other GPUs over NVLink, flags as in
-                              // the fused Jacobi kernel): no exchange() left in steady state
+    bool fusedYZFaces = true; // ... and pushes its y / z face rows, its yz edge bundles and the x wrap of all of them (xy / xz
+                              // edges, corners) into the neighbours' halos (other GPUs over NVLink, flags as in the fused
+                              // Jacobi kernel): all 26 directions stay current with no exchange() left in steady state
+    bool narrowTiles = true;  // TMA kernel: cover the remainder of rows that are not a multiple of the tile with 8-lane tiles
+    bool flaggedFirst = true; // TMA kernel: schedule the tiles that push to ANOTHER GPU first
+    double crossWeight = 0.25; // Star19Cross: weight of the cross-derivative terms
     bool useTma = true; // Star19: TMA + mbarrier pipelined kernel for regions wide enough to fill its tiles
     std::vector<int> gpus;
     double period = 10;
@@ -48,9 +55,10 @@ public:
   /* one iteration: interior, exchange, exterior, synchronise, swap */
   void step();
   void sync();
-  /* `iters` iterations; returns host wall seconds (max over ranks) and, in *exchangeSeconds, the part spent inside
-     exchange() */
-  double run(int iters, double *exchangeSeconds = nullptr);
+  /* `iters` iterations; returns host wall seconds (max over ranks), in *exchangeSeconds the part spent inside
+     exchange(), and in *deviceSeconds the time between CUDA events recorded on every compute stream before the first and
+     after the last iteration (max over local GPUs and ranks) */
+  double run(int iters, double *exchangeSeconds = nullptr, double *deviceSeconds = nullptr);
   unsigned long long launches() const { return launches_; }
   /* dense host copy [z][y][x] of field f over the whole domain owned by this rank (NaN elsewhere), as double */
   std::vector<double> gather(int field);
@@ -66,7 +74,7 @@ private:
 
 /* host reference: one step of one field on a dense periodic array (same arithmetic order as the kernel) */
 void astaroth_host_step(std::vector<double> &next, const std::vector<double> &curr, const Dim3 &size, AstarothSim::Stencil st, bool fp64,
-                        double dt);
+                        double dt, double crossWeight = 0.25);
 /* the initial field value at a global coordinate */
 double astaroth_init_value(const Dim3 &p, double period, bool fp64);
 

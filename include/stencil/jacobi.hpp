@@ -45,8 +45,12 @@ public:
   const DataHandle<float> &handle() const { return h_; }
   Mode mode() const { return opt_.mode; }
 
-  /* curr = 0.5 on every compute region (halos are filled by the first exchange / fused step) */
+  /* curr = 0.5 on every compute region (halos are filled by the first exchange / fused step); also resets the
+     iteration count of the engine's flags hand-shake consistently on all ranks (collective) */
   void init();
+  /* curr = a pseudo-random value in [0,1) that depends only on `seed` and the cell's GLOBAL coordinate
+     (jacobi_random_value), so every partition and every schedule starts from the same field (collective) */
+  void init_random(unsigned seed);
   /* enqueue one iteration and swap. Fused mode does not block the host. */
   void step();
   /* One iteration with per-step host I/O, all stream-ordered (no host blocking): first copy `nbytes`
@@ -65,12 +69,17 @@ public:
 
   /* sum of curr over the compute regions of all ranks (fp64 accumulation) */
   double checksum();
+  /* 64-bit fingerprint of curr over the compute regions of all ranks: every cell's bit pattern is mixed with its
+     global coordinate and the results are added modulo 2^64, so the value does not depend on the partition or on the
+     order of summation, and two runs agree exactly when (up to a 2^-64 accident) every cell agrees bit for bit */
+  unsigned long long fingerprint();
   /* value at global coordinate p if this rank owns it (returns false otherwise) */
   bool probe(const Dim3 &p, float *out);
 
 private:
   struct Impl;
   void build(size_t x, size_t y, size_t z, Comm *comm);
+  void fill(bool random, unsigned seed);
   Options opt_;
   std::unique_ptr<DistributedDomain> dd_;
   DataHandle<float> h_;
@@ -80,6 +89,9 @@ private:
 
 /* test hook: how many of `values` does the kernel's 3-instruction x/6 round differently from IEEE division (expect 0) */
 unsigned jacobi_div6_mismatches(const std::vector<float> &values);
+
+/* the value init_random() gives global cell p of a domain of size `global` */
+float jacobi_random_value(unsigned seed, const Dim3 &p, const Dim3 &global);
 
 /* host reference of one Jacobi iteration on a dense periodic X*Y*Z array (same arithmetic and order as the kernel) */
 void jacobi_host_step(std::vector<float> &next, const std::vector<float> &curr, const Dim3 &size);

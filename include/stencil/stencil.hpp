@@ -188,6 +188,10 @@ public:
   Placement *placement() const noexcept { return placement_.get(); }
   /* the stream exchange() uses for local subdomain i (HIGH priority, on that subdomain's GPU) */
   cudaStream_t exchange_stream(size_t i) const;
+  /* `iters` blocking exchange() calls between barriers: returns the host wall seconds (max over ranks) and, in
+     *deviceSeconds (may be null), the device time between CUDA events recorded on every exchange stream before the
+     first and after the last call (max over local GPUs and ranks). What bin/weak_exchange.cu prints. */
+  double time_exchange(int iters, double *deviceSeconds = nullptr);
   /* number of completed exchange() calls (the epoch published in the arrival flags) */
   unsigned epoch() const noexcept;
   stencil::Exchanger *exchanger() const noexcept { return ex_.get(); }

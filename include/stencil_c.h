@@ -131,6 +131,12 @@ void *stencil_domain_exchange_done_event(const stencil_domain_t *dd, int subdoma
 int stencil_domain_exchange_after(stencil_domain_t *dd, int subdomain, void *cuda_event);
 int stencil_domain_swap(stencil_domain_t *dd);
 int stencil_domain_num_subdomains(const stencil_domain_t *dd);
+/* how the domain was cut: subdomains along x, y, z over the whole job (valid after realize) */
+int stencil_domain_grid(const stencil_domain_t *dd, int64_t grid_out[3]);
+/* `iters` blocking exchanges between barriers: returns host wall seconds (max over ranks); *device_seconds (may be
+   NULL) = time between CUDA events on every exchange stream around the calls (max over GPUs and ranks).
+   Reference: the loop bin/weak_exchange.cu times. */
+double stencil_domain_time_exchange(stencil_domain_t *dd, int iters, double *device_seconds);
 uint64_t stencil_domain_exchange_bytes(const stencil_domain_t *dd, int methods);
 int stencil_domain_write_paraview(stencil_domain_t *dd, const char *prefix, int zero_nans);
 /* geometry of local subdomain di */
@@ -154,11 +160,17 @@ stencil_jacobi_t *stencil_jacobi_create(uint64_t x, uint64_t y, uint64_t z, int 
                                         const int *gpus, int ngpus, int tile_z);
 void stencil_jacobi_destroy(stencil_jacobi_t *j);
 int stencil_jacobi_init(stencil_jacobi_t *j);
+/* initial field = pseudo-random values in [0,1) that depend only on seed and the global coordinate of the cell */
+int stencil_jacobi_init_random(stencil_jacobi_t *j, unsigned seed);
+float stencil_jacobi_random_value(unsigned seed, int64_t x, int64_t y, int64_t z, int64_t gx, int64_t gy, int64_t gz);
 int stencil_jacobi_step(stencil_jacobi_t *j);
 int stencil_jacobi_sync(stencil_jacobi_t *j);
 /* device-timed seconds for `iters` iterations: CUDA events per local GPU, max over GPUs and ranks */
 double stencil_jacobi_run(stencil_jacobi_t *j, int iters);
 double stencil_jacobi_checksum(stencil_jacobi_t *j);
+/* 64-bit fingerprint of the whole field (all ranks): independent of partition and schedule, equal exactly when every
+   cell agrees bit for bit (up to a 2^-64 accident) */
+uint64_t stencil_jacobi_fingerprint(stencil_jacobi_t *j);
 /* returns 1 and writes *out if this rank owns the cell, else 0 */
 int stencil_jacobi_probe(stencil_jacobi_t *j, int64_t x, int64_t y, int64_t z, float *out);
 uint64_t stencil_jacobi_launches(const stencil_jacobi_t *j);
@@ -176,6 +188,7 @@ int stencil_jacobi_host_step(float *next, const float *curr, int64_t x, int64_t 
 typedef struct stencil_astaroth stencil_astaroth_t;
 #define STENCIL_ASTAROTH_AVERAGE7 0 /* the reference's stand-in compute */
 #define STENCIL_ASTAROTH_STAR19 1   /* next = curr + dt * (6th-order 19-point Laplacian) */
+#define STENCIL_ASTAROTH_STAR19_CROSS 2 /* ... + 0.25 * (6th-order mixed second derivatives + a corner term): reads all 26 halo directions */
 /* overlap: 1 interior/exchange/exterior schedule, 0 exchange then one whole-region launch, -1 engine's choice */
 stencil_astaroth_t *stencil_astaroth_create(uint64_t x, uint64_t y, uint64_t z, int methods, int placement, int stencil_kind, int fields,
                                             int fp64, int overlap, const int *gpus, int ngpus, double dt);
@@ -185,6 +198,8 @@ int stencil_astaroth_step(stencil_astaroth_t *a);
 int stencil_astaroth_sync(stencil_astaroth_t *a);
 /* `iters` iterations; host wall seconds (max over ranks); *exchange_seconds (may be NULL) = time inside exchange() */
 double stencil_astaroth_run(stencil_astaroth_t *a, int iters, double *exchange_seconds);
+/* same, and *device_seconds = time between CUDA events on the compute streams around the loop (max over GPUs and ranks) */
+double stencil_astaroth_run_timed(stencil_astaroth_t *a, int iters, double *exchange_seconds, double *device_seconds);
 uint64_t stencil_astaroth_launches(const stencil_astaroth_t *a);
 /* dense [z][y][x] copy of one field as double into out[x*y*z]; cells owned by other ranks are NaN */
 int stencil_astaroth_gather(stencil_astaroth_t *a, int field, double *out, uint64_t count);

@@ -161,41 +161,105 @@ template <typename T, bool STAR> __global__ void __launch_bounds__(kLanes *kRows
   }
 }
 
-/* ---------------- TMA-pipelined radius-3 star kernel ----------------
-   Same structure as the Jacobi kernel (src/jacobi.cu): a tile is 32 lanes x 16 rows, a lane owns one 16-byte vector
-   of cells (N = 4 fp32 / 2 fp64), thread 0 streams (32N + 8) x (16 + 6) input planes of ONE field into a 6-stage
-   shared-memory ring with cp.async.bulk.tensor.3d, eight warps (two rows each) consume. The z direction never goes
-   back to memory: each arriving plane adds its "above" contribution to the three pending outputs and its centre
-   stays in registers for the three "below" contributions that follow, so a plane is read from shared memory once. */
-constexpr int kTRows = 16, kTMargin = 4, kTStages = 6, kTLag = 2, kTThreads = 256;
-
-template <typename T> struct TmaGeom {
-  static constexpr int N = Vec<T>::n;
-  static constexpr int tileX = 32 * N;
-  static constexpr int boxX = tileX + 2 * kTMargin;
-  static constexpr int boxY = kTRows + 2 * kR;
-  static constexpr int planeBytes = boxX * boxY * int(sizeof(T));
-  static constexpr int stageBytes = (planeBytes + 127) / 128 * 128;
-  static constexpr int smemBytes = kTStages * stageBytes + 2 * kTStages * 8;
+/* Cross-derivative terms (Stencil::Star19Cross). Real Astaroth-style MHD right-hand sides contain mixed second
+   derivatives, which read the DIAGONAL neighbours and therefore the edge halos a 19-point star never touches:
+     next = curr + dt * ( L6(curr) + eta * ( Dxy + Dxz + Dyz + Dxyz ) )
+   Dab = sum_k m_k [ f(+k,+k) - f(+k,-k) - f(-k,+k) + f(-k,-k) ] along the diagonals of the ab plane, k = 1..3, with the
+   6th-order weights m = (270, -27, 2) / 720; Dxyz = m_1 * sum of sign(dx dy dz) f(+-1,+-1,+-1) reads the eight corner
+   directions. All 26 halo directions take part, so a wrong edge or corner block fails the comparison with the host. */
+template <typename T> struct CrossW {
+  static constexpr T m1() { return T(270.0 / 720.0); }
+  static constexpr T m2() { return T(-27.0 / 720.0); }
+  static constexpr T m3() { return T(2.0 / 720.0); }
 };
 
-/* Fused y / z face pushes: tiles on a y or z face of the subdomain also store their rows into
-   the neighbour's `next` halo — peer pointers over NVLink, or plain stores when the neighbour shares the GPU — and
-   the kernels of neighbouring GPUs hand-shake through epoch flags exactly as the fused Jacobi kernel does
-   (src/jacobi.cu): boundary CTAs wait for the neighbours' flags of the previous iteration before reading halos,
-   count themselves done after a GPU-scope fence, and the last one raises the neighbours' flags behind one
-   system-scope fence. A 19-point star reads face halos only, so in steady state no exchange() is left. */
-enum PushFace { kYM = 0, kYP = 1, kZM = 2, kZP = 3 };
+template <typename T, typename At> __host__ __device__ inline T cross_terms(At at) { // at(dx,dy,dz)
+  const T m[3] = {CrossW<T>::m1(), CrossW<T>::m2(), CrossW<T>::m3()};
+  T s = T(0);
+  for (int k = 1; k <= 3; ++k) {
+    s += m[k - 1] * (((at(k, k, 0) - at(k, -k, 0)) - at(-k, k, 0)) + at(-k, -k, 0));
+    s += m[k - 1] * (((at(k, 0, k) - at(-k, 0, k)) - at(k, 0, -k)) + at(-k, 0, -k));
+    s += m[k - 1] * (((at(0, k, k) - at(0, -k, k)) - at(0, k, -k)) + at(0, -k, -k));
+  }
+  s += m[0] * ((((at(1, 1, 1) - at(1, -1, 1)) - at(-1, 1, 1)) + at(-1, -1, 1)) - (((at(1, 1, -1) - at(1, -1, -1)) - at(-1, 1, -1)) + at(-1, -1, -1)));
+  return s;
+}
+
+/* Star19Cross without the TMA pipeline: one thread per cell, every point straight from global memory (L1/L2 absorb
+   the reuse). Slow and general: thin regions of the overlap schedule, Options::useTma = false, and an independent
+   device-side check of the pipelined kernel. */
+template <typename T> __global__ void __launch_bounds__(kLanes *kRows) astaroth_cross_kernel(const __grid_constant__ FieldParams<T> P, T eta) {
+  const int field = blockIdx.z / P.nChunks, chunk = blockIdx.z % P.nChunks;
+  const int x = P.lox + blockIdx.x * kLanes + threadIdx.x;
+  const int y = P.loy + blockIdx.y * kRows + threadIdx.y;
+  const int z0 = P.loz + chunk * P.tileZ, z1 = min(z0 + P.tileZ, P.hiz);
+  if (x >= P.hix || y >= P.hiy) return;
+  for (int z = z0; z < z1; ++z) {
+    const T *c = P.src[field] + (long long)z * P.pitchXY + (long long)y * P.pitchX + x;
+    auto at = [&](int dx, int dy, int dz) { return c[(long long)dz * P.pitchXY + (long long)dy * P.pitchX + dx]; };
+    T xm[3], xp[3], ym[3], yp[3], zm[3], zp[3];
+    for (int k = 0; k < 3; ++k) {
+      xm[k] = at(-k - 1, 0, 0), xp[k] = at(k + 1, 0, 0);
+      ym[k] = at(0, -k - 1, 0), yp[k] = at(0, k + 1, 0);
+      zm[k] = at(0, 0, -k - 1), zp[k] = at(0, 0, k + 1);
+    }
+    const T v = star19<T>(c[0], xm, xp, ym, yp, zm, zp, P.dt) + P.dt * (eta * cross_terms<T>(at));
+    P.dst[field][(long long)z * P.pitchXY + (long long)y * P.pitchX + x] = v;
+  }
+}
+
+/* ---------------- TMA-pipelined radius-3 kernel ----------------
+   Same structure as the Jacobi kernel (src/jacobi.cu): thread 0 streams the input planes of ONE field of one tile
+   into a 6-stage shared-memory ring with cp.async.bulk.tensor.3d, eight warps consume, a lane owns one 16-byte vector
+   of cells (N = 4 fp32 / 2 fp64) in each of two rows. Two tile shapes, picked per tile (uniform per CTA):
+     wide   32 lanes per row: 32N cells x 16 rows;   narrow   8 lanes per row: 8N cells x 64 rows
+   — narrow tiles cover what is left of a row after the last full wide tile (323- and 406-cell rows of the weak-scaling
+   rule would otherwise pay a whole tile for 3 / 22 cells). The z direction never goes back to memory: each arriving
+   plane adds its "above" contribution to the three pending outputs and its centre stays in registers for the three
+   "below" contributions that follow, so a plane is read from shared memory once. */
+constexpr int kTRows = 16, kTMargin = 4, kTStages = 6, kTLag = 2, kTThreads = 256;
+
+template <typename T, int LW> struct TmaGeom {
+  static constexpr int N = Vec<T>::n;
+  static constexpr int kSub = 32 / LW;           // row pairs per warp
+  static constexpr int tileX = LW * N;
+  static constexpr int tileY = kTRows * kSub;
+  static constexpr int boxX = tileX + 2 * kTMargin;
+  static constexpr int boxY = tileY + 2 * kR;
+  static constexpr int planeBytes = boxX * boxY * int(sizeof(T));
+  static constexpr int stageBytes = (planeBytes + 127) / 128 * 128;
+  static constexpr int barOffset = kTStages * stageBytes;
+  static constexpr int smemBytes = barOffset + 2 * kTStages * 8;
+};
+template <typename T> constexpr int tma_smem_bytes() {
+  return TmaGeom<T, 8>::smemBytes > TmaGeom<T, 32>::smemBytes ? TmaGeom<T, 8>::smemBytes : TmaGeom<T, 32>::smemBytes;
+}
+
+/* Fused halo pushes. The kernel keeps all 26 halo directions of `next` current by itself, so in
+   steady state no exchange() is left:
+     +-x faces       the subdomain is its own x neighbour (precondition of the fused path): the lanes that own the first /
+                     last three cells of a row store them a second time, sx cells further / earlier in the same row;
+     y, z faces      a tile on such a face copies, after its plane loop, the rows it has just written (still in L2) into
+                     the neighbour's halo — peer pointers over NVLink, or plain stores when the neighbour shares the GPU;
+     yz edges        tiles on a y AND a z face copy their 3 x 3 row bundle to the diagonal neighbour as well;
+     xy, xz edges, corners   every row copied above also carries its own x wrap: cells 0..2 land once more sx cells
+                     further, cells sx-3..sx-1 sx cells earlier, in the destination's x halo.
+   That is 8 destinations ("push directions") per subdomain. Kernels of neighbouring GPUs hand-shake through one epoch
+   flag and one completion counter PER DIRECTION, exactly as the fused Jacobi kernel does per face (src/jacobi.cu):
+   a tile waits for the flags of the directions it touches before reading halos, counts itself done on them after a
+   GPU-scope fence, and whoever completes a direction raises that neighbour's flag behind one system-scope fence. */
+constexpr int kDirs = 8;
+enum PushDir { kYM = 0, kYP = 1, kZM = 2, kZP = 3, kYMZM = 4, kYMZP = 5, kYPZM = 6, kYPZP = 7 };
 constexpr int kFusedFlagBase = 64; // word offset of the fused-iteration flags inside a control block (as in jacobi.cu)
 
 template <typename T> struct PushParams {
-  T *nb[4][kMaxFields];      // my compute cell (x,y,z) on face f lands at nb[f][field] + z*nbPitchXY[f] + y*nbPitchX[f] + x
-  long long nbPitchX[4], nbPitchXY[4];
-  unsigned *nbFlag[4];       // neighbour's flag to raise (nullptr: ordered by streams on one GPU)
-  const unsigned *myFlag[4]; // my flag the neighbour raises
-  unsigned faceMask, flagMask;
-  unsigned nBoundary; // CTAs that take part in the hand-shake
-  unsigned *done, *err;
+  T *nb[kDirs][kMaxFields];      // my compute cell (x,y,z) lands at nb[d][field] + z*nbPitchXY[d] + y*nbPitchX[d] + x
+  long long nbPitchX[kDirs], nbPitchXY[kDirs];
+  unsigned *nbFlag[kDirs];       // neighbour's flag to raise (nullptr: ordered by streams on one GPU)
+  const unsigned *myFlag[kDirs]; // my flag the neighbour raises
+  unsigned dirMask, flagMask;
+  unsigned nDir[kDirs]; // CTAs that take part in the hand-shake, per direction
+  unsigned *done, *err; // done: kDirs counters
   unsigned long long timeoutNs;
   int sx, sy, sz;
 };
@@ -214,47 +278,58 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
   return t;
 }
 
-/* Boundary tiles only, after their plane loop: copy the rows of this tile that lie on y / z faces from my `next`
-   buffer (written a moment ago by this CTA) to the matching halo rows of the neighbours' `next` buffers.
-   One warp per row, 16-byte vectors when both sides are aligned. Loads bypass L1 (ld.global.cg). */
+/* Boundary tiles only, after their plane loop: copy the rows of this tile that belong to each push direction from my
+   `next` buffer (written a moment ago by this CTA) to the matching halo rows of that neighbour's `next` buffer, x wrap
+   included. One warp per row, 16-byte vectors when both sides are aligned. Loads bypass L1 (ld.global.cg). */
 template <typename T>
-__device__ __noinline__ void push_tile_faces(const PushParams<T> &Q, int field, unsigned faces, int xlo, int ylo, int z0, int z1, const T *mine,
-                                             long long pitchX, long long pitchXY) {
+__device__ __noinline__ void push_tile_dirs(const PushParams<T> &Q, int field, unsigned dirs, int xlo, int tw, int ylo, int tr, int z0, int z1,
+                                            const T *mine, long long pitchX, long long pitchXY) {
   typedef typename Vec<T>::type V;
   constexpr int N = Vec<T>::n;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = kTThreads / 32;
-  const int xhi = min(xlo + 32 * N, Q.sx), yhi = min(ylo + kTRows, Q.sy);
-  for (int f = 0; f < 4; ++f) {
-    if (!((faces >> f) & 1u)) continue;
+  const int xhi = min(xlo + tw, Q.sx), yhi = min(ylo + tr, Q.sy);
+  for (int d = 0; d < kDirs; ++d) {
+    if (!((dirs >> d) & 1u)) continue;
+    const int dy = d == kYM || d == kYMZM || d == kYMZP ? -1 : (d == kYP || d == kYPZM || d == kYPZP ? 1 : 0);
+    const int dz = d == kZM || d == kYMZM || d == kYPZM ? -1 : (d == kZP || d == kYMZP || d == kYPZP ? 1 : 0);
     int ya = ylo, yb = yhi, za = z0, zb = z1;
-    if (f == kYM) yb = min(yb, kR);
-    if (f == kYP) ya = max(ya, Q.sy - kR);
-    if (f == kZM) zb = min(zb, kR);
-    if (f == kZP) za = max(za, Q.sz - kR);
+    if (dy < 0) yb = min(yb, kR);
+    if (dy > 0) ya = max(ya, Q.sy - kR);
+    if (dz < 0) zb = min(zb, kR);
+    if (dz > 0) za = max(za, Q.sz - kR);
     const int ny = yb - ya, rows = ny * (zb - za);
-    T *nb = Q.nb[f][field];
-    const long long npx = Q.nbPitchX[f], npxy = Q.nbPitchXY[f];
+    if (ny <= 0 || zb <= za) continue;
+    T *nb = Q.nb[d][field];
+    const long long npx = Q.nbPitchX[d], npxy = Q.nbPitchXY[d];
     for (int r = warp; r < rows; r += nwarps) {
       const int z = za + r / ny, y = ya + r % ny;
       const T *src = mine + (long long)z * pitchXY + (long long)y * pitchX;
       T *dst = nb + (long long)z * npxy + (long long)y * npx;
       const bool vec = ((reinterpret_cast<unsigned long long>(dst + xlo) | reinterpret_cast<unsigned long long>(src + xlo)) & (sizeof(V) - 1)) == 0;
       if (vec) {
-        const int x = xlo + lane * N;
-        if (x + N <= xhi) {
-          *reinterpret_cast<V *>(dst + x) = __ldcg(reinterpret_cast<const V *>(src + x));
-        } else {
-          for (int i = x; i < xhi; ++i) dst[i] = __ldcg(src + i);
+        for (int x = xlo + lane * N; x < xhi; x += 32 * N) {
+          if (x + N <= xhi) {
+            *reinterpret_cast<V *>(dst + x) = __ldcg(reinterpret_cast<const V *>(src + x));
+          } else {
+            for (int i = x; i < xhi; ++i) dst[i] = __ldcg(src + i);
+          }
         }
       } else {
         for (int x = xlo + lane; x < xhi; x += 32) dst[x] = __ldcg(src + x);
+      }
+      /* x wrap of this row (xy / xz edges and corners of the destination): only the cells this tile owns */
+      if (lane < kR) {
+        if (lane >= xlo && lane < xhi) dst[lane + Q.sx] = __ldcg(src + lane);
+      } else if (lane < 2 * kR) {
+        const int x = Q.sx - 2 * kR + lane;
+        if (x >= xlo && x < xhi) dst[x - Q.sx] = __ldcg(src + x);
       }
     }
   }
 }
 
-template <typename T> __device__ __noinline__ void wait_neighbours(const PushParams<T> &Q, unsigned faces, unsigned epoch) {
-  if (threadIdx.x < 4 && ((faces >> threadIdx.x) & 1u)) {
+template <typename T> __device__ __noinline__ void wait_dirs(const PushParams<T> &Q, unsigned dirs, unsigned epoch) {
+  if (threadIdx.x < kDirs && ((dirs >> threadIdx.x) & 1u)) {
     const unsigned *f = Q.myFlag[threadIdx.x];
     if (f) {
       const unsigned long long t0 = globaltimer_ns();
@@ -269,57 +344,70 @@ template <typename T> __device__ __noinline__ void wait_neighbours(const PushPar
   }
 }
 
-template <typename T> __device__ __noinline__ void signal_neighbours(const PushParams<T> &Q, unsigned epoch) {
+/* thread 0 of a tile that stored into another GPU (after a CTA barrier) */
+template <typename T> __device__ __noinline__ void signal_dirs(const PushParams<T> &Q, unsigned dirs, unsigned epoch) {
   __threadfence();
-  const unsigned prev = atomicAdd(Q.done, 1u);
-  if (prev == Q.nBoundary - 1) {
-    *Q.done = 0;
+  unsigned ready = 0;
+  for (int d = 0; d < kDirs; ++d)
+    if ((dirs >> d) & 1u) {
+      if (atomicAdd(Q.done + d, 1u) == Q.nDir[d] - 1) {
+        Q.done[d] = 0;
+        ready |= 1u << d;
+      }
+    }
+  if (ready) {
     __threadfence_system();
-    for (int f = 0; f < 4; ++f)
-      if (Q.nbFlag[f]) st_flag_sys(Q.nbFlag[f], epoch);
+    for (int d = 0; d < kDirs; ++d)
+      if ((ready >> d) & 1u) st_flag_sys(Q.nbFlag[d], epoch);
   }
 }
 
-/* which y / z faces does tile (ty, z-chunk [z0,z1)) own cells on? (host and device agree through this one function) */
-__host__ __device__ inline unsigned tile_faces(int ty, int z0, int z1, int sy, int sz, unsigned faceMask) {
+/* which push directions does a tile with rows [ylo, ylo+tr) and planes [z0, z1) own cells for? */
+inline unsigned tile_dirs(int ylo, int tr, int z0, int z1, int sy, int sz, unsigned dirMask) {
+  const bool ym = ylo < kR, yp = ylo + tr > sy - kR && ylo < sy, zm = z0 < kR, zp = z1 > sz - kR;
   unsigned f = 0;
-  const int ylo = ty * 16, yhi = ylo + 16;
-  if (ylo < kR) f |= 1u << kYM;
-  if (yhi > sy - kR && ylo < sy) f |= 1u << kYP;
-  if (z0 < kR) f |= 1u << kZM;
-  if (z1 > sz - kR) f |= 1u << kZP;
-  return f & faceMask;
+  if (ym) f |= 1u << kYM;
+  if (yp) f |= 1u << kYP;
+  if (zm) f |= 1u << kZM;
+  if (zp) f |= 1u << kZP;
+  if (ym && zm) f |= 1u << kYMZM;
+  if (ym && zp) f |= 1u << kYMZP;
+  if (yp && zm) f |= 1u << kYPZM;
+  if (yp && zp) f |= 1u << kYPZP;
+  return f & dirMask;
 }
+
+struct ATile {
+  int x0, y0;           // first cell / row of the tile (compute coordinates)
+  unsigned short chunk; // z chunk of the region: planes loz + chunk*tileZ ...
+  unsigned char field, dirs, narrow, pad[3];
+};
 
 template <typename T> struct TmaParams {
   T *dst[kMaxFields];      // compute cell (0,0,0) of next, per field
-  const CUtensorMap *maps; // device array: one map per field over the CURRENT curr buffers
+  const CUtensorMap *maps; // device array over the CURRENT curr buffers: [2 * field + narrow]
+  const ATile *tiles;
   long long pitchX, pitchXY;
   int lox, loy, loz, hix, hiy, hiz; // cells to update, compute coordinates, half open
-  int tileZ, tilesX, tilesY, nChunks;
-  int tx0, ty0;            // first tile column / row of the region (tile grid is anchored at compute cell 0)
+  int tileZ;
   int x0pad;               // index of compute x = 0 inside a padded row (TMA coordinates start at the row start)
-  const PushParams<T> *push; // device pointer, nullptr: no y / z pushes
-  unsigned pushFaceMask, pushFlagMask; // copies of push->faceMask / flagMask (decided before anything is loaded)
-  unsigned epoch;                      // iteration being computed (1-based)
-  int sy, sz;                          // compute extent of the subdomain (for the face tests)
+  const PushParams<T> *push; // device pointer, nullptr: no pushes
+  unsigned pushFlagMask;     // copy of push->flagMask (decided before anything is loaded)
+  unsigned epoch;            // iteration being computed (1-based)
   int wrapX;               // > 0: the subdomain is its own +-x neighbour and is wrapX cells wide; the kernel then also
                            // writes its first / last three cells of every row into the opposite x halo of `next`
-  T dt;
+  T dt, eta;               // eta: weight of the cross terms (CROSS instantiations)
 };
 
-template <typename T> __global__ void __launch_bounds__(kTThreads, 2) astaroth_tma_kernel(const __grid_constant__ TmaParams<T> P) {
-  typedef TmaGeom<T> G;
+template <typename T, int LW, bool CROSS>
+__device__ __forceinline__ void astaroth_tile(unsigned char *smem, const TmaParams<T> &P, const ATile &t) {
+  typedef TmaGeom<T, LW> G;
   typedef typename Vec<T>::type V;
   constexpr int N = G::N;
-  extern __shared__ __align__(128) unsigned char smem[];
-  unsigned long long *full = reinterpret_cast<unsigned long long *>(smem + kTStages * G::stageBytes);
+  unsigned long long *full = reinterpret_cast<unsigned long long *>(smem + G::barOffset);
   unsigned long long *empty = full + kTStages;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, field = blockIdx.y;
-  int tile = blockIdx.x;
-  const int tx = P.tx0 + tile % P.tilesX;
-  tile /= P.tilesX;
-  const int ty = P.ty0 + tile % P.tilesY, chunk = tile / P.tilesY;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, field = t.field;
+  const int xl = lane & (LW - 1), sub = lane / LW;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kTStages; ++s) {
@@ -328,18 +416,20 @@ template <typename T> __global__ void __launch_bounds__(kTThreads, 2) astaroth_t
     }
     tma::mbar_fence_init();
   }
-  const int z0 = P.loz + chunk * P.tileZ, z1 = min(z0 + P.tileZ, P.hiz);
-  /* y / z faces this tile pushes to neighbours; tiles that exchange with another GPU first wait for that GPU's flags of
-     the previous iteration (they are the only tiles that read halo cells it wrote) */
-  const unsigned faces = P.push ? tile_faces(ty, z0, z1, P.sy, P.sz, P.pushFaceMask) : 0u;
-  if (faces & P.pushFlagMask) wait_neighbours<T>(*P.push, faces & P.pushFlagMask, P.epoch);
+  const int z0 = P.loz + int(t.chunk) * P.tileZ, z1 = min(z0 + P.tileZ, P.hiz);
+  /* tiles that exchange with another GPU first wait for that GPU's flags of the previous iteration (they are the only
+     tiles that read halo cells it wrote); the TMA reads that follow are async-proxy accesses, ordered after the
+     acquire by an explicit proxy fence of the issuing thread */
+  const unsigned dirs = P.push ? unsigned(t.dirs) : 0u;
+  if (dirs & P.pushFlagMask) wait_dirs<T>(*P.push, dirs & P.pushFlagMask, P.epoch);
   __syncthreads();
+  if ((dirs & P.pushFlagMask) && threadIdx.x == 0) asm volatile("fence.proxy.async.global;" ::: "memory");
 
   const int nplanes = z1 - z0 + 2 * kR; // input planes z0-3 .. z1+2
-  const CUtensorMap *map = P.maps + field;
-  const int cx = P.x0pad + tx * G::tileX - kTMargin; // raw x of smem column 0
-  const int cy = ty * kTRows;                        // raw row of compute row ty*16 - 3 (raw = compute + 3)
-  auto issue = [&](int j) {                          // input plane j = compute plane z0 - 3 + j = raw plane z0 + j
+  const CUtensorMap *map = P.maps + 2 * field + (LW == 32 ? 0 : 1);
+  const int cx = P.x0pad + t.x0 - kTMargin; // raw x of smem column 0
+  const int cy = t.y0;                      // raw row of compute row y0 - 3 (raw = compute + 3)
+  auto issue = [&](int j) {                 // input plane j = compute plane z0 - 3 + j = raw plane z0 + j
     const int sj = j % kTStages;
     if (j >= kTStages) tma::mbar_wait(&empty[sj], ((j / kTStages) - 1) & 1);
     tma::mbar_arrive_expect_tx(&full[sj], G::planeBytes);
@@ -348,8 +438,8 @@ template <typename T> __global__ void __launch_bounds__(kTThreads, 2) astaroth_t
   if (threadIdx.x == 0)
     for (int j = 0; j < kTStages - kTLag && j < nplanes; ++j) issue(j);
 
-  const int r0 = 2 * warp;
-  const int x0 = tx * G::tileX + lane * N, y0 = ty * kTRows + r0;
+  const int r0 = 2 * (warp * G::kSub + sub);
+  const int x0 = t.x0 + xl * N, y0 = t.y0 + r0;
   /* where the two rows of this lane go, decided once */
   T *dp[2];
   int mode[2];
@@ -376,20 +466,26 @@ template <typename T> __global__ void __launch_bounds__(kTThreads, 2) astaroth_t
     }
   }
   const T c1 = T(1.5), c2 = T(-0.15), c3 = T(1.0 / 90.0), c0x3 = T(3) * T(-49.0 / 18.0);
+  const T k1 = P.eta * CrossW<T>::m1(), k2 = P.eta * CrossW<T>::m2(), k3 = P.eta * CrossW<T>::m3();
   /* pending sums for the planes 1, 2, 3 behind the newest one, and the centres of those planes */
   T a1[2][N], a2[2][N], a3[2][N], h1[2][N], h2[2][N], h3[2][N];
+  /* CROSS: sums collected AHEAD of the planes 1, 2, 3 in front of the newest one (the "below" halves of Dxz, Dyz, Dxyz) */
+  T b1[2][N], b2[2][N], b3[2][N];
 #pragma unroll
   for (int r = 0; r < 2; ++r)
 #pragma unroll
-    for (int i = 0; i < N; ++i) a1[r][i] = a2[r][i] = a3[r][i] = h1[r][i] = h2[r][i] = h3[r][i] = T(0);
+    for (int i = 0; i < N; ++i) {
+      a1[r][i] = a2[r][i] = a3[r][i] = h1[r][i] = h2[r][i] = h3[r][i] = T(0);
+      b1[r][i] = b2[r][i] = b3[r][i] = T(0);
+    }
 
   int s = 0;
   unsigned phase = 0;
   for (int j = 0; j < nplanes; ++j) {
     tma::mbar_wait(&full[s], phase);
     const T *pl = reinterpret_cast<const T *>(smem + s * G::stageBytes);
-    /* smem row q holds compute row ty*16 + q - 3; smem column kTMargin + k holds compute x = tx*tileX + k */
-    const T *base = pl + (r0 + kR) * G::boxX + kTMargin + lane * N;
+    /* smem row q holds compute row t.y0 + q - 3; smem column kTMargin + k holds compute x = t.x0 + k */
+    const T *base = pl + (r0 + kR) * G::boxX + kTMargin + xl * N;
     T col[8][N]; // rows r0-3 .. r0+4 at my x: col[3], col[4] are my two centre rows
 #pragma unroll
     for (int q = 0; q < 8; ++q) {
@@ -398,7 +494,10 @@ template <typename T> __global__ void __launch_bounds__(kTThreads, 2) astaroth_t
     }
     const bool inPlane = j >= kR && j < nplanes - kR; // this plane is an output plane: it needs its in-plane sum
     T an[2][N];
-    if (inPlane) {
+    /* CROSS: e_k = [f(x+k) - f(x-k)] + [f(y+k) - f(y-k)] (+ the in-plane diagonal difference for k = 1) of THIS plane at
+       my cells: what this plane contributes, with weight +-m_k, to the outputs k planes below / above it */
+    T e1[2][N], e2[2][N], e3[2][N];
+    if (CROSS || inPlane) {
 #pragma unroll
       for (int r = 0; r < 2; ++r) {
         /* x window of row r: cells x0 - kTMargin .. x0 + N + kTMargin - 1 */
@@ -410,8 +509,8 @@ template <typename T> __global__ void __launch_bounds__(kTThreads, 2) astaroth_t
 #pragma unroll
             for (int i = 0; i < N; ++i) win[kTMargin + i] = col[3 + r][i];
           } else {
-            const V t = *reinterpret_cast<const V *>(row + v * N - kTMargin);
-            memcpy(win + v * N, &t, sizeof(V));
+            const V tv = *reinterpret_cast<const V *>(row + v * N - kTMargin);
+            memcpy(win + v * N, &tv, sizeof(V));
           }
         }
 #pragma unroll
@@ -425,10 +524,49 @@ template <typename T> __global__ void __launch_bounds__(kTThreads, 2) astaroth_t
           lap += c1 * h1[r][i];
           lap += c2 * h2[r][i];
           lap += c3 * h3[r][i];
-          an[r][i] = lap;
+          an[r][i] = CROSS ? lap + b1[r][i] : lap;
+          if (CROSS) {
+            e1[r][i] = (win[c + 1] - win[c - 1]) + (col[3 + r + 1][i] - col[3 + r - 1][i]);
+            e2[r][i] = (win[c + 2] - win[c - 2]) + (col[3 + r + 2][i] - col[3 + r - 2][i]);
+            e3[r][i] = (win[c + 3] - win[c - 3]) + (col[3 + r + 3][i] - col[3 + r - 3][i]);
+          }
         }
       }
-    } else {
+      if (CROSS) {
+        /* in-plane diagonals: row q of the bundle, k = |q - centre row| cells to either side, feeds Dxy of my two rows;
+           the k = 1 difference is also the corner term's contribution of this plane and rides along in e1 */
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          T win[N + 2 * kTMargin];
+          const T *row = base + (q - 3) * G::boxX;
+#pragma unroll
+          for (int v = 0; v < (N + 2 * kTMargin) / N; ++v) {
+            if (v * N == kTMargin) {
+#pragma unroll
+              for (int i = 0; i < N; ++i) win[kTMargin + i] = col[q][i];
+            } else {
+              const V tv = *reinterpret_cast<const V *>(row + v * N - kTMargin);
+              memcpy(win + v * N, &tv, sizeof(V));
+            }
+          }
+#pragma unroll
+          for (int r = 0; r < 2; ++r) {
+            const int dy = q - 3 - r;
+            if (dy == 0 || dy < -kR || dy > kR) continue;
+            const int k = dy < 0 ? -dy : dy;
+            const T w = (k == 1 ? k1 : (k == 2 ? k2 : k3)) * T(dy < 0 ? -1 : 1);
+#pragma unroll
+            for (int i = 0; i < N; ++i) {
+              const int c = kTMargin + i;
+              const T d = win[c + k] - win[c - k];
+              an[r][i] += w * d;
+              if (k == 1) e1[r][i] += T(dy < 0 ? -1 : 1) * d;
+            }
+          }
+        }
+      }
+    }
+    if (!inPlane) {
 #pragma unroll
       for (int r = 0; r < 2; ++r)
 #pragma unroll
@@ -449,9 +587,18 @@ template <typename T> __global__ void __launch_bounds__(kTThreads, 2) astaroth_t
 #pragma unroll
       for (int i = 0; i < N; ++i) {
         const T c = col[3 + r][i];
-        out[i] = h3[r][i] + P.dt * (a3[r][i] + c3 * c);
-        a3[r][i] = a2[r][i] + c2 * c;
-        a2[r][i] = a1[r][i] + c1 * c;
+        if (CROSS) {
+          out[i] = h3[r][i] + P.dt * ((a3[r][i] + c3 * c) + k3 * e3[r][i]);
+          a3[r][i] = (a2[r][i] + c2 * c) + k2 * e2[r][i];
+          a2[r][i] = (a1[r][i] + c1 * c) + k1 * e1[r][i];
+          b1[r][i] = b2[r][i] - k1 * e1[r][i];
+          b2[r][i] = b3[r][i] - k2 * e2[r][i];
+          b3[r][i] = -(k3 * e3[r][i]);
+        } else {
+          out[i] = h3[r][i] + P.dt * (a3[r][i] + c3 * c);
+          a3[r][i] = a2[r][i] + c2 * c;
+          a2[r][i] = a1[r][i] + c1 * c;
+        }
         a1[r][i] = an[r][i];
         h3[r][i] = h2[r][i];
         h2[r][i] = h1[r][i];
@@ -484,16 +631,26 @@ template <typename T> __global__ void __launch_bounds__(kTThreads, 2) astaroth_t
       }
     }
   }
-  if (faces) {
-    /* The plane loop above is untouched by the fusion. A boundary tile copies the face rows it has just written
-       (still in L2) into the neighbours' halos here, whole CTA, one warp per row. */
+  if (dirs) {
+    /* The plane loop above is untouched by the fusion. A boundary tile copies the rows it has just written (still in
+       L2) into the neighbours' halos here, whole CTA, one warp per row. */
     __syncthreads();
-    push_tile_faces<T>(*P.push, field, faces, tx * G::tileX, ty * kTRows, z0, z1, P.dst[field], P.pitchX, P.pitchXY);
-    if (faces & P.pushFlagMask) {
+    push_tile_dirs<T>(*P.push, field, dirs, t.x0, G::tileX, t.y0, G::tileY, z0, z1, P.dst[field], P.pitchX, P.pitchXY);
+    if (dirs & P.pushFlagMask) {
       __syncthreads();
-      if (threadIdx.x == 0) signal_neighbours<T>(*P.push, P.epoch);
+      if (threadIdx.x == 0) signal_dirs<T>(*P.push, dirs & P.pushFlagMask, P.epoch);
     }
   }
+}
+
+template <typename T, bool CROSS>
+__global__ void __launch_bounds__(kTThreads, CROSS ? 1 : 2) astaroth_tma_kernel(const __grid_constant__ TmaParams<T> P) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  const ATile t = P.tiles[blockIdx.x];
+  if (t.narrow)
+    astaroth_tile<T, 8, CROSS>(smem, P, t);
+  else
+    astaroth_tile<T, 32, CROSS>(smem, P, t);
 }
 
 template <typename T>
@@ -515,9 +672,24 @@ __global__ void astaroth_init_kernel(T *logical0, long long pitchX, long long pi
 
 struct AstarothSim::Impl {
   std::vector<RcStream> streams;
-  std::vector<CUtensorMap *> maps[2]; // per subdomain: device array of one tensor map per field, per curr parity
+  std::vector<CUtensorMap *> maps[2]; // per subdomain: device array of two tensor maps (wide, narrow box) per field, per curr parity
   std::vector<Rect3> interior;
   std::vector<std::vector<Rect3>> exterior;
+  /* tile tables of the TMA kernel, per subdomain: whole compute region (with push directions), interior, exterior slabs */
+  struct Tiles {
+    ATile *dev = nullptr;
+    unsigned n = 0;
+  };
+  static Tiles upload(const std::vector<ATile> &t) {
+    Tiles r;
+    r.n = unsigned(t.size());
+    if (t.empty()) return r;
+    CUDA_RUNTIME(cudaMalloc(&r.dev, t.size() * sizeof(ATile)));
+    CUDA_RUNTIME(cudaMemcpy(r.dev, t.data(), t.size() * sizeof(ATile), cudaMemcpyHostToDevice));
+    return r;
+  }
+  std::vector<Tiles> tilesAll, tilesInterior;
+  std::vector<std::vector<Tiles>> tilesExterior;
   double exchangeSeconds = 0;
   /* free-running schedule: no host synchronisation inside the loop (exchange_async + events) */
   bool freeRun = false;
@@ -525,11 +697,13 @@ struct AstarothSim::Impl {
      those faces out */
   bool fusedX = false;
   bool xHalosFromKernel = false; // the previous step's kernel filled the x halos of what is now `curr`
-  /* y / z faces pushed by the kernel too (with fusedX: no exchange() left in steady state) */
+  /* y / z faces, yz edges and the x wrap of all of them pushed by the kernel too (with fusedX: no exchange() left in
+     steady state, all 26 directions stay current) */
   bool fusedYZ = false;
   struct Push {
     void *dev[2] = {nullptr, nullptr}; // PushParams<T> per curr parity, in device memory
-    unsigned faceMask = 0, flagMask = 0;
+    unsigned dirMask = 0, flagMask = 0;
+    unsigned nDir[kDirs] = {0, 0, 0, 0, 0, 0, 0, 0};
     unsigned *done = nullptr;
     std::vector<int> sameDevDeps; // local subdomains on the same GPU that push into me / I push into
     WaitSet finalWait;
@@ -542,45 +716,102 @@ struct AstarothSim::Impl {
 };
 
 namespace {
-const Dim3 kPushDir[4] = {Dim3(0, -1, 0), Dim3(0, 1, 0), Dim3(0, 0, -1), Dim3(0, 0, 1)};
+const Dim3 kPushDir[kDirs] = {Dim3(0, -1, 0), Dim3(0, 1, 0), Dim3(0, 0, -1), Dim3(0, 0, 1), Dim3(0, -1, -1), Dim3(0, -1, 1), Dim3(0, 1, -1), Dim3(0, 1, 1)};
+
+/* Tiles of the TMA kernel covering region [lo,hi) (compute coordinates) of a subdomain of size sz, for `fields` fields.
+   vecN = cells per 16-byte vector (wide tile = 32 vecN cells x 16 rows, narrow = 8 vecN x 64). dirMask: push directions
+   in use (0: no pushes); flagMask: those whose neighbour is another GPU; nDir[d] receives the number of CTAs that push
+   to such a neighbour in direction d. Order: field-major, then (z, y, x), which keeps the tiles that share halo rows
+   and planes resident together; tiles that push to another GPU come first (z directions, then the others) so that
+   every direction is announced early in the kernel — see make_tiles() in src/jacobi.cu for the reasoning. */
+std::vector<ATile> make_atiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int fields, int tileZ, int vecN, unsigned dirMask, unsigned flagMask,
+                               unsigned *nDir, bool narrowOk, bool flaggedFirst) {
+  std::vector<ATile> out;
+  if (nDir)
+    for (int d = 0; d < kDirs; ++d) nDir[d] = 0;
+  if (hi.x <= lo.x || hi.y <= lo.y || hi.z <= lo.z) return out;
+  const int64_t wideX = 32 * vecN, narrowX = 8 * vecN, narrowY = 4 * kTRows;
+  std::vector<std::pair<int64_t, bool>> cols;
+  for (int64_t x = lo.x / wideX * wideX; x < hi.x;) {
+    const int64_t left = std::min<int64_t>(hi.x, sz.x) - x;
+    if (narrowOk && left <= 3 * narrowX) {
+      if (x + narrowX > lo.x) cols.emplace_back(x, true);
+      x += narrowX;
+    } else {
+      cols.emplace_back(x, false);
+      x += wideX;
+    }
+  }
+  const int64_t nChunks = (hi.z - lo.z + tileZ - 1) / tileZ;
+  for (int f = 0; f < fields; ++f)
+    for (int64_t c = 0; c < nChunks; ++c) {
+      const int z0 = int(lo.z + c * tileZ), z1 = int(std::min<int64_t>(z0 + tileZ, hi.z));
+      auto emit = [&](int64_t x0, int64_t y0, int64_t tr, bool nar) {
+        ATile t;
+        std::memset(&t, 0, sizeof(t));
+        t.x0 = int(x0);
+        t.y0 = int(y0);
+        t.chunk = (unsigned short)c;
+        t.field = (unsigned char)f;
+        t.narrow = nar ? 1 : 0;
+        t.dirs = (unsigned char)tile_dirs(int(y0), int(tr), z0, z1, int(sz.y), int(sz.z), dirMask);
+        if (nDir)
+          for (int d = 0; d < kDirs; ++d)
+            if ((t.dirs & flagMask) >> d & 1u) ++nDir[d];
+        out.push_back(t);
+      };
+      for (int64_t y0 = lo.y / kTRows * kTRows; y0 < hi.y; y0 += kTRows)
+        for (const auto &col : cols)
+          if (!col.second) emit(col.first, y0, kTRows, false);
+      for (int64_t y0 = lo.y / narrowY * narrowY; y0 < hi.y; y0 += narrowY)
+        for (const auto &col : cols)
+          if (col.second) emit(col.first, y0, narrowY, true);
+    }
+  if (flaggedFirst && flagMask) {
+    const unsigned zbits = (1u << kZM) | (1u << kZP);
+    auto prio = [&](const ATile &t) { return (t.dirs & flagMask & zbits) ? 0 : ((t.dirs & flagMask) ? 1 : 2); };
+    std::stable_sort(out.begin(), out.end(), [&](const ATile &a, const ATile &b) { return prio(a) < prio(b); });
+  }
+  return out;
+}
 
 /* one PushParams<T> (device memory) for local subdomain di with `curr` = buffer `parity` */
 template <typename T>
-void *build_push(DistributedDomain &dd, size_t di, int parity, int fields, const NeighborInfo (*nbs)[kMaxFields], unsigned faceMask, unsigned flagMask,
-                 unsigned nBoundary, unsigned *done, unsigned *err) {
+void *build_push(DistributedDomain &dd, size_t di, int parity, int fields, const NeighborInfo (*nbs)[kMaxFields], unsigned dirMask, unsigned flagMask,
+                 const unsigned *nDir, unsigned *done, unsigned *err) {
   LocalDomain &ld = dd.domains()[di];
   PushParams<T> Q;
   std::memset(&Q, 0, sizeof(Q));
   const Dim3 sz = ld.size();
-  for (int f = 0; f < 4; ++f) {
-    if (!((faceMask >> f) & 1u)) continue;
+  for (int d = 0; d < kDirs; ++d) {
+    if (!((dirMask >> d) & 1u)) continue;
+    const Dim3 dir = kPushDir[d];
     for (int q = 0; q < fields; ++q) {
-      const NeighborInfo &n = nbs[f][q];
+      const NeighborInfo &n = nbs[d][q];
       const long long npx = n.view.pitchY / (long long)sizeof(T), npxy = n.view.pitchZ / (long long)sizeof(T);
       T *interior = reinterpret_cast<T *>(n.view.base[parity ^ 1]) + (long long)kR * (npxy + npx + 1); // its NEXT buffer
+      /* my first rows / planes land behind its last ones (+ halo), my last rows / planes before its first ones (- halo) */
       long long shift = 0;
-      switch (f) {
-      case kYM: shift = n.size.y * npx; break;  // my rows 0..2 -> its +y halo
-      case kYP: shift = -sz.y * npx; break;     // my last rows -> its -y halo
-      case kZM: shift = n.size.z * npxy; break;
-      case kZP: shift = -sz.z * npxy; break;
-      }
-      Q.nb[f][q] = interior + shift;
-      Q.nbPitchX[f] = npx;
-      Q.nbPitchXY[f] = npxy;
+      if (dir.y < 0) shift += n.size.y * npx;
+      if (dir.y > 0) shift -= sz.y * npx;
+      if (dir.z < 0) shift += n.size.z * npxy;
+      if (dir.z > 0) shift -= sz.z * npxy;
+      Q.nb[d][q] = interior + shift;
+      Q.nbPitchX[d] = npx;
+      Q.nbPitchXY[d] = npxy;
     }
-    if ((flagMask >> f) & 1u) {
+    if ((flagMask >> d) & 1u) {
       /* I raise the slot "from direction -dir" in the neighbour; the neighbour raises slot "from dir" in me */
-      Q.nbFlag[f] = nbs[f][0].control + kFusedFlagBase + DirectionMap<int>::slot(kPushDir[f] * -1);
-      Q.myFlag[f] = ld.arrive_flags() + kFusedFlagBase + DirectionMap<int>::slot(kPushDir[f]);
+      Q.nbFlag[d] = nbs[d][0].control + kFusedFlagBase + DirectionMap<int>::slot(dir * -1);
+      Q.myFlag[d] = ld.arrive_flags() + kFusedFlagBase + DirectionMap<int>::slot(dir);
     }
+    Q.nDir[d] = nDir[d];
   }
-  Q.faceMask = faceMask;
+  Q.dirMask = dirMask;
   Q.flagMask = flagMask;
-  Q.nBoundary = nBoundary;
   Q.done = done;
   Q.err = err;
-  Q.timeoutNs = 5000000000ull;
+  Q.timeoutNs = flag_timeout_ns();
   Q.sx = int(sz.x);
   Q.sy = int(sz.y);
   Q.sz = int(sz.z);
@@ -590,6 +821,8 @@ void *build_push(DistributedDomain &dd, size_t di, int parity, int fields, const
   return d;
 }
 } // namespace
+
+static bool is_star(AstarothSim::Stencil st) { return st != AstarothSim::Stencil::Average7; }
 
 AstarothSim::AstarothSim(size_t x, size_t y, size_t z, const Options &opt) : opt_(opt) {
   if (opt_.fields < 1 || opt_.fields > kMaxFields) LOG_FATAL("AstarothSim supports 1.." << kMaxFields << " fields");
@@ -606,6 +839,8 @@ AstarothSim::AstarothSim(size_t x, size_t y, size_t z, const Options &opt) : opt
   impl_->interior = dd_->get_interior();
   impl_->exterior = dd_->get_exterior();
   if (std::getenv("STENCIL_ASTAROTH_NO_TMA")) opt_.useTma = false;
+  if (std::getenv("STENCIL_ASTAROTH_NO_NARROW")) opt_.narrowTiles = false;
+  if (std::getenv("STENCIL_ASTAROTH_NATURAL_ORDER")) opt_.flaggedFirst = false;
   for (LocalDomain &ld : dd_->domains()) {
     DevGuard g(ld.gpu());
     cudaEvent_t e;
@@ -613,20 +848,27 @@ AstarothSim::AstarothSim(size_t x, size_t y, size_t z, const Options &opt) : opt
     impl_->computeDone.push_back(e);
     impl_->computeRecorded.push_back(false);
   }
-  if (opt_.autoSchedule && opt_.useTma && opt_.stencil == Stencil::Star19) opt_.overlap = false;
+  const bool star = is_star(opt_.stencil);
+  if (opt_.autoSchedule && opt_.useTma && star) opt_.overlap = false;
   impl_->freeRun = !opt_.overlap && opt_.freeRunning && dd_->exchange_device_only() && !std::getenv("STENCIL_ASTAROTH_HOST_SYNC");
+  const int vecN = opt_.fp64 ? Vec<double>::n : Vec<float>::n;
   {
     /* whole-region TMA launches only, every subdomain its own x neighbour, rows that keep the second store aligned */
-    const int n = opt_.fp64 ? TmaGeom<double>::N : TmaGeom<float>::N, tileX = 32 * n;
-    bool ok = !opt_.overlap && opt_.fusedXFaces && opt_.useTma && opt_.stencil == Stencil::Star19 && dd_->subdomain_grid().x == 1 &&
-              dd_->exchange_x_faces_all_local() && !std::getenv("STENCIL_ASTAROTH_NO_FUSED_X");
-    for (LocalDomain &ld : dd_->domains()) ok = ok && ld.size().x >= tileX / 2 && ld.size().x >= 2 * kR + n && ld.size().y >= kTRows / 2;
+    const int tileX = 32 * vecN;
+    bool ok = !opt_.overlap && opt_.fusedXFaces && opt_.useTma && star && dd_->subdomain_grid().x == 1 && dd_->exchange_x_faces_all_local() &&
+              !std::getenv("STENCIL_ASTAROTH_NO_FUSED_X");
+    for (LocalDomain &ld : dd_->domains()) ok = ok && ld.size().x >= tileX / 2 && ld.size().x >= 2 * kR + vecN && ld.size().y >= kTRows / 2;
     impl_->fusedX = ok;
   }
   setup_fused_faces();
-  if (opt_.useTma && opt_.stencil == Stencil::Star19) {
-    /* one tensor map per field and buffer: the padded buffer as (row pitch, rows, planes) */
-    for (LocalDomain &ld : dd_->domains()) {
+  if (opt_.useTma && star) {
+    /* two tensor maps per field and buffer: the padded buffer as (row pitch, rows, planes) with the wide and the narrow box */
+    std::vector<LocalDomain> &doms = dd_->domains();
+    impl_->tilesAll.resize(doms.size());
+    impl_->tilesInterior.resize(doms.size());
+    impl_->tilesExterior.resize(doms.size());
+    for (size_t di = 0; di < doms.size(); ++di) {
+      LocalDomain &ld = doms[di];
       DevGuard g(ld.gpu());
       const Dim3 raw = ld.raw_size();
       for (int parity = 0; parity < 2; ++parity) {
@@ -634,16 +876,32 @@ AstarothSim::AstarothSim(size_t x, size_t y, size_t z, const Options &opt) : opt
         for (int f = 0; f < opt_.fields; ++f) {
           char *buf = static_cast<char *>(ld.slab()) + ld.buffer_start_offset(size_t(f), parity);
           const Dim3 pitch = ld.pitch(size_t(f));
-          host.push_back(opt_.fp64 ? tma::make_plane_map(buf, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, pitch.x, raw.y, raw.z, TmaGeom<double>::boxX, TmaGeom<double>::boxY)
-                                   : tma::make_plane_map(buf, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, pitch.x, raw.y, raw.z, TmaGeom<float>::boxX, TmaGeom<float>::boxY));
+          if (opt_.fp64) {
+            host.push_back(tma::make_plane_map(buf, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, pitch.x, raw.y, raw.z, TmaGeom<double, 32>::boxX, TmaGeom<double, 32>::boxY));
+            host.push_back(tma::make_plane_map(buf, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, pitch.x, raw.y, raw.z, TmaGeom<double, 8>::boxX, TmaGeom<double, 8>::boxY));
+          } else {
+            host.push_back(tma::make_plane_map(buf, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, pitch.x, raw.y, raw.z, TmaGeom<float, 32>::boxX, TmaGeom<float, 32>::boxY));
+            host.push_back(tma::make_plane_map(buf, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, pitch.x, raw.y, raw.z, TmaGeom<float, 8>::boxX, TmaGeom<float, 8>::boxY));
+          }
         }
         CUtensorMap *d = nullptr;
         CUDA_RUNTIME(cudaMalloc(&d, host.size() * sizeof(CUtensorMap)));
         CUDA_RUNTIME(cudaMemcpy(d, host.data(), host.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice));
         impl_->maps[parity].push_back(d);
       }
-      CUDA_RUNTIME(cudaFuncSetAttribute(astaroth_tma_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, TmaGeom<double>::smemBytes));
-      CUDA_RUNTIME(cudaFuncSetAttribute(astaroth_tma_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, TmaGeom<float>::smemBytes));
+      CUDA_RUNTIME(cudaFuncSetAttribute(astaroth_tma_kernel<double, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, tma_smem_bytes<double>()));
+      CUDA_RUNTIME(cudaFuncSetAttribute(astaroth_tma_kernel<float, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, tma_smem_bytes<float>()));
+      CUDA_RUNTIME(cudaFuncSetAttribute(astaroth_tma_kernel<double, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tma_smem_bytes<double>()));
+      CUDA_RUNTIME(cudaFuncSetAttribute(astaroth_tma_kernel<float, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tma_smem_bytes<float>()));
+      /* tile tables: the whole region carries the push directions (filled in by setup_fused_faces when fused) */
+      const Dim3 sz = ld.size(), org = ld.origin();
+      if (!impl_->tilesAll[di].dev)
+        impl_->tilesAll[di] = Impl::upload(make_atiles(Dim3(0, 0, 0), sz, sz, opt_.fields, opt_.tileZ, vecN, 0, 0, nullptr, opt_.narrowTiles, false));
+      impl_->tilesInterior[di] = Impl::upload(make_atiles(impl_->interior[di].lo - org, impl_->interior[di].hi - org, sz, opt_.fields, opt_.tileZ,
+                                                          vecN, 0, 0, nullptr, opt_.narrowTiles, false));
+      for (const Rect3 &r : impl_->exterior[di])
+        impl_->tilesExterior[di].push_back(
+            Impl::upload(make_atiles(r.lo - org, r.hi - org, sz, opt_.fields, opt_.tileZ, vecN, 0, 0, nullptr, opt_.narrowTiles, false)));
     }
   }
   init();
@@ -652,17 +910,18 @@ AstarothSim::AstarothSim(size_t x, size_t y, size_t z, const Options &opt) : opt
 void AstarothSim::setup_fused_faces() {
   std::vector<LocalDomain> &doms = dd_->domains();
   impl_->push.resize(doms.size());
+  impl_->tilesAll.resize(doms.size());
   bool ok = impl_->fusedX && impl_->freeRun && opt_.fusedYZFaces && !std::getenv("STENCIL_ASTAROTH_NO_FUSED_YZ");
-  std::vector<std::vector<NeighborInfo>> all(doms.size()); // [di][f * kMaxFields + q]
+  std::vector<std::vector<NeighborInfo>> all(doms.size()); // [di][d * kMaxFields + q]
   if (ok)
     for (size_t di = 0; di < doms.size() && ok; ++di) {
-      all[di].resize(4 * kMaxFields);
+      all[di].resize(kDirs * kMaxFields);
       if (doms[di].size().y < 2 * kR || doms[di].size().z < 2 * kR || opt_.tileZ < kR) ok = false;
-      for (int f = 0; f < 4 && ok; ++f)
+      for (int d = 0; d < kDirs && ok; ++d)
         for (int q = 0; q < opt_.fields; ++q) {
-          const NeighborInfo n = dd_->neighbor(di, kPushDir[f], size_t(q));
-          all[di][size_t(f * kMaxFields + q)] = n;
-          /* every face needs a neighbour we can store into; two processes on one GPU cannot hand-shake by spinning */
+          const NeighborInfo n = dd_->neighbor(di, kPushDir[d], size_t(q));
+          all[di][size_t(d * kMaxFields + q)] = n;
+          /* every direction needs a neighbour we can store into; two processes on one GPU cannot hand-shake by spinning */
           if (!n.exists || !n.reachable || (n.sameDevice && !n.sameRank) || n.size.x != doms[di].size().x) ok = false;
         }
     }
@@ -671,39 +930,33 @@ void AstarothSim::setup_fused_faces() {
   if (!ok) return;
   CUDA_RUNTIME(cudaHostAlloc(&impl_->err, sizeof(unsigned), cudaHostAllocMapped | cudaHostAllocPortable));
   *impl_->err = 0;
-  const int n = opt_.fp64 ? TmaGeom<double>::N : TmaGeom<float>::N, tileX = 32 * n;
+  const int vecN = opt_.fp64 ? Vec<double>::n : Vec<float>::n;
   for (size_t di = 0; di < doms.size(); ++di) {
     LocalDomain &ld = doms[di];
     DevGuard g(ld.gpu());
     Impl::Push &p = impl_->push[di];
-    NeighborInfo nbs[4][kMaxFields];
+    NeighborInfo nbs[kDirs][kMaxFields];
     std::set<int> deps;
     p.finalWait.n = 0;
-    for (int f = 0; f < 4; ++f) {
-      for (int q = 0; q < opt_.fields; ++q) nbs[f][q] = all[di][size_t(f * kMaxFields + q)];
-      const NeighborInfo &nb = nbs[f][0];
-      p.faceMask |= 1u << f;
-      if (!(nb.sameRank && nb.sameDevice)) p.flagMask |= 1u << f;
+    for (int d = 0; d < kDirs; ++d) {
+      for (int q = 0; q < opt_.fields; ++q) nbs[d][q] = all[di][size_t(d * kMaxFields + q)];
+      const NeighborInfo &nb = nbs[d][0];
+      p.dirMask |= 1u << d;
+      if (!(nb.sameRank && nb.sameDevice)) p.flagMask |= 1u << d;
       if (nb.sameRank && nb.sameDevice && nb.dom != int(di)) deps.insert(nb.dom);
     }
     p.sameDevDeps.assign(deps.begin(), deps.end());
-    /* CTAs of a whole-region launch that take part in the flag hand-shake (same classification as the kernel) */
+    /* the tile table of the whole-region launch decides which CTAs take part in which hand-shake */
     const Dim3 sz = ld.size();
-    const int tilesX = int((sz.x + tileX - 1) / tileX), tilesY = int((sz.y + kTRows - 1) / kTRows);
-    const int nChunks = int((sz.z + opt_.tileZ - 1) / opt_.tileZ);
-    unsigned nBoundary = 0;
-    for (int c = 0; c < nChunks; ++c)
-      for (int ty = 0; ty < tilesY; ++ty) {
-        const int z0 = c * opt_.tileZ, z1 = std::min<int>(z0 + opt_.tileZ, int(sz.z));
-        if (tile_faces(ty, z0, z1, int(sz.y), int(sz.z), p.faceMask) & p.flagMask) nBoundary += unsigned(tilesX * opt_.fields);
-      }
-    CUDA_RUNTIME(cudaMalloc(&p.done, sizeof(unsigned)));
-    CUDA_RUNTIME(cudaMemset(p.done, 0, sizeof(unsigned)));
+    impl_->tilesAll[di] = Impl::upload(make_atiles(Dim3(0, 0, 0), sz, sz, opt_.fields, opt_.tileZ, vecN, p.dirMask, p.flagMask, p.nDir,
+                                                   opt_.narrowTiles, opt_.flaggedFirst));
+    CUDA_RUNTIME(cudaMalloc(&p.done, kDirs * sizeof(unsigned)));
+    CUDA_RUNTIME(cudaMemset(p.done, 0, kDirs * sizeof(unsigned)));
     for (int parity = 0; parity < 2; ++parity)
-      p.dev[parity] = opt_.fp64 ? build_push<double>(*dd_, di, parity, opt_.fields, nbs, p.faceMask, p.flagMask, nBoundary, p.done, impl_->err)
-                                : build_push<float>(*dd_, di, parity, opt_.fields, nbs, p.faceMask, p.flagMask, nBoundary, p.done, impl_->err);
-    for (int f = 0; f < 4; ++f)
-      if ((p.flagMask >> f) & 1u) p.finalWait.flag[p.finalWait.n++] = ld.arrive_flags() + kFusedFlagBase + DirectionMap<int>::slot(kPushDir[f]);
+      p.dev[parity] = opt_.fp64 ? build_push<double>(*dd_, di, parity, opt_.fields, nbs, p.dirMask, p.flagMask, p.nDir, p.done, impl_->err)
+                                : build_push<float>(*dd_, di, parity, opt_.fields, nbs, p.dirMask, p.flagMask, p.nDir, p.done, impl_->err);
+    for (int d = 0; d < kDirs; ++d)
+      if ((p.flagMask >> d) & 1u) p.finalWait.flag[p.finalWait.n++] = ld.arrive_flags() + kFusedFlagBase + DirectionMap<int>::slot(kPushDir[d]);
   }
 }
 
@@ -716,6 +969,13 @@ AstarothSim::~AstarothSim() {
       cudaFree(impl_->push[di].dev[0]);
       cudaFree(impl_->push[di].dev[1]);
       cudaFree(impl_->push[di].done);
+    }
+    for (size_t di = 0; di < dd_->domains().size(); ++di) {
+      DevGuard g(dd_->domains()[di].gpu());
+      if (di < impl_->tilesAll.size()) cudaFree(impl_->tilesAll[di].dev);
+      if (di < impl_->tilesInterior.size()) cudaFree(impl_->tilesInterior[di].dev);
+      if (di < impl_->tilesExterior.size())
+        for (Impl::Tiles &t : impl_->tilesExterior[di]) cudaFree(t.dev);
     }
     if (impl_->err) cudaFreeHost(impl_->err);
   }
@@ -754,7 +1014,8 @@ void AstarothSim::init() {
   impl_->xHalosFromKernel = false; // curr was just rewritten: the next exchange carries the x faces again
 }
 
-template <typename T> static void launch_region(AstarothSim::Stencil st, LocalDomain &ld, int fields, const Rect3 &reg, int tileZ, T dt, cudaStream_t stream) {
+template <typename T>
+static void launch_region(AstarothSim::Stencil st, LocalDomain &ld, int fields, const Rect3 &reg, int tileZ, T dt, T eta, cudaStream_t stream) {
   if (reg.empty()) return;
   FieldParams<T> P;
   std::memset(&P, 0, sizeof(P));
@@ -776,27 +1037,34 @@ template <typename T> static void launch_region(AstarothSim::Stencil st, LocalDo
   P.nChunks = (P.hiz - P.loz + tileZ - 1) / tileZ;
   P.dt = dt;
   constexpr int N = Vec<T>::n;
-  const int xSpan = P.hix - (P.lox / N) * N;
-  const dim3 block(kLanes, kRows, 1), grid(unsigned((xSpan + kLanes * N - 1) / (kLanes * N)), unsigned((P.hiy - P.loy + kRows - 1) / kRows),
-                                           unsigned(P.nChunks * fields));
-  if (st == AstarothSim::Stencil::Star19)
-    astaroth_kernel<T, true><<<grid, block, 0, stream>>>(P);
-  else
-    astaroth_kernel<T, false><<<grid, block, 0, stream>>>(P);
+  const dim3 block(kLanes, kRows, 1);
+  if (st == AstarothSim::Stencil::Star19Cross) {
+    const dim3 grid(unsigned((P.hix - P.lox + kLanes - 1) / kLanes), unsigned((P.hiy - P.loy + kRows - 1) / kRows), unsigned(P.nChunks * fields));
+    astaroth_cross_kernel<T><<<grid, block, 0, stream>>>(P, eta);
+  } else {
+    const int xSpan = P.hix - (P.lox / N) * N;
+    const dim3 grid(unsigned((xSpan + kLanes * N - 1) / (kLanes * N)), unsigned((P.hiy - P.loy + kRows - 1) / kRows), unsigned(P.nChunks * fields));
+    if (st == AstarothSim::Stencil::Star19)
+      astaroth_kernel<T, true><<<grid, block, 0, stream>>>(P);
+    else
+      astaroth_kernel<T, false><<<grid, block, 0, stream>>>(P);
+  }
   CUDA_RUNTIME(cudaGetLastError());
 }
 
-/* the TMA kernel on a region that is wide enough to fill its tiles */
+/* the TMA kernel on a region, through its tile table */
 template <typename T>
-static void launch_region_tma(LocalDomain &ld, int fields, const CUtensorMap *maps, const Rect3 &reg, int tileZ, T dt, cudaStream_t stream,
-                              bool wrapX = false, const void *push = nullptr, unsigned faceMask = 0, unsigned flagMask = 0, unsigned epoch = 0) {
-  typedef TmaGeom<T> G;
+static void launch_region_tma(bool cross, LocalDomain &ld, int fields, const CUtensorMap *maps, const ATile *tiles, unsigned nTiles, const Rect3 &reg,
+                              int tileZ, T dt, T eta, cudaStream_t stream, bool wrapX = false, const void *push = nullptr, unsigned flagMask = 0,
+                              unsigned epoch = 0) {
+  if (!nTiles) return;
   TmaParams<T> P;
   std::memset(&P, 0, sizeof(P));
   const Dim3 pitch = ld.pitch(0), org = ld.origin();
   const long long interiorOff = (long long)kR * (pitch.x * pitch.y + pitch.x + 1);
   for (int f = 0; f < fields; ++f) P.dst[f] = static_cast<T *>(ld.next_data(size_t(f))) + interiorOff;
   P.maps = maps;
+  P.tiles = tiles;
   P.pitchX = pitch.x;
   P.pitchXY = pitch.x * pitch.y;
   P.lox = int(reg.lo.x - org.x);
@@ -806,52 +1074,51 @@ static void launch_region_tma(LocalDomain &ld, int fields, const CUtensorMap *ma
   P.hiy = int(reg.hi.y - org.y);
   P.hiz = int(reg.hi.z - org.z);
   P.tileZ = tileZ;
-  P.tx0 = P.lox / G::tileX;
-  P.ty0 = P.loy / kTRows;
-  P.tilesX = (P.hix - 1) / G::tileX - P.tx0 + 1;
-  P.tilesY = (P.hiy - 1) / kTRows - P.ty0 + 1;
-  P.nChunks = (P.hiz - P.loz + tileZ - 1) / tileZ;
   P.x0pad = int(ld.lead_elems(0)) + kR;
   P.dt = dt;
+  P.eta = eta;
   P.wrapX = wrapX ? int(ld.size().x) : 0;
   P.push = static_cast<const PushParams<T> *>(push);
-  P.pushFaceMask = faceMask;
   P.pushFlagMask = flagMask;
   P.epoch = epoch;
-  P.sy = int(ld.size().y);
-  P.sz = int(ld.size().z);
-  const dim3 grid(unsigned(P.tilesX * P.tilesY * P.nChunks), unsigned(fields), 1);
-  astaroth_tma_kernel<T><<<grid, kTThreads, G::smemBytes, stream>>>(P);
+  if (cross)
+    astaroth_tma_kernel<T, true><<<nTiles, kTThreads, tma_smem_bytes<T>(), stream>>>(P);
+  else
+    astaroth_tma_kernel<T, false><<<nTiles, kTThreads, tma_smem_bytes<T>(), stream>>>(P);
   CUDA_RUNTIME(cudaGetLastError());
 }
 
 void AstarothSim::step() {
   STENCIL_RANGE("AstarothSim::step");
   std::vector<LocalDomain> &doms = dd_->domains();
-  auto launch = [&](size_t di, const Rect3 &reg) {
+  const bool star = is_star(opt_.stencil), cross = opt_.stencil == Stencil::Star19Cross;
+  /* tiles == nullptr: the region has no tile table (plain kernels only) */
+  auto launch = [&](size_t di, const Rect3 &reg, const Impl::Tiles *tiles, bool whole) {
     if (reg.empty()) return;
     DevGuard g(doms[di].gpu());
     const Dim3 ext = reg.extent();
-    const int tileX = opt_.fp64 ? TmaGeom<double>::tileX : TmaGeom<float>::tileX;
-    if (opt_.useTma && opt_.stencil == Stencil::Star19 && ext.x >= tileX / 2 && ext.y >= kTRows / 2) {
+    const int tileX = 32 * (opt_.fp64 ? Vec<double>::n : Vec<float>::n);
+    if (opt_.useTma && star && tiles && tiles->n && ext.x >= tileX / 2 && ext.y >= kTRows / 2) {
       const CUtensorMap *maps = impl_->maps[doms[di].parity()][di];
-      const void *pushDev = impl_->fusedYZ ? impl_->push[di].dev[doms[di].parity()] : nullptr;
-      const unsigned pushFaces = impl_->fusedYZ ? impl_->push[di].faceMask : 0u, pushFlags = impl_->fusedYZ ? impl_->push[di].flagMask : 0u;
+      const bool fused = whole && impl_->fusedYZ;
+      const void *pushDev = fused ? impl_->push[di].dev[doms[di].parity()] : nullptr;
+      const unsigned pushFlags = fused ? impl_->push[di].flagMask : 0u;
       if (opt_.fp64)
-        launch_region_tma<double>(doms[di], opt_.fields, maps, reg, opt_.tileZ, opt_.dt, impl_->streams[di], impl_->fusedX, pushDev, pushFaces,
-                                  pushFlags, impl_->iter);
+        launch_region_tma<double>(cross, doms[di], opt_.fields, maps, tiles->dev, tiles->n, reg, opt_.tileZ, opt_.dt, opt_.crossWeight, impl_->streams[di],
+                                  whole && impl_->fusedX, pushDev, pushFlags, impl_->iter);
       else
-        launch_region_tma<float>(doms[di], opt_.fields, maps, reg, opt_.tileZ, float(opt_.dt), impl_->streams[di], impl_->fusedX, pushDev, pushFaces,
-                                 pushFlags, impl_->iter);
+        launch_region_tma<float>(cross, doms[di], opt_.fields, maps, tiles->dev, tiles->n, reg, opt_.tileZ, float(opt_.dt), float(opt_.crossWeight),
+                                 impl_->streams[di], whole && impl_->fusedX, pushDev, pushFlags, impl_->iter);
       ++launches_;
       return;
     }
     if (opt_.fp64)
-      launch_region<double>(opt_.stencil, doms[di], opt_.fields, reg, opt_.tileZ, opt_.dt, impl_->streams[di]);
+      launch_region<double>(opt_.stencil, doms[di], opt_.fields, reg, opt_.tileZ, opt_.dt, opt_.crossWeight, impl_->streams[di]);
     else
-      launch_region<float>(opt_.stencil, doms[di], opt_.fields, reg, opt_.tileZ, float(opt_.dt), impl_->streams[di]);
+      launch_region<float>(opt_.stencil, doms[di], opt_.fields, reg, opt_.tileZ, float(opt_.dt), float(opt_.crossWeight), impl_->streams[di]);
     ++launches_;
   };
+  auto tiles_all = [&](size_t di) { return di < impl_->tilesAll.size() ? &impl_->tilesAll[di] : nullptr; };
   /* x halos of `curr`: written by the previous step's kernel if there was one, else by this exchange */
   dd_->exchange_skip_local_x_faces(impl_->fusedX && impl_->xHalosFromKernel);
   const bool steady = impl_->fusedYZ && impl_->xHalosFromKernel; // every halo of `curr` was written by the previous kernels
@@ -860,7 +1127,7 @@ void AstarothSim::step() {
   if (impl_->freeRun) {
     /* exchange_async() on the exchange streams, then one whole-region launch per subdomain ordered after it by an
        event; the next exchange is ordered after these launches the same way. The host only enqueues.
-       With fused faces there is no exchange at all after the first step: kernels of different GPUs hand-shake through
+       With fused pushes there is no exchange at all after the first step: kernels of different GPUs hand-shake through
        flags, kernels of subdomains that share a GPU are ordered by events. */
     if (!steady) {
       for (size_t di = 0; di < doms.size(); ++di)
@@ -878,7 +1145,7 @@ void AstarothSim::step() {
     }
     for (size_t di = 0; di < doms.size(); ++di) {
       DevGuard g(doms[di].gpu());
-      launch(di, doms[di].get_compute_region());
+      launch(di, doms[di].get_compute_region(), tiles_all(di), true);
       CUDA_RUNTIME(cudaEventRecord(impl_->computeDone[di], impl_->streams[di]));
       impl_->computeRecorded[di] = true;
     }
@@ -886,15 +1153,18 @@ void AstarothSim::step() {
     return;
   }
   if (opt_.overlap)
-    for (size_t di = 0; di < doms.size(); ++di) launch(di, impl_->interior[di]);
+    for (size_t di = 0; di < doms.size(); ++di) launch(di, impl_->interior[di], di < impl_->tilesInterior.size() ? &impl_->tilesInterior[di] : nullptr, false);
   const double t0 = Comm::wtime();
   dd_->exchange();
   impl_->exchangeSeconds += Comm::wtime() - t0;
   for (size_t di = 0; di < doms.size(); ++di) {
-    if (opt_.overlap)
-      for (const Rect3 &r : impl_->exterior[di]) launch(di, r);
-    else
-      launch(di, doms[di].get_compute_region());
+    if (opt_.overlap) {
+      for (size_t si = 0; si < impl_->exterior[di].size(); ++si)
+        launch(di, impl_->exterior[di][si], di < impl_->tilesExterior.size() && si < impl_->tilesExterior[di].size() ? &impl_->tilesExterior[di][si] : nullptr,
+               false);
+    } else {
+      launch(di, doms[di].get_compute_region(), tiles_all(di), true);
+    }
   }
   sync();
   dd_->swap();
@@ -905,21 +1175,47 @@ void AstarothSim::sync() {
     DevGuard g(dd_->domains()[di].gpu());
     /* fused faces: my halos of the last iteration are complete only when every neighbour GPU raised its last flag */
     if (impl_->fusedYZ && impl_->iter > 0 && impl_->xHalosFromKernel)
-      launch_wait_flags(impl_->push[di].finalWait, impl_->iter, impl_->err, 5000000000ull, impl_->streams[di]);
+      launch_wait_flags(impl_->push[di].finalWait, impl_->iter, impl_->err, flag_timeout_ns(), impl_->streams[di]);
     CUDA_RUNTIME(cudaStreamSynchronize(impl_->streams[di]));
   }
   dd_->exchange_wait(); // no-op unless an asynchronous exchange is still in flight
   if (impl_->err && *impl_->err) LOG_FATAL("AstarothSim: timed out waiting for a neighbour GPU (code " << *impl_->err << ", iteration " << impl_->iter << ")");
 }
 
-double AstarothSim::run(int iters, double *exchangeSeconds) {
+double AstarothSim::run(int iters, double *exchangeSeconds, double *deviceSeconds) {
   sync();
   dd_->comm().barrier();
   impl_->exchangeSeconds = 0;
+  const size_t nd = dd_->domains().size();
+  std::vector<cudaEvent_t> e0(nd), e1(nd);
+  for (size_t di = 0; di < nd; ++di) {
+    DevGuard g(dd_->domains()[di].gpu());
+    CUDA_RUNTIME(cudaEventCreate(&e0[di]));
+    CUDA_RUNTIME(cudaEventCreate(&e1[di]));
+    CUDA_RUNTIME(cudaEventRecord(e0[di], impl_->streams[di]));
+  }
   const double t0 = Comm::wtime();
   for (int i = 0; i < iters; ++i) step();
+  for (size_t di = 0; di < nd; ++di) {
+    DevGuard g(dd_->domains()[di].gpu());
+    CUDA_RUNTIME(cudaEventRecord(e1[di], impl_->streams[di]));
+  }
   if (impl_->freeRun) sync();
   const double t = dd_->comm().allreduce_max(Comm::wtime() - t0);
+  {
+    float worst = 0;
+    for (size_t di = 0; di < nd; ++di) {
+      DevGuard g(dd_->domains()[di].gpu());
+      CUDA_RUNTIME(cudaEventSynchronize(e1[di]));
+      float ms = 0;
+      CUDA_RUNTIME(cudaEventElapsedTime(&ms, e0[di], e1[di]));
+      worst = std::max(worst, ms);
+      cudaEventDestroy(e0[di]);
+      cudaEventDestroy(e1[di]);
+    }
+    const double dev = dd_->comm().allreduce_max(double(worst) * 1e-3);
+    if (deviceSeconds) *deviceSeconds = dev;
+  }
   if (impl_->freeRun) {
     /* the loop never stops for the exchange, so its share is reported as the cost of the same exchange run alone */
     dd_->comm().barrier();
@@ -955,7 +1251,8 @@ double astaroth_init_value(const Dim3 &p, double period, bool fp64) {
   return fp64 ? v : double(float(v));
 }
 
-template <typename T> static void host_step(std::vector<double> &next, const std::vector<double> &curr, const Dim3 &size, AstarothSim::Stencil st, T dt) {
+template <typename T>
+static void host_step(std::vector<double> &next, const std::vector<double> &curr, const Dim3 &size, AstarothSim::Stencil st, T dt, T eta) {
   const int64_t X = size.x, Y = size.y, Z = size.z;
   next.resize(curr.size());
   auto at = [&](int64_t x, int64_t y, int64_t z) { return T(curr[size_t((((z + 3 * Z) % Z) * Y + (y + 3 * Y) % Y) * X + (x + 3 * X) % X)]); };
@@ -974,6 +1271,18 @@ template <typename T> static void host_step(std::vector<double> &next, const std
             zp[k] = at(x, y, z + k + 1);
           }
           v = star19<T>(at(x, y, z), xm, xp, ym, yp, zm, zp, dt);
+        } else if (st == AstarothSim::Stencil::Star19Cross) {
+          T xm[3], xp[3], ym[3], yp[3], zm[3], zp[3];
+          for (int k = 0; k < 3; ++k) {
+            xm[k] = at(x - k - 1, y, z);
+            xp[k] = at(x + k + 1, y, z);
+            ym[k] = at(x, y - k - 1, z);
+            yp[k] = at(x, y + k + 1, z);
+            zm[k] = at(x, y, z - k - 1);
+            zp[k] = at(x, y, z + k + 1);
+          }
+          auto rel = [&](int dx, int dy, int dz) { return at(x + dx, y + dy, z + dz); };
+          v = star19<T>(at(x, y, z), xm, xp, ym, yp, zm, zp, dt) + dt * (eta * cross_terms<T>(rel));
         } else {
           v = average7<T>(at(x - 1, y, z), at(x, y - 1, z), at(x, y, z - 1), at(x + 1, y, z), at(x, y + 1, z), at(x, y, z + 1));
         }
@@ -981,11 +1290,12 @@ template <typename T> static void host_step(std::vector<double> &next, const std
       }
 }
 
-void astaroth_host_step(std::vector<double> &next, const std::vector<double> &curr, const Dim3 &size, AstarothSim::Stencil st, bool fp64, double dt) {
+void astaroth_host_step(std::vector<double> &next, const std::vector<double> &curr, const Dim3 &size, AstarothSim::Stencil st, bool fp64, double dt,
+                        double crossWeight) {
   if (fp64)
-    host_step<double>(next, curr, size, st, dt);
+    host_step<double>(next, curr, size, st, dt, crossWeight);
   else
-    host_step<float>(next, curr, size, st, float(dt));
+    host_step<float>(next, curr, size, st, float(dt), float(crossWeight));
 }
 
 } // namespace stencil

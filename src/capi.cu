@@ -259,6 +259,14 @@ int stencil_domain_swap(stencil_domain_t *dd) {
   return 0;
 }
 int stencil_domain_num_subdomains(const stencil_domain_t *dd) { return dd ? int(dd->dd->domains().size()) : -1; }
+int stencil_domain_grid(const stencil_domain_t *dd, int64_t grid_out[3]) {
+  if (!dd || !grid_out) return -1;
+  put(grid_out, dd->dd->subdomain_grid());
+  return 0;
+}
+double stencil_domain_time_exchange(stencil_domain_t *dd, int iters, double *device_seconds) {
+  return dd && iters > 0 ? dd->dd->time_exchange(iters, device_seconds) : -1.0;
+}
 uint64_t stencil_domain_exchange_bytes(const stencil_domain_t *dd, int methods) {
   return dd ? dd->dd->exchange_bytes_for_method(static_cast<MethodFlags>(methods)) : 0;
 }
@@ -350,6 +358,15 @@ int stencil_jacobi_sync(stencil_jacobi_t *j) {
 }
 double stencil_jacobi_run(stencil_jacobi_t *j, int iters) { return j ? j->j->run(iters) : -1.0; }
 double stencil_jacobi_checksum(stencil_jacobi_t *j) { return j ? j->j->checksum() : 0.0; }
+uint64_t stencil_jacobi_fingerprint(stencil_jacobi_t *j) { return j ? j->j->fingerprint() : 0; }
+int stencil_jacobi_init_random(stencil_jacobi_t *j, unsigned seed) {
+  if (!j) return -1;
+  j->j->init_random(seed);
+  return 0;
+}
+float stencil_jacobi_random_value(unsigned seed, int64_t x, int64_t y, int64_t z, int64_t gx, int64_t gy, int64_t gz) {
+  return stencil::jacobi_random_value(seed, Dim3(x, y, z), Dim3(gx, gy, gz));
+}
 int stencil_jacobi_probe(stencil_jacobi_t *j, int64_t x, int64_t y, int64_t z, float *out) {
   if (!j || !out) return -1;
   return j->j->probe(Dim3(x, y, z), out) ? 1 : 0;
@@ -378,13 +395,18 @@ int stencil_jacobi_host_step(float *next, const float *curr, int64_t x, int64_t 
 }
 
 /* ---- AstarothSim ---- */
+static stencil::AstarothSim::Stencil astaroth_kind(int k) {
+  return k == STENCIL_ASTAROTH_STAR19_CROSS ? stencil::AstarothSim::Stencil::Star19Cross
+                                            : (k == STENCIL_ASTAROTH_STAR19 ? stencil::AstarothSim::Stencil::Star19 : stencil::AstarothSim::Stencil::Average7);
+}
+
 stencil_astaroth_t *stencil_astaroth_create(uint64_t x, uint64_t y, uint64_t z, int methods, int placement, int stencil_kind, int fields,
                                             int fp64, int overlap, const int *gpus, int ngpus, double dt) {
   if (fields < 1) return nullptr;
   stencil::AstarothSim::Options opt;
   opt.methods = static_cast<MethodFlags>(methods);
   opt.placement = placement == STENCIL_PLACEMENT_TRIVIAL ? PlacementStrategy::Trivial : PlacementStrategy::NodeAware;
-  opt.stencil = stencil_kind == STENCIL_ASTAROTH_STAR19 ? stencil::AstarothSim::Stencil::Star19 : stencil::AstarothSim::Stencil::Average7;
+  opt.stencil = astaroth_kind(stencil_kind);
   opt.fields = fields;
   opt.fp64 = fp64 != 0;
   opt.autoSchedule = overlap < 0;
@@ -413,6 +435,9 @@ int stencil_astaroth_sync(stencil_astaroth_t *a) {
   return 0;
 }
 double stencil_astaroth_run(stencil_astaroth_t *a, int iters, double *exchange_seconds) { return a ? a->a->run(iters, exchange_seconds) : -1.0; }
+double stencil_astaroth_run_timed(stencil_astaroth_t *a, int iters, double *exchange_seconds, double *device_seconds) {
+  return a ? a->a->run(iters, exchange_seconds, device_seconds) : -1.0;
+}
 uint64_t stencil_astaroth_launches(const stencil_astaroth_t *a) { return a ? a->a->launches() : 0; }
 int stencil_astaroth_gather(stencil_astaroth_t *a, int field, double *out, uint64_t count) {
   if (!a || !out || field < 0 || field >= a->a->options().fields) return -1;
@@ -425,7 +450,7 @@ int stencil_astaroth_host_step(double *next, const double *curr, int64_t x, int6
   if (!next || !curr || x < 1 || y < 1 || z < 1) return -1;
   std::vector<double> c(curr, curr + x * y * z), n;
   stencil::astaroth_host_step(n, c, Dim3(x, y, z),
-                              stencil_kind == STENCIL_ASTAROTH_STAR19 ? stencil::AstarothSim::Stencil::Star19 : stencil::AstarothSim::Stencil::Average7,
+                              astaroth_kind(stencil_kind),
                               fp64 != 0, dt);
   std::memcpy(next, n.data(), n.size() * sizeof(double));
   return 0;

@@ -630,6 +630,40 @@ __global__ void fill_kernel(float *interior, long long pitchX, long long pitchXY
   for (int z = blockIdx.z; z < sz; z += gridDim.z) interior[(long long)z * pitchXY + (long long)y * pitchX + x] = v;
 }
 
+__host__ __device__ inline unsigned long long mix64(unsigned long long h) {
+  h ^= h >> 30;
+  h *= 0xBF58476D1CE4E5B9ull;
+  h ^= h >> 27;
+  h *= 0x94D049BB133111EBull;
+  h ^= h >> 31;
+  return h;
+}
+__host__ __device__ inline float random_value(unsigned seed, unsigned long long globalIndex) {
+  return float(unsigned(mix64(globalIndex + (unsigned long long)seed * 0x9E3779B97F4A7C15ull) >> 40)) * (1.0f / 16777216.0f);
+}
+
+__global__ void fill_random_kernel(float *interior, long long pitchX, long long pitchXY, int sx, int sy, int sz, long long ox, long long oy,
+                                   long long oz, long long gx, long long gy, unsigned seed) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y;
+  if (x >= sx || y >= sy) return;
+  for (int z = blockIdx.z; z < sz; z += gridDim.z)
+    interior[(long long)z * pitchXY + (long long)y * pitchX + x] = random_value(seed, (unsigned long long)(((oz + z) * gy + oy + y) * gx + ox + x));
+}
+
+__global__ void fingerprint_kernel(const float *interior, long long pitchX, long long pitchXY, int sx, int sy, int sz, long long ox, long long oy,
+                                   long long oz, long long gx, long long gy, unsigned long long *out) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y;
+  unsigned long long acc = 0;
+  if (x < sx && y < sy)
+    for (int z = blockIdx.z; z < sz; z += gridDim.z) {
+      const unsigned long long g = (unsigned long long)(((oz + z) * gy + oy + y) * gx + ox + x);
+      const unsigned bits = __float_as_uint(interior[(long long)z * pitchXY + (long long)y * pitchX + x]);
+      acc += mix64(((unsigned long long)bits << 32 | 0x5bd1e995u) ^ mix64(g + 1));
+    }
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+  if (((threadIdx.y * blockDim.x + threadIdx.x) & 31) == 0 && acc) atomicAdd(out, acc);
+}
+
 struct DevGuard {
   int prev = 0;
   explicit DevGuard(int d) {
@@ -994,15 +1028,28 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
   init();
 }
 
-void Jacobi3D::init() {
+void Jacobi3D::init() { fill(false, 0); }
+void Jacobi3D::init_random(unsigned seed) { fill(true, seed); }
+
+void Jacobi3D::fill(bool random, unsigned seed) {
   std::vector<LocalDomain> &doms = dd_->domains();
+  /* neighbours may still be storing the last iteration's faces into these buffers */
+  if (impl_->iter > 0) {
+    sync();
+    dd_->comm().barrier();
+  }
+  const Dim3 global = dd_->size();
   for (size_t di = 0; di < doms.size(); ++di) {
     LocalDomain &ld = doms[di];
     Impl::Dom &d = impl_->doms[di];
     DevGuard g(ld.gpu());
     const JacobiParams &P = d.base[ld.parity()];
     const dim3 block(128, 4, 1), grid(unsigned((P.sx + 127) / 128), unsigned((P.sy + 3) / 4), unsigned(std::min(P.sz, 64)));
-    fill_kernel<<<grid, block, 0, d.stream>>>(const_cast<float *>(P.src), P.pitchX, P.pitchXY, P.sx, P.sy, P.sz, 0.5f);
+    if (random)
+      fill_random_kernel<<<grid, block, 0, d.stream>>>(const_cast<float *>(P.src), P.pitchX, P.pitchXY, P.sx, P.sy, P.sz, P.ox, P.oy, P.oz, global.x,
+                                                       global.y, seed);
+    else
+      fill_kernel<<<grid, block, 0, d.stream>>>(const_cast<float *>(P.src), P.pitchX, P.pitchXY, P.sx, P.sy, P.sz, 0.5f);
     CUDA_RUNTIME(cudaGetLastError());
     ++launches_;
   }
@@ -1180,6 +1227,39 @@ double Jacobi3D::checksum() {
   double s = 0;
   for (double v : all) s += v;
   return s;
+}
+
+unsigned long long Jacobi3D::fingerprint() {
+  sync();
+  std::vector<LocalDomain> &doms = dd_->domains();
+  const Dim3 global = dd_->size();
+  unsigned long long total = 0;
+  for (size_t di = 0; di < doms.size(); ++di) {
+    LocalDomain &ld = doms[di];
+    Impl::Dom &d = impl_->doms[di];
+    DevGuard g(ld.gpu());
+    const JacobiParams &P = d.base[ld.parity()];
+    /* the per-face counters are idle between iterations; word 6 of that block is free: use words 6..7 as the accumulator */
+    unsigned long long *acc = reinterpret_cast<unsigned long long *>(d.doneCounter + 6);
+    CUDA_RUNTIME(cudaMemsetAsync(acc, 0, sizeof(unsigned long long), d.stream));
+    const dim3 block(128, 4, 1), grid(unsigned((P.sx + 127) / 128), unsigned((P.sy + 3) / 4), unsigned(std::min(P.sz, 64)));
+    fingerprint_kernel<<<grid, block, 0, d.stream>>>(P.src, P.pitchX, P.pitchXY, P.sx, P.sy, P.sz, P.ox, P.oy, P.oz, global.x, global.y, acc);
+    CUDA_RUNTIME(cudaGetLastError());
+    unsigned long long h = 0;
+    CUDA_RUNTIME(cudaMemcpyAsync(&h, acc, sizeof(h), cudaMemcpyDeviceToHost, d.stream));
+    CUDA_RUNTIME(cudaStreamSynchronize(d.stream));
+    total += h;
+    ++launches_;
+  }
+  std::vector<unsigned long long> all(static_cast<size_t>(dd_->comm().size()));
+  dd_->comm().allgather(&total, all.data(), sizeof(total));
+  unsigned long long s = 0;
+  for (unsigned long long v : all) s += v;
+  return s;
+}
+
+float jacobi_random_value(unsigned seed, const Dim3 &p, const Dim3 &global) {
+  return random_value(seed, (unsigned long long)((p.z * global.y + p.y) * global.x + p.x));
 }
 
 bool Jacobi3D::probe(const Dim3 &p, float *out) {

@@ -1031,6 +1031,33 @@ void DistributedDomain::exchange() {
   if (exchangeStats_) timeExchange_ += comm_->allreduce_max(stencil::Comm::wtime() - t);
 }
 
+double DistributedDomain::time_exchange(int iters, double *deviceSeconds) {
+  std::vector<cudaEvent_t> t0(domains_.size()), t1(domains_.size());
+  comm_->barrier();
+  for (size_t di = 0; di < domains_.size(); ++di) {
+    stencil::DevGuard g(domains_[di].gpu());
+    CUDA_RUNTIME(cudaEventCreate(&t0[di]));
+    CUDA_RUNTIME(cudaEventCreate(&t1[di]));
+    CUDA_RUNTIME(cudaEventRecord(t0[di], exchange_stream(di)));
+  }
+  double elapsed = stencil::Comm::wtime();
+  for (int i = 0; i < iters; ++i) ex_->exchange();
+  elapsed = comm_->allreduce_max(stencil::Comm::wtime() - elapsed);
+  float worst = 0;
+  for (size_t di = 0; di < domains_.size(); ++di) {
+    stencil::DevGuard g(domains_[di].gpu());
+    CUDA_RUNTIME(cudaEventRecord(t1[di], exchange_stream(di)));
+    CUDA_RUNTIME(cudaEventSynchronize(t1[di]));
+    float ms = 0;
+    CUDA_RUNTIME(cudaEventElapsedTime(&ms, t0[di], t1[di]));
+    worst = std::max(worst, ms);
+    cudaEventDestroy(t0[di]);
+    cudaEventDestroy(t1[di]);
+  }
+  if (deviceSeconds) *deviceSeconds = comm_->allreduce_max(double(worst) * 1e-3);
+  return elapsed;
+}
+
 std::vector<Rect3> DistributedDomain::get_interior() const {
   std::vector<Rect3> out;
   for (const LocalDomain &d : domains_) {

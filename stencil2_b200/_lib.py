@@ -67,6 +67,8 @@ def _declare(l):
         "stencil_domain_exchange_after": (i, [vp, i, vp]),
         "stencil_domain_swap": (i, [vp]),
         "stencil_domain_num_subdomains": (i, [vp]),
+        "stencil_domain_grid": (i, [vp, I64x3]),
+        "stencil_domain_time_exchange": (dbl, [vp, i, P(dbl)]),
         "stencil_domain_exchange_bytes": (u64, [vp, i]),
         "stencil_domain_write_paraview": (i, [vp, C.c_char_p, i]),
         "stencil_subdomain_info": (i, [vp, i, I64x3, I64x3, I64x3, P(i)]),
@@ -78,6 +80,9 @@ def _declare(l):
         "stencil_jacobi_create": (vp, [u64, u64, u64, i, i, i, P(i), i, i]),
         "stencil_jacobi_destroy": (None, [vp]),
         "stencil_jacobi_init": (i, [vp]),
+        "stencil_jacobi_init_random": (i, [vp, C.c_uint]),
+        "stencil_jacobi_random_value": (C.c_float, [C.c_uint, i64, i64, i64, i64, i64, i64]),
+        "stencil_jacobi_fingerprint": (u64, [vp]),
         "stencil_jacobi_step": (i, [vp]),
         "stencil_jacobi_sync": (i, [vp]),
         "stencil_jacobi_run": (dbl, [vp, i]),
@@ -94,6 +99,7 @@ def _declare(l):
         "stencil_astaroth_step": (i, [vp]),
         "stencil_astaroth_sync": (i, [vp]),
         "stencil_astaroth_run": (dbl, [vp, i, P(dbl)]),
+        "stencil_astaroth_run_timed": (dbl, [vp, i, P(dbl), P(dbl)]),
         "stencil_astaroth_launches": (u64, [vp]),
         "stencil_astaroth_gather": (i, [vp, i, vp, u64]),
         "stencil_astaroth_host_step": (i, [vp, vp, i64, i64, i64, i, i, dbl]),

@@ -1,6 +1,7 @@
 """AstarothSim: the reference's multi-field radius-3 workload (bin/astaroth_sim.cu) on the native engine
-(src/astaroth.cu): `fields` quantities of fp32 or fp64, the reference's 7-point stand-in or a real 19-point
-6th-order Laplacian step, TMA-pipelined kernel on B200."""
+(src/astaroth.cu): `fields` quantities of fp32 or fp64, the reference's 7-point stand-in, a real 19-point
+6th-order Laplacian step, or that step plus cross-derivative terms (reads all 26 halo directions); TMA-pipelined
+kernel on B200."""
 import ctypes as C
 
 import numpy as np
@@ -10,7 +11,7 @@ from .domain import DistributedDomain, Method, Placement
 
 
 class AstarothSim:
-    AVERAGE7, STAR19 = 0, 1
+    AVERAGE7, STAR19, STAR19_CROSS = 0, 1, 2
 
     def __init__(self, x, y, z, fields=1, fp64=False, stencil=0, overlap=None, methods=Method.ALL, placement=Placement.NODE_AWARE,
                  gpus=None, dt=0.01):
@@ -50,6 +51,12 @@ class AstarothSim:
         ex = C.c_double(0)
         t = lib().stencil_astaroth_run(self._h, int(iters), C.byref(ex))
         return t, ex.value
+
+    def run_timed(self, iters):
+        """(host seconds, seconds inside exchange(), device seconds between CUDA events around the loop)."""
+        ex, dev = C.c_double(0), C.c_double(0)
+        t = lib().stencil_astaroth_run_timed(self._h, int(iters), C.byref(ex), C.byref(dev))
+        return t, ex.value, dev.value
 
     @property
     def launches(self):

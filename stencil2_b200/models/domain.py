@@ -136,6 +136,19 @@ class DistributedDomain:
         """The next exchange_async() starts after `cuda_event` (raw cudaEvent_t handle, e.g. torch.cuda.Event().cuda_event)."""
         lib().stencil_domain_exchange_after(self._h, int(subdomain), cuda_event)
 
+    def time_exchange(self, iters):
+        """(host seconds, device seconds) of `iters` blocking exchanges, max over ranks (what weak-exchange prints)."""
+        dev = C.c_double(0)
+        t = lib().stencil_domain_time_exchange(self._h, int(iters), C.byref(dev))
+        return t, dev.value
+
+    @property
+    def grid(self):
+        """Subdomains along (x, y, z) over the whole job."""
+        g = I64x3()
+        lib().stencil_domain_grid(self._h, g)
+        return tuple(g)
+
     def swap(self):
         lib().stencil_domain_swap(self._h)
 

@@ -34,6 +34,14 @@ class Jacobi3D:
     def init(self):
         lib().stencil_jacobi_init(self._h)
 
+    def init_random(self, seed=1):
+        """Initial field = pseudo-random values in [0,1) that depend only on the seed and the global cell coordinate."""
+        lib().stencil_jacobi_init_random(self._h, int(seed))
+
+    def fingerprint(self):
+        """64-bit fingerprint of the whole field over all ranks; equal between two runs exactly when every cell agrees."""
+        return int(lib().stencil_jacobi_fingerprint(self._h))
+
     def step(self):
         lib().stencil_jacobi_step(self._h)
 

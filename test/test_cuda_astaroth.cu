@@ -8,7 +8,7 @@
 
 namespace {
 double max_abs_err(const Dim3 &size, stencil::AstarothSim::Stencil st, bool fp64, int fields, const std::vector<int> &gpus, bool overlap, int iters,
-                   MethodFlags methods = MethodFlags::All) {
+                   MethodFlags methods = MethodFlags::All, bool useTma = true, bool narrowTiles = true) {
   stencil::AstarothSim::Options opt;
   opt.stencil = st;
   opt.fp64 = fp64;
@@ -18,6 +18,8 @@ double max_abs_err(const Dim3 &size, stencil::AstarothSim::Stencil st, bool fp64
   opt.autoSchedule = false; // test exactly the schedule asked for
   opt.tileZ = 8;
   opt.methods = methods;
+  opt.useTma = useTma;
+  opt.narrowTiles = narrowTiles;
   stencil::AstarothSim sim(size_t(size.x), size_t(size.y), size_t(size.z), opt);
   /* start from the device's own initial field: the device and host sin() differ in the last bits of a double */
   std::vector<double> ref = sim.gather(0), tmp;
@@ -29,7 +31,7 @@ double max_abs_err(const Dim3 &size, stencil::AstarothSim::Stencil st, bool fp64
   if (!(initErr < 1e-6)) return 1e30; // the initial condition itself is wrong
   for (int it = 0; it < iters; ++it) {
     sim.step();
-    stencil::astaroth_host_step(tmp, ref, size, st, fp64, opt.dt);
+    stencil::astaroth_host_step(tmp, ref, size, st, fp64, opt.dt, opt.crossWeight);
     ref.swap(tmp);
   }
   double worst = 0;
@@ -79,6 +81,35 @@ TEST_CASE("astaroth: 19-point radius-3 stencil, fp64 and fp32, many fields and s
   REQUIRE(max_abs_err(Dim3(64, 35, 50), S::Star19, true, 2, {0, 0, 0}, false, 8) < 1e-13);
 }
 
+TEST_CASE("astaroth: rows that are not a multiple of the tile use narrow remainder tiles", "[cuda][astaroth][narrow]") {
+  using S = stencil::AstarothSim::Stencil;
+  /* fp64: wide 64 x 16, narrow 16 x 64; fp32: wide 128 x 16, narrow 32 x 64 */
+  REQUIRE(max_abs_err(Dim3(70, 70, 20), S::Star19, true, 2, {0}, false, 5) < 1e-13);     // 64 + 6: one narrow column, two narrow row blocks
+  REQUIRE(max_abs_err(Dim3(100, 40, 20), S::Star19, true, 2, {0, 0}, false, 5) < 1e-13); // 64 + 36: three narrow columns
+  REQUIRE(max_abs_err(Dim3(120, 24, 20), S::Star19, true, 1, {0}, false, 4) < 1e-13);    // 64 + 56: a second wide column instead
+  REQUIRE(max_abs_err(Dim3(200, 70, 14), S::Star19, false, 2, {0}, false, 5) < 2e-5);    // 128 + 72: three narrow fp32 columns
+  REQUIRE(max_abs_err(Dim3(150, 37, 21), S::Star19, true, 2, {0, 0}, true, 3) < 1e-13);  // overlap schedule: interior / exterior tile tables
+  REQUIRE(max_abs_err(Dim3(70, 70, 20), S::Star19, true, 2, {0}, false, 5, MethodFlags::All, true, false) < 1e-13); // remainder tiles off
+}
+
+TEST_CASE("astaroth: cross-derivative stencil reads edge and corner halos", "[cuda][astaroth][cross]") {
+  using S = stencil::AstarothSim::Stencil;
+  /* plain kernel (one thread per cell), exchange() every step */
+  REQUIRE(max_abs_err(Dim3(40, 24, 20), S::Star19Cross, true, 1, {0}, true, 3, MethodFlags::All, false) < 1e-12);
+  REQUIRE(max_abs_err(Dim3(41, 23, 19), S::Star19Cross, true, 2, {0, 0, 0}, false, 3, MethodFlags::All, false) < 1e-12);
+  REQUIRE(max_abs_err(Dim3(40, 24, 20), S::Star19Cross, false, 2, {0, 0}, true, 3, MethodFlags::All, false) < 5e-5);
+  /* pipelined kernel, overlap schedule (exchange() every step, tile tables of interior and exterior) */
+  REQUIRE(max_abs_err(Dim3(150, 37, 21), S::Star19Cross, true, 2, {0, 0}, true, 3) < 1e-12);
+  REQUIRE(max_abs_err(Dim3(150, 37, 21), S::Star19Cross, false, 2, {0}, true, 3) < 5e-5);
+  /* pipelined kernel, fused: after the first step every halo — faces, the 12 edges, the 8 corners — comes from the
+     kernels' own pushes; a wrong or stale edge / corner block shows up here */
+  REQUIRE(max_abs_err(Dim3(64, 40, 64), S::Star19Cross, true, 2, {0}, false, 6) < 1e-12);
+  REQUIRE(max_abs_err(Dim3(64, 40, 64), S::Star19Cross, true, 2, {0, 0}, false, 8) < 1e-12);
+  REQUIRE(max_abs_err(Dim3(70, 44, 50), S::Star19Cross, true, 3, {0, 0, 0, 0}, false, 8) < 1e-12);
+  REQUIRE(max_abs_err(Dim3(64, 35, 50), S::Star19Cross, true, 1, {0, 0, 0}, false, 8) < 1e-12);
+  REQUIRE(max_abs_err(Dim3(133, 40, 36), S::Star19Cross, false, 2, {0, 0, 0, 0}, false, 8) < 1e-4);
+}
+
 TEST_CASE("astaroth: all visible GPUs", "[cuda][astaroth][multigpu]") {
   int n = 0;
   cudaGetDeviceCount(&n);
@@ -98,4 +129,9 @@ TEST_CASE("astaroth: all visible GPUs", "[cuda][astaroth][multigpu]") {
   std::vector<int> twice = gpus;
   twice.insert(twice.end(), gpus.begin(), gpus.end());
   REQUIRE(max_abs_err(Dim3(66, 48, 64), S::Star19, true, 2, twice, false, 7) < 1e-13);
+  /* all 26 directions from the kernels' pushes across GPUs, checked through the cross terms; odd sizes give uneven
+     subdomains and narrow remainder tiles */
+  REQUIRE(max_abs_err(Dim3(64, 48, 64), S::Star19Cross, true, 3, gpus, false, 8) < 1e-12);
+  REQUIRE(max_abs_err(Dim3(70, 50, 66), S::Star19Cross, true, 2, gpus, false, 9) < 1e-12);
+  REQUIRE(max_abs_err(Dim3(70, 50, 66), S::Star19Cross, true, 2, twice, false, 7) < 1e-12);
 }

@@ -149,6 +149,18 @@ def test_host_astaroth_step_against_numpy(built):
     c = astaroth_host_step(a, stencil=0, fp64=True)
     avg = sum(np.roll(a, s, ax) for ax in range(3) for s in (1, -1)) / 6
     assert np.allclose(c, avg, rtol=0, atol=1e-13)
+    # cross-derivative variant: 6th-order mixed second derivatives along the diagonals of the three planes plus the
+    # d3/dxdydz corner term, weight 0.25 (array axes are [z, y, x]; f(x+k) is np.roll(a, -k, axis=2))
+    d = astaroth_host_step(a, stencil=2, fp64=True, dt=dt)
+    sh = lambda dx, dy, dz: np.roll(a, (-dz, -dy, -dx), axis=(0, 1, 2))
+    cross = np.zeros_like(a)
+    for k, m in ((1, 270.0 / 720.0), (2, -27.0 / 720.0), (3, 2.0 / 720.0)):
+        cross += m * (sh(k, k, 0) - sh(k, -k, 0) - sh(-k, k, 0) + sh(-k, -k, 0))
+        cross += m * (sh(k, 0, k) - sh(-k, 0, k) - sh(k, 0, -k) + sh(-k, 0, -k))
+        cross += m * (sh(0, k, k) - sh(0, -k, k) - sh(0, k, -k) + sh(0, -k, -k))
+    cross += (270.0 / 720.0) * sum(sx * sy * sz * sh(sx, sy, sz) for sx in (1, -1) for sy in (1, -1) for sz in (1, -1))
+    assert np.allclose(d, a + dt * (lap + 0.25 * cross), rtol=0, atol=1e-12)
+    assert np.abs(cross).max() > 0.1  # the terms are really there
 
 
 def test_two_process_tcp_group(built, tmp_path):

@@ -1,17 +1,20 @@
 #!/bin/bash
-# Scratch script for one-off GPU experiments (edited per experiment, run through gpurun). The kept measurement
-# scripts are gpu_tests.sh (pytest -m gpu), gpu_multi.sh N (multi-GPU validation + benches), gpu_ncu.sh (ncu captures),
-# gpu_perf.sh / gpu_apps.sh (app-level numbers).
+# Scratch script for one-off GPU experiments (edited per experiment, run through gpurun).
 mkdir -p gpurun_out
 cd /root/repo
 export STENCIL_LOG_LEVEL=1
 O=gpurun_out/exp.txt
 : > $O
-timeout 600 ./build/bin/test_cuda "[jacobi]" > gpurun_out/test_jacobi.log 2>&1; echo "test_jacobi rc=$? $(tail -1 gpurun_out/test_jacobi.log)" >> $O
 J=./build/bin/jacobi3d
-for sz in "512 512 512" "645 645 323" "813 407 407" "1024 512 256"; do
-  echo "## $sz narrow" >> $O; timeout 120 $J $sz --exact-size -n 30 --tile-z 16 --device-time 2>/dev/null >> $O
-  echo "## $sz wide only" >> $O; STENCIL_JACOBI_NO_NARROW=1 timeout 120 $J $sz --exact-size -n 30 --tile-z 16 --device-time 2>/dev/null >> $O
+run() { echo "## $*" >> $O; timeout 120 "$@" 2>/dev/null | grep device >> $O; }
+for sz in "512 512 512" "1024 512 256" "1024 256 512" "512 1024 256" "512 256 1024" "2048 256 256" "256 1024 512"; do
+  run $J $sz --exact-size -n 30 --tile-z 16 --device-time
 done
-timeout 300 python bench.py --steps 30 --warmup 5 > gpurun_out/bench1.json 2> gpurun_out/bench1.err; echo "bench rc=$?" >> $O
-cat $O; grep -B2 -A8 FAIL gpurun_out/test_jacobi.log | head -40; cat gpurun_out/bench1.json
+run $J 1024 512 256 --exact-size -n 30 --tile-z 32 --device-time
+run $J 1024 512 256 --exact-size -n 30 --tile-z 64 --device-time
+run $J 1024 512 256 --exact-size -n 30 --tile-z 8 --device-time
+STENCIL_JACOBI_DEBUG_SKIP=6 run $J 1024 512 256 --exact-size -n 30 --tile-z 16 --device-time
+STENCIL_JACOBI_DEBUG_SKIP=6 run $J 512 512 512 --exact-size -n 30 --tile-z 16 --device-time
+run $J 1024 512 256 --exact-size -n 30 --tile-z 16 --device-time --no-overlap
+run $J 512 512 512 --exact-size -n 30 --tile-z 16 --device-time --no-overlap
+cat $O
