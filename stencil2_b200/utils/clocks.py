@@ -13,9 +13,13 @@ _REASONS = {
 
 
 class ClockSampler:
-    def __init__(self, device_index=0, period_s=0.05):
-        self.idx, self.period = device_index, period_s
+    def __init__(self, device_index=0, period_s=0.05, busy_only=False):
+        """busy_only: keep only samples taken while the GPU was not idle (NVML's gpu_idle reason clear) — for a timed
+        region that this process cannot bracket exactly, e.g. a benchmark binary run as a subprocess, whose set-up
+        phase would otherwise drag the median down to the idle clock."""
+        self.idx, self.period, self.busy_only = device_index, period_s, busy_only
         self.samples, self.reasons, self.max_mhz = [], set(), None
+        self.idle_samples = []
         self._stop = threading.Event()
         self._thread = None
         self._proc = None
@@ -45,11 +49,16 @@ class ClockSampler:
         nv = self._nv
         while not self._stop.is_set():
             try:
-                self.samples.append(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM))
+                mhz = nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM)
                 try:
                     mask = nv.nvmlDeviceGetCurrentClocksEventReasons(self._h)
                 except Exception:
                     mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self._h)
+                if self.busy_only and (mask & 0x1):
+                    self.idle_samples.append(mhz)
+                    time.sleep(self.period)
+                    continue
+                self.samples.append(mhz)
                 for bit, name in _REASONS.items():
                     if mask & bit and name != "gpu_idle":
                         self.reasons.add(name)
@@ -81,6 +90,9 @@ class ClockSampler:
         return self.summary()
 
     def summary(self):
+        if not self.samples and self.idle_samples:  # never saw the GPU busy: say so instead of reporting nothing
+            return {"sm_mhz": int(statistics.median(self.idle_samples)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                    "samples": 0, "idle_samples": len(self.idle_samples), "source": self._mode, "note": "no sample caught the GPU busy"}
         if not self.samples:
             return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "source": self._mode or "unavailable"}
         return {"sm_mhz": int(statistics.median(self.samples)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
