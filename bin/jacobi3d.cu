@@ -6,6 +6,7 @@
    Additions: --direct (MethodFlags::NvlinkDirect), --no-fused (use the reference's exchange() schedule instead of
    the fused compute+push kernel), --exact-size (do not weak-scale the positional size), --tile-z. */
 #include <cmath>
+#include <cstdio>
 #include <iostream>
 
 #include "common.hpp"
@@ -16,6 +17,8 @@ int main(int argc, char **argv) {
   MethodArgs methodArgs;
   bool trivial = false, noOverlap = false, paraview = false, noFused = false, exactSize = false, ldg = false, naturalOrder = false;
   bool deviceTime = false;
+  int verifyIters = 0, delayRank = 0;
+  double delayUs = 0;
   size_t x = 512, y = 512, z = 512;
   std::string prefix;
   int iters = 30, period = -1, tileZ = 32;
@@ -28,6 +31,10 @@ int main(int argc, char **argv) {
   parser.add_flag(ldg, "--ldg")->help("use the plain-load kernel variant instead of the TMA pipeline");
   parser.add_flag(naturalOrder, "--natural-order")->help("do not schedule the tiles that push to other GPUs first");
   parser.add_flag(deviceTime, "--device-time")->help("also print the free-running device time per iteration (no host sync in the loop)");
+  parser.add_option(verifyIters, "--verify")->help("instead of timing: N iterations from a random field with the plain kernel + exchange() and "
+                                                    "with the fused kernel, then compare the fingerprints of the two fields");
+  parser.add_option(delayUs, "--delay-us")->help("--verify: hold back one GPU by this many microseconds before every fused iteration");
+  parser.add_option(delayRank, "--delay-rank")->help("--verify: the rank whose first GPU is held back (default 0)");
   parser.add_flag(exactSize, "--exact-size")->help("use X Y Z as the whole domain (no weak scaling)");
   parser.add_option(prefix, "--prefix")->help("prefix for paraview files");
   parser.add_flag(paraview, "--paraview")->help("dump paraview files");
@@ -65,6 +72,37 @@ int main(int argc, char **argv) {
   }
 
   const MethodFlags methods = methodArgs.flags();
+
+  if (verifyIters > 0) {
+    /* fused == plain, bit for bit, on this size and these GPUs; the fingerprint does not depend on the partition */
+    unsigned long long fp[2] = {0, 0};
+    for (int pass = 0; pass < 2; ++pass) {
+      stencil::Jacobi3D::Options opt;
+      opt.methods = methods;
+      opt.placement = trivial ? PlacementStrategy::Trivial : PlacementStrategy::NodeAware;
+      opt.mode = pass == 0 ? stencil::Jacobi3D::Mode::NoOverlap : stencil::Jacobi3D::Mode::Fused;
+      opt.tileZ = tileZ;
+      opt.useTma = !ldg;
+      opt.flaggedFirst = !naturalOrder;
+      stencil::Jacobi3D solver(x, y, z, opt);
+      solver.init_random(12345);
+      for (int iter = 0; iter < verifyIters; ++iter) {
+        if (pass == 1 && delayUs > 0 && rank == delayRank) solver.delay(0, (unsigned long long)(delayUs * 1e3));
+        solver.step();
+      }
+      fp[pass] = solver.fingerprint();
+      if (pass == 1 && solver.mode() != stencil::Jacobi3D::Mode::Fused && rank == 0) std::cerr << "fused mode not available: compared plain with overlap\n";
+    }
+    const bool ok = fp[0] == fp[1];
+    if (rank == 0) {
+      char line[256];
+      std::snprintf(line, sizeof(line), "jacobi3d-verify,%d,%d,%zu,%zu,%zu,%d,%016llx,%016llx,%s", size, devCount, x, y, z, verifyIters, fp[0], fp[1],
+                    ok ? "ok" : "FAILED");
+      std::cout << line << "\n";
+    }
+    stencil::finalize_world();
+    return ok ? 0 : 1;
+  }
 
   Statistics iterTime;
   {

@@ -32,6 +32,11 @@ public:
 
   /* eager tagged send; returns once the payload is buffered or on the wire */
   virtual void send(int dst, int tag, const void *buf, size_t bytes) = 0;
+  /* Block until every buffer handed to send() so far may be reused. Communicators that copy the payload inside
+     send() (all the built-in ones for host pointers) have nothing to do. A communicator that sends IN PLACE — MpiComm
+     with device pointers — completes its outstanding sends here; callers invoke it only after they have posted or
+     finished their own receives, so two ranks sending each other rendezvous-sized messages cannot block each other. */
+  virtual void flush_sends() {}
   /* non-blocking: true and fills buf iff a matching (src, tag) message of exactly `bytes` has arrived */
   virtual bool try_recv(int src, int tag, void *buf, size_t bytes) = 0;
   /* blocking receive (spins on try_recv with a timeout; fatal on timeout) */

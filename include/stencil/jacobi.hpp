@@ -66,6 +66,10 @@ public:
   double run(int iters);
   /* kernels enqueued by this object so far (all local GPUs) */
   unsigned long long launches() const { return launches_; }
+  /* test hook: keep the stream of local subdomain di busy for about `ns` nanoseconds before whatever is enqueued
+     next, so that this GPU falls behind its neighbours (opens the window in which a fast neighbour's pushes of
+     iteration k+1 could overtake this GPU's reads of iteration k if the flag protocol were wrong) */
+  void delay(size_t di, unsigned long long ns);
 
   /* sum of curr over the compute regions of all ranks (fp64 accumulation) */
   double checksum();

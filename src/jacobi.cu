@@ -642,6 +642,11 @@ __host__ __device__ inline float random_value(unsigned seed, unsigned long long 
   return float(unsigned(mix64(globalIndex + (unsigned long long)seed * 0x9E3779B97F4A7C15ull) >> 40)) * (1.0f / 16777216.0f);
 }
 
+__global__ void spin_kernel(unsigned long long ns) {
+  const unsigned long long t0 = globaltimer_ns();
+  while (globaltimer_ns() - t0 < ns) __nanosleep(256);
+}
+
 __global__ void fill_random_kernel(float *interior, long long pitchX, long long pitchXY, int sx, int sy, int sz, long long ox, long long oy,
                                    long long oz, long long gx, long long gy, unsigned seed) {
   const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y;
@@ -1227,6 +1232,13 @@ double Jacobi3D::checksum() {
   double s = 0;
   for (double v : all) s += v;
   return s;
+}
+
+void Jacobi3D::delay(size_t di, unsigned long long ns) {
+  if (di >= impl_->doms.size()) return;
+  DevGuard g(dd_->domains()[di].gpu());
+  spin_kernel<<<1, 1, 0, impl_->doms[di].stream>>>(ns);
+  CUDA_RUNTIME(cudaGetLastError());
 }
 
 unsigned long long Jacobi3D::fingerprint() {

@@ -69,16 +69,29 @@ public:
   void send(int dst, int tag, const void *buf, size_t bytes) override {
     reap();
     if (bytes > size_t(2147483647)) LOG_FATAL("MpiComm::send: message of " << bytes << " B exceeds INT_MAX");
-    if (device_buffers()) { // may be a device pointer: cannot be copied with memcpy, send in place and complete
-      MPI_Request req;
-      MPI_Isend(buf, int(bytes), MPI_BYTE, dst, fold(tag), comm_, &req);
-      MPI_Wait(&req, MPI_STATUS_IGNORE);
+    if (device_buffers()) {
+      /* may be a device pointer: it cannot be copied with memcpy, so it is sent in place — and NOT completed here:
+         device buffers usually go by rendezvous, and two ranks that both wait for their send before polling a receive
+         would wait for each other for ever (the reference posts Isend and polls, tx_cuda.cuh:776-974). The request is
+         reaped by later calls; flush_sends() completes it before the caller reuses the buffer. */
+      pending_.emplace_back();
+      pending_.back().inPlace = true;
+      MPI_Isend(buf, int(bytes), MPI_BYTE, dst, fold(tag), comm_, &pending_.back().req);
       return;
     }
     pending_.emplace_back();
     Pending &p = pending_.back();
     p.data.assign(static_cast<const char *>(buf), static_cast<const char *>(buf) + bytes);
     MPI_Isend(p.data.data(), int(bytes), MPI_BYTE, dst, fold(tag), comm_, &p.req);
+  }
+
+  void flush_sends() override {
+    for (;;) {
+      reap();
+      bool open = false;
+      for (const Pending &p : pending_) open = open || p.inPlace;
+      if (!open) return;
+    }
   }
 
   bool try_recv(int src, int tag, void *buf, size_t bytes) override {
@@ -114,6 +127,7 @@ private:
   struct Pending {
     std::vector<char> data;
     MPI_Request req;
+    bool inPlace = false; // the caller's own (device) buffer is on the wire
   };
   /* library tags can exceed the smallest legal MPI_TAG_UB; fold the high bits down (collisions would need two live
      messages between the same pair whose tags differ only above bit 14 and alias after folding: the kinds in

@@ -753,6 +753,10 @@ public:
       if (open && stencil::Comm::wtime() - t0 > 120.0) LOG_FATAL("exchange(): host-mediated transports made no progress for 120 s");
     }
 
+    /* every receive of mine is in: in-place (device-pointer) sends may now be completed without two ranks waiting for
+       each other, and must be before the packers are filled again */
+    if (deviceMsgs_) comm.flush_sends();
+
     /* 7. completion */
     STENCIL_RANGE("DD::exchange: wait");
     for (size_t di = 0; di < nd_; ++di) {

@@ -73,6 +73,22 @@ def test_astaroth_sim(bin_dir, tmp_path):
     assert f[1] == "peer/kernel" and f[7:11] == ["8", "fp64", "star19", "3"] and float(f[13]) > 0
 
 
+def test_astaroth_sim_cross_terms_check(bin_dir, tmp_path):
+    """--cross reads edge and corner halos; --check compares with the host loop after steps in which every halo comes from
+    the kernels' own pushes."""
+    out = _run(bin_dir, tmp_path, "astaroth-sim", "--x", "70", "--y", "44", "--z", "50", "--fields", "2", "--double", "--cross", "--iters", "6", "--check")
+    line = [l for l in out.splitlines() if l.startswith("astaroth-check,")][-1]
+    assert line.endswith(",ok"), out
+
+
+def test_jacobi3d_verify_mode(bin_dir, tmp_path):
+    """jacobi3d --verify: fused kernel vs plain kernel + exchange() from a random field, fingerprints must agree; with one
+    GPU held back before every iteration the flag protocol still has to keep the iterations apart."""
+    out = _run(bin_dir, tmp_path, "jacobi3d", "200", "70", "40", "--exact-size", "--verify", "12", "--tile-z", "8", "--delay-us", "200")
+    line = [l for l in out.splitlines() if l.startswith("jacobi3d-verify,")][-1].split(",")
+    assert line[-1] == "ok" and line[-2] == line[-3] and line[6] == "12", out
+
+
 def test_topology_benchmarks_run(bin_dir, tmp_path):
     out = _run(bin_dir, tmp_path, "bench-alltoallv", "--iters", "2", "--cap-mib", "4")
     assert out.splitlines()[0] == "stencil" and "direct-store" in out and "All-to-all 8MiB" in out
