@@ -1090,6 +1090,8 @@ static void launch_region_tma(bool cross, LocalDomain &ld, int fields, const CUt
 
 void AstarothSim::step() {
   STENCIL_RANGE("AstarothSim::step");
+  if (impl_->err && *impl_->err)
+    LOG_FATAL("AstarothSim: timed out waiting for a neighbour GPU (code " << *impl_->err << ", iteration " << impl_->iter << ")");
   std::vector<LocalDomain> &doms = dd_->domains();
   const bool star = is_star(opt_.stencil), cross = opt_.stencil == Stencil::Star19Cross;
   /* tiles == nullptr: the region has no tile table (plain kernels only) */

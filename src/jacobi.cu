@@ -1065,6 +1065,9 @@ void Jacobi3D::fill(bool random, unsigned seed) {
 
 void Jacobi3D::step() {
   STENCIL_RANGE("Jacobi3D::step");
+  /* a flag wait that timed out inside a kernel only breaks out of its loop: stop here instead of computing further
+     iterations on stale halos (the word is host-mapped memory, reading it costs nothing) */
+  if (*impl_->err) LOG_FATAL("Jacobi3D: timed out waiting for a neighbour (code " << *impl_->err << ", iteration " << impl_->iter << ")");
   std::vector<LocalDomain> &doms = dd_->domains();
   const size_t nd = doms.size();
   ++impl_->iter;

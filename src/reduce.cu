@@ -17,14 +17,14 @@ namespace {
 constexpr int kThreads = 256;
 
 __global__ void __launch_bounds__(kThreads)
-    reduce_sum_f32_kernel(const float *__restrict__ src, long long pitchX, long long pitchXY, int ex, int ey, int ez,
+    reduce_sum_f32_kernel(const float *__restrict__ src, long long pitchX, long long pitchXY, long long ex, long long ey, long long ez,
                           double *partials, unsigned long long *ticket, double *out) {
-  /* rows are distributed round-robin over CTAs; a thread strides along x */
+  /* rows are distributed round-robin over CTAs; a thread strides along x (64-bit indices: a row may be INT_MAX cells) */
   double acc = 0;
-  const long long rows = (long long)ey * ez;
+  const long long rows = ey * ez;
   for (long long r = blockIdx.x; r < rows; r += gridDim.x) {
     const float *p = src + (r / ey) * pitchXY + (r % ey) * pitchX;
-    for (int x = threadIdx.x; x < ex; x += kThreads) acc += double(p[x]);
+    for (long long x = threadIdx.x; x < ex; x += kThreads) acc += double(p[x]);
   }
   /* CTA reduction in a fixed tree order */
   __shared__ double sh[kThreads];
@@ -66,8 +66,8 @@ void reduce_sum_f32(const float *src, const Dim3 &pitch, const Dim3 &ext, void *
   unsigned long long *ticket = reinterpret_cast<unsigned long long *>(partials + kReduceMaxBlocks);
   const long long rows = std::max<long long>(1, ext.y * ext.z);
   const unsigned blocks = unsigned(std::min<long long>(rows, kReduceMaxBlocks));
-  reduce_sum_f32_kernel<<<blocks, kThreads, 0, stream>>>(src, pitch.x, pitch.x * pitch.y, int(ext.x), int(ext.y), int(ext.z), partials,
-                                                         ticket, out);
+  reduce_sum_f32_kernel<<<blocks, kThreads, 0, stream>>>(src, pitch.x, pitch.x * pitch.y, (long long)ext.x, (long long)ext.y, (long long)ext.z,
+                                                         partials, ticket, out);
   CUDA_RUNTIME(cudaGetLastError());
 }
 
@@ -142,7 +142,7 @@ extern "C" int stencil_reduce_sum_f32_noalloc(const float *src, const int64_t pi
     std::fprintf(stderr, "stencil_reduce_sum_f32_noalloc: negative extent or pitch smaller than the box\n");
     return -2;
   }
-  /* the fixed scratch serves boxes up to the kernel's 32-bit row arithmetic: reject anything beyond, loudly */
+  /* the stated maximum of this entry point (the kernel itself indexes with 64 bits): reject anything beyond, loudly */
   if (ext[0] > STENCIL_NOALLOC_MAX_ROW_CELLS || (ext[1] > 0 && ext[2] > STENCIL_NOALLOC_MAX_ROWS / ext[1])) {
     std::fprintf(stderr,
                  "stencil_reduce_sum_f32_noalloc: box %lld x %lld x %lld exceeds the supported maximum (%lld cells per row, %lld rows);"

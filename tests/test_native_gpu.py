@@ -10,7 +10,7 @@ pytestmark = pytest.mark.gpu
 
 
 @pytest.mark.parametrize("group", ["[accessor]", "[align]", "[allocator]", "[array]", "[topo]", "[rcstream]", "[pack]", "[translate]",
-                                   "[packer]", "[local_domain]", "[exchange]", "[jacobi]", "[astaroth]", "[derivative]"])
+                                   "[packer]", "[tx]", "[local_domain]", "[exchange]", "[jacobi]", "[astaroth]", "[derivative]"])
 def test_native_cuda_group(bin_dir, group, tmp_path):
     r = run_native(os.path.join(bin_dir, "test_cuda"), group, cwd=str(tmp_path))
     assert r.returncode == 0, r.stdout[-6000:]

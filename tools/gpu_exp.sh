@@ -5,24 +5,15 @@ cd /root/repo
 export STENCIL_LOG_LEVEL=1
 O=gpurun_out/exp.txt
 : > $O
-A=./build/bin/astaroth-sim
-OLD=./build/old_src/bld/bin/astaroth-sim
-run() { echo "## $*" >> $O; timeout 300 "$@" 2>/dev/null | grep -E "device|astaroth" >> $O; }
-for i in 1 2; do
-run $A --x 256 --y 256 --z 256 --fields 8 --double --star19 --iters 20
-run $OLD --x 256 --y 256 --z 256 --fields 8 --double --star19 --iters 20
-done
-M=gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,lts__t_sector_hit_rate.pct,sm__warps_active.avg.pct_of_peak_sustained_active
-J="./build/bin/jacobi3d"
-for cfg in "512 512 512" "1024 512 256" "2048 256 256"; do
-  for mode in "" "--no-overlap"; do
-    tag=$(echo "$cfg$mode" | tr ' ' '_')
-    ncu --metrics $M --clock-control none -k regex:jacobi7 -s 4 -c 3 --csv --log-file gpurun_out/ncu_$tag.csv $J $cfg --exact-size -n 8 --tile-z 16 $mode > /dev/null 2>&1
-    echo "## ncu $cfg $mode" >> $O; grep -E "jacobi7" gpurun_out/ncu_$tag.csv | awk -F'","' '{print $5, $(NF-2), $(NF)}' | tail -15 >> $O
+J=./build/bin/jacobi3d
+run() { echo "## $PADS $SKEW $*" >> $O; STENCIL_ROW_PAD_UNITS=$PADS STENCIL_BUF_SKEW_BYTES=$SKEW timeout 300 "$@" 2>/dev/null | grep -E "device" >> $O; }
+for cfg in "2048 256 256" "1024 512 256" "512 512 512"; do
+  for PADS in 0 1 2 3 4 6 8 16; do
+    SKEW=0 run $J $cfg --exact-size -n 30 --tile-z 16 --device-time --no-overlap
+  done
+  PADS=0
+  for SKEW in 4096 65536 1048576 1310720; do
+    run $J $cfg --exact-size -n 30 --tile-z 16 --device-time --no-overlap
   done
 done
-ncu --metrics $M --clock-control none -k regex:astaroth_tma -s 3 -c 2 --csv --log-file gpurun_out/ncu_ast_new.csv $A --x 256 --y 256 --z 256 --fields 8 --double --star19 --iters 6 > /dev/null 2>&1
-ncu --metrics $M --clock-control none -k regex:astaroth_tma -s 3 -c 2 --csv --log-file gpurun_out/ncu_ast_old.csv $OLD --x 256 --y 256 --z 256 --fields 8 --double --star19 --iters 6 > /dev/null 2>&1
-echo "## ncu astaroth new" >> $O; grep astaroth_tma gpurun_out/ncu_ast_new.csv | awk -F'","' '{print $(NF-2), $(NF)}' >> $O
-echo "## ncu astaroth old" >> $O; grep astaroth_tma gpurun_out/ncu_ast_old.csv | awk -F'","' '{print $(NF-2), $(NF)}' >> $O
 cat $O
