@@ -8,6 +8,7 @@
    radius-3 stencil, so the engine is templated over the element type, takes any number of fields, and adds
    Stencil::Star19: next = curr + dt * L(curr) with the 6th-order, 19-point radius-3 Laplacian every Astaroth-style
    MHD code is built from. All fields are advanced by ONE launch per region (field index is a grid dimension). */
+#include <atomic>
 #include <memory>
 #include <vector>
 
@@ -69,7 +70,7 @@ private:
   Options opt_;
   std::unique_ptr<DistributedDomain> dd_;
   std::unique_ptr<Impl> impl_;
-  unsigned long long launches_ = 0;
+  std::atomic<unsigned long long> launches_{0};
 };
 
 /* host reference: one step of one field on a dense periodic array (same arithmetic order as the kernel) */

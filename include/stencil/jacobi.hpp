@@ -15,6 +15,7 @@
                      kernel, so the transfer hides behind the computation. (N2 + N3.)
      Mode::Overlap   the reference's schedule: interior kernel, exchange(), exterior slabs, synchronise, swap.
      Mode::NoOverlap exchange(), whole-region kernel, synchronise, swap (reference --no-overlap). */
+#include <atomic>
 #include <memory>
 #include <vector>
 
@@ -35,6 +36,7 @@ public:
     bool flaggedFirst = true; // schedule the tiles that push to ANOTHER GPU first, so each face is announced early
     bool narrowTiles = true;  // cover the remainder of rows that are not a multiple of 128 cells with 32 x 64 tiles
     bool planFile = false;
+    bool launchThreads = true; // several local GPUs: enqueue each GPU's work from its own host thread (STENCIL_LAUNCH_THREADS=0 turns it off)
   };
 
   Jacobi3D(size_t x, size_t y, size_t z, const Options &opt);
@@ -88,7 +90,7 @@ private:
   std::unique_ptr<DistributedDomain> dd_;
   DataHandle<float> h_;
   std::unique_ptr<Impl> impl_;
-  unsigned long long launches_ = 0;
+  std::atomic<unsigned long long> launches_{0};
 };
 
 /* test hook: how many of `values` does the kernel's 3-instruction x/6 round differently from IEEE division (expect 0) */

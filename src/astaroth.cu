@@ -18,6 +18,7 @@
 #include <set>
 
 #include "stencil/copy_plan.hpp"
+#include "stencil/detail/launch_pool.hpp"
 #include "stencil/detail/tma.cuh"
 
 namespace stencil {
@@ -711,8 +712,12 @@ struct AstarothSim::Impl {
   std::vector<Push> push;
   unsigned iter = 0;       // iterations launched (the epoch published in the flags)
   unsigned *err = nullptr; // host-mapped error word for flag time-outs
-  std::vector<cudaEvent_t> computeDone;
-  std::vector<bool> computeRecorded;
+  /* computeDone: end of each subdomain's kernel of the step being enqueued, computePrev: of the previous step (what
+     same-GPU neighbours and the next exchange wait for); swapped every step so enqueueing threads never share one */
+  std::vector<cudaEvent_t> computeDone, computePrev;
+  std::vector<bool> computeRecorded; // computePrev[di] has been recorded
+  detail::LaunchPool pool; // one enqueueing thread per local subdomain (1 process x N GPUs)
+  bool launchThreads = true;
 };
 
 namespace {
@@ -841,11 +846,14 @@ AstarothSim::AstarothSim(size_t x, size_t y, size_t z, const Options &opt) : opt
   if (std::getenv("STENCIL_ASTAROTH_NO_TMA")) opt_.useTma = false;
   if (std::getenv("STENCIL_ASTAROTH_NO_NARROW")) opt_.narrowTiles = false;
   if (std::getenv("STENCIL_ASTAROTH_NATURAL_ORDER")) opt_.flaggedFirst = false;
+  if (const char *e = std::getenv("STENCIL_LAUNCH_THREADS")) impl_->launchThreads = std::atoi(e) != 0;
   for (LocalDomain &ld : dd_->domains()) {
     DevGuard g(ld.gpu());
     cudaEvent_t e;
     CUDA_RUNTIME(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     impl_->computeDone.push_back(e);
+    CUDA_RUNTIME(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    impl_->computePrev.push_back(e);
     impl_->computeRecorded.push_back(false);
   }
   const bool star = is_star(opt_.stencil);
@@ -981,6 +989,8 @@ AstarothSim::~AstarothSim() {
   }
   if (impl_)
     for (cudaEvent_t e : impl_->computeDone) cudaEventDestroy(e);
+  if (impl_)
+    for (cudaEvent_t e : impl_->computePrev) cudaEventDestroy(e);
   if (impl_ && dd_)
     for (int parity = 0; parity < 2; ++parity)
       for (size_t di = 0; di < impl_->maps[parity].size(); ++di) {
@@ -1133,24 +1143,26 @@ void AstarothSim::step() {
        flags, kernels of subdomains that share a GPU are ordered by events. */
     if (!steady) {
       for (size_t di = 0; di < doms.size(); ++di)
-        if (impl_->computeRecorded[di]) dd_->exchange_after(di, impl_->computeDone[di]);
+        if (impl_->computeRecorded[di]) dd_->exchange_after(di, impl_->computePrev[di]);
       dd_->exchange_async();
     }
-    for (size_t di = 0; di < doms.size(); ++di) {
+    const std::function<void(size_t)> enqueue = [&](size_t di) {
       DevGuard g(doms[di].gpu());
       if (!steady) {
         CUDA_RUNTIME(cudaStreamWaitEvent(impl_->streams[di], dd_->exchange_done_event(di), 0));
       } else {
         for (int dep : impl_->push[di].sameDevDeps)
-          if (impl_->computeRecorded[size_t(dep)]) CUDA_RUNTIME(cudaStreamWaitEvent(impl_->streams[di], impl_->computeDone[size_t(dep)], 0));
+          if (impl_->computeRecorded[size_t(dep)]) CUDA_RUNTIME(cudaStreamWaitEvent(impl_->streams[di], impl_->computePrev[size_t(dep)], 0));
       }
-    }
-    for (size_t di = 0; di < doms.size(); ++di) {
-      DevGuard g(doms[di].gpu());
       launch(di, doms[di].get_compute_region(), tiles_all(di), true);
       CUDA_RUNTIME(cudaEventRecord(impl_->computeDone[di], impl_->streams[di]));
-      impl_->computeRecorded[di] = true;
-    }
+    };
+    if (doms.size() > 1 && impl_->launchThreads)
+      impl_->pool.run(doms.size(), enqueue);
+    else
+      for (size_t di = 0; di < doms.size(); ++di) enqueue(di);
+    impl_->computeDone.swap(impl_->computePrev);
+    for (size_t di = 0; di < doms.size(); ++di) impl_->computeRecorded[di] = true;
     dd_->swap();
     return;
   }

@@ -40,6 +40,7 @@
 #include <cuda.h>
 
 #include "stencil/copy_plan.hpp"
+#include "stencil/detail/launch_pool.hpp"
 #include "stencil/reduce.hpp"
 
 namespace stencil {
@@ -685,7 +686,10 @@ struct DevGuard {
 struct Jacobi3D::Impl {
   struct Dom {
     RcStream stream;
-    cudaEvent_t done = nullptr, t0 = nullptr, t1 = nullptr;
+    /* done: end of this subdomain's kernel of the step being enqueued; donePrev: of the previous step (what same-GPU
+       neighbours wait for). Two events, swapped every step, so that enqueueing threads never race on one. */
+    cudaEvent_t done = nullptr, donePrev = nullptr, t0 = nullptr, t1 = nullptr;
+    bool hasDependents = false; // some other local subdomain waits for my `done`
     Tile *tilesAll = nullptr; // whole compute region, tiles that push to another GPU first
     unsigned nAll = 0, nFace[6] = {0, 0, 0, 0, 0, 0};
     Tile *tilesInterior = nullptr;
@@ -712,6 +716,7 @@ struct Jacobi3D::Impl {
     WaitSet finalWait;
   };
   std::vector<Dom> doms;
+  detail::LaunchPool pool; // one enqueueing thread per local subdomain (1 process x N GPUs)
   unsigned iter = 0;
   unsigned *err = nullptr;
   bool fusedOk = true;
@@ -819,6 +824,7 @@ Jacobi3D::~Jacobi3D() {
       DevGuard g(dd_->domains()[di].gpu());
       cudaStreamSynchronize(d.stream);
       cudaEventDestroy(d.done);
+      cudaEventDestroy(d.donePrev);
       cudaEventDestroy(d.t0);
       cudaEventDestroy(d.t1);
       cudaFree(d.tilesAll);
@@ -843,6 +849,7 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
   if (opt_.useTma && opt_.tileZ > kMaxTileZ) opt_.tileZ = kMaxTileZ;
   if (std::getenv("STENCIL_JACOBI_NATURAL_ORDER")) opt_.flaggedFirst = false;
   if (std::getenv("STENCIL_JACOBI_NO_NARROW")) opt_.narrowTiles = false;
+  if (const char *e = std::getenv("STENCIL_LAUNCH_THREADS")) opt_.launchThreads = std::atoi(e) != 0;
   dd_.reset(comm ? new DistributedDomain(x, y, z, *comm) : new DistributedDomain(x, y, z));
   if (!opt_.gpus.empty()) dd_->set_gpus(opt_.gpus);
   Radius radius = Radius::constant(0);
@@ -902,6 +909,7 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
           CUDA_RUNTIME(cudaFuncSetAttribute(*k, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
     }
     CUDA_RUNTIME(cudaEventCreateWithFlags(&d.done, cudaEventDisableTiming));
+    CUDA_RUNTIME(cudaEventCreateWithFlags(&d.donePrev, cudaEventDisableTiming));
     CUDA_RUNTIME(cudaEventCreate(&d.t0));
     CUDA_RUNTIME(cudaEventCreate(&d.t1));
     CUDA_RUNTIME(cudaMalloc(&d.doneCounter, 8 * sizeof(unsigned)));
@@ -1030,6 +1038,8 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
       }
     }
   }
+  for (Impl::Dom &d : impl_->doms)
+    for (int dep : d.sameDevDeps) impl_->doms[size_t(dep)].hasDependents = true;
   init();
 }
 
@@ -1106,16 +1116,21 @@ void Jacobi3D::step() {
   if (opt_.mode == Mode::Fused) {
     /* same-GPU neighbours (oversubscription) are ordered by events: flags must never be spun on by a kernel that
        shares the device with the kernel that raises them */
-    for (size_t di = 0; di < nd; ++di) {
-      DevGuard g(doms[di].gpu());
-      for (int dep : impl_->doms[di].sameDevDeps) CUDA_RUNTIME(cudaStreamWaitEvent(impl_->doms[di].stream, impl_->doms[size_t(dep)].done, 0));
-    }
-    for (size_t di = 0; di < nd; ++di) {
+    /* each subdomain waits for the PREVIOUS iteration of its same-GPU neighbours (their `done` events were recorded
+       in the previous step), launches, and records its own `done`: independent per subdomain, so with several local
+       GPUs every subdomain is enqueued from its own host thread */
+    const std::function<void(size_t)> enqueue = [&](size_t di) {
       DevGuard g(doms[di].gpu());
       Impl::Dom &d = impl_->doms[di];
+      for (int dep : d.sameDevDeps) CUDA_RUNTIME(cudaStreamWaitEvent(d.stream, impl_->doms[size_t(dep)].donePrev, 0));
       launch(di, d.tilesAll, d.nAll, doms[di].get_compute_region(), true);
-      if (!d.sameDevDeps.empty() || nd > 1) CUDA_RUNTIME(cudaEventRecord(d.done, d.stream));
-    }
+      if (d.hasDependents) CUDA_RUNTIME(cudaEventRecord(d.done, d.stream));
+    };
+    if (nd > 1 && opt_.launchThreads)
+      impl_->pool.run(nd, enqueue);
+    else
+      for (size_t di = 0; di < nd; ++di) enqueue(di);
+    for (Impl::Dom &d : impl_->doms) std::swap(d.done, d.donePrev);
     dd_->swap();
     return;
   }

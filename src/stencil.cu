@@ -13,6 +13,7 @@
 #include <tuple>
 
 #include "stencil/copy_plan.hpp"
+#include "stencil/detail/launch_pool.hpp"
 #include "stencil/nvtx.hpp"
 #include "stencil/packer.cuh"
 
@@ -91,6 +92,15 @@ class Exchanger {
   int trace_ = 0;
   std::vector<cudaEvent_t> trA_, trB_, trC_;
   unsigned epoch_ = 0;
+  /* several local GPUs: the per-subdomain parts of enqueue() run on one host thread per subdomain */
+  stencil::detail::LaunchPool pool_;
+  bool threads_ = true;
+  void for_each_dom(const std::function<void(size_t)> &fn) {
+    if (threads_ && nd_ > 1)
+      pool_.run(nd_, fn);
+    else
+      for (size_t di = 0; di < nd_; ++di) fn(di);
+  }
   unsigned *errWord_ = nullptr; // pinned + mapped
   unsigned long long timeoutNs_;
 
@@ -263,7 +273,9 @@ class Exchanger {
   }
 
 public:
-  explicit Exchanger(DistributedDomain &dd) : dd_(dd), nd_(dd.domains_.size()), timeoutNs_(flag_timeout_ns()) {}
+  explicit Exchanger(DistributedDomain &dd) : dd_(dd), nd_(dd.domains_.size()), timeoutNs_(flag_timeout_ns()) {
+    if (const char *e = std::getenv("STENCIL_LAUNCH_THREADS")) threads_ = std::atoi(e) != 0;
+  }
 
   ~Exchanger() {
     for (auto &kv : remote_) {
@@ -616,18 +628,13 @@ public:
 
     /* work the caller declared with exchange_after(): producers of the data to send, and consumers of the halos about to
        be overwritten. Any local subdomain may receive from any other, so every exchange stream waits for all of them. */
-    for (size_t di = 0; di < nd_; ++di) {
+    for_each_dom([&](size_t di) {
       DevGuard g(doms[di].gpu());
       for (size_t dj = 0; dj < nd_; ++dj)
         if (after_[dj]) CUDA_RUNTIME(cudaStreamWaitEvent(streams_[di], after_[dj], 0));
-    }
-
-    /* 0. tell cross-process senders that my halos are free for this epoch (only other processes can be ahead of me) */
-    for (size_t di = 0; di < nd_; ++di) {
-      if (readySig_[di].n == 0) continue;
-      DevGuard g(doms[di].gpu());
-      launch_signal_flags(readySig_[di], epoch_, streams_[di]);
-    }
+      /* 0. tell cross-process senders that my halos are free for this epoch (only other processes can be ahead of me) */
+      if (readySig_[di].n) launch_signal_flags(readySig_[di], epoch_, streams_[di]);
+    });
 
     /* 1. longest paths first: staged sends (pack + D2H) */
     {
@@ -673,8 +680,8 @@ public:
     }
 
     /* 4. direct pushes: wait for cross-process credits, store into the neighbours' halos, raise their flags */
-    for (size_t di = 0; di < nd_; ++di) {
-      if (push_[di].empty() && arriveSig_[di].n == 0) continue;
+    for_each_dom([&](size_t di) {
+      if (push_[di].empty() && arriveSig_[di].n == 0) return;
       STENCIL_RANGE("DD::exchange: direct push");
       DevGuard g(doms[di].gpu());
       launch_wait_flags(readyWait_[di], epoch_, errWord_, timeoutNs_, streams_[di]);
@@ -682,7 +689,7 @@ public:
       push_[di].launch_and_signal(doms[di].parity(), arriveSig_[di], epoch_, streams_[di], !skipXLocal_);
       if (trace_) CUDA_RUNTIME(cudaEventRecord(trB_[di], streams_[di]));
       CUDA_RUNTIME(cudaEventRecord(pushDone_[di], streams_[di]));
-    }
+    });
 
     /* 5. phase B: everything that waits on another stream is enqueued only now, so no stream can wait on work
           that has not been submitted */
@@ -691,13 +698,13 @@ public:
       CUDA_RUNTIME(cudaStreamWaitEvent(streams_[size_t(pc.dst)], pc.copied, 0));
       pc.unpacker->unpack();
     }
-    for (size_t di = 0; di < nd_; ++di) {
+    for_each_dom([&](size_t di) {
       DevGuard g(doms[di].gpu());
       for (int dep : sameDevDeps_[di]) CUDA_RUNTIME(cudaStreamWaitEvent(streams_[di], pushDone_[size_t(dep)], 0));
       launch_wait_flags(arriveWait_[di], epoch_, errWord_, timeoutNs_, streams_[di]);
       scatter_[di].launch(doms[di].parity(), streams_[di]);
       if (trace_) CUDA_RUNTIME(cudaEventRecord(trC_[di], streams_[di]));
-    }
+    });
 
     if (device_only())
       for (size_t di = 0; di < nd_; ++di) {

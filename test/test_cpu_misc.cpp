@@ -190,3 +190,35 @@ TEST_CASE("boundary flags", "[boundary]") {
   REQUIRE(!(b == Boundary::periodic()));
   REQUIRE(!Boundary::none().dir(1, 1, 1));
 }
+
+#include <atomic>
+#include <chrono>
+#include <thread>
+#include "stencil/detail/launch_pool.hpp"
+
+TEST_CASE("launch pool runs every index exactly once per call, spinning or asleep", "[misc][pool]") {
+  stencil::detail::LaunchPool pool;
+  std::vector<std::atomic<int>> hits(6);
+  for (auto &h : hits) h = 0;
+  std::atomic<int> concurrent{0}, peak{0};
+  const std::function<void(size_t)> fn = [&](size_t i) {
+    const int now = ++concurrent;
+    int p = peak.load();
+    while (now > p && !peak.compare_exchange_weak(p, now)) {
+    }
+    ++hits[i];
+    std::this_thread::sleep_for(std::chrono::microseconds(200));
+    --concurrent;
+  };
+  for (int round = 0; round < 50; ++round) pool.run(6, fn); // back to back: workers are still spinning
+  std::this_thread::sleep_for(std::chrono::milliseconds(20)); // long enough for the workers to fall asleep
+  for (int round = 0; round < 5; ++round) {
+    pool.run(6, fn);
+    std::this_thread::sleep_for(std::chrono::milliseconds(5));
+  }
+  pool.run(3, fn); // fewer indices than workers
+  pool.run(1, fn);
+  for (size_t i = 0; i < 6; ++i) REQUIRE(hits[i] == 55 + (i < 3 ? 1 : 0) + (i < 1 ? 1 : 0));
+  REQUIRE(peak.load() > 1); // they did overlap
+}
+
