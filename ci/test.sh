@@ -5,9 +5,13 @@ cd "$(dirname "$0")/.."
 ./build/bin/test_cpu
 python -m pytest tests -q -m "not gpu"
 if ./build/bin/test_cuda "[align]" >/dev/null 2>&1; then
-  # memcheck is optional: some pools close compute-sanitizer (STENCIL_CI_MEMCHECK=1 turns it on)
-  if [ "${STENCIL_CI_MEMCHECK:-0}" = 1 ]; then compute-sanitizer --tool memcheck ./build/bin/test_cuda "[pack]"; fi
   python -m pytest tests -q -m gpu
+  # sanitizer gate (the reference's CTest command is `cuda-memcheck test_cuda`): memcheck + racecheck over the tests of
+  # the hand-written synchronisation; STENCIL_CI_SANITIZE=0 skips it on pools where compute-sanitizer is closed
+  if [ "${STENCIL_CI_SANITIZE:-1}" = 1 ]; then
+    tools/gpu_sanitize.sh
+    if grep -q "rc=[1-9]" gpurun_out/sanitizer/summary.txt; then echo "sanitizer gate failed"; exit 1; fi
+  fi
 else
   echo "no CUDA device: GPU tier skipped"
 fi

@@ -680,10 +680,12 @@ struct AstarothSim::Impl {
   struct Tiles {
     ATile *dev = nullptr;
     unsigned n = 0;
+    bool hasNarrow = false; // decides how much shared memory a launch asks for
   };
   static Tiles upload(const std::vector<ATile> &t) {
     Tiles r;
     r.n = unsigned(t.size());
+    for (const ATile &a : t) r.hasNarrow = r.hasNarrow || a.narrow;
     if (t.empty()) return r;
     CUDA_RUNTIME(cudaMalloc(&r.dev, t.size() * sizeof(ATile)));
     CUDA_RUNTIME(cudaMemcpy(r.dev, t.data(), t.size() * sizeof(ATile), cudaMemcpyHostToDevice));
@@ -1064,7 +1066,8 @@ static void launch_region(AstarothSim::Stencil st, LocalDomain &ld, int fields, 
 
 /* the TMA kernel on a region, through its tile table */
 template <typename T>
-static void launch_region_tma(bool cross, LocalDomain &ld, int fields, const CUtensorMap *maps, const ATile *tiles, unsigned nTiles, const Rect3 &reg,
+static void launch_region_tma(bool cross, LocalDomain &ld, int fields, const CUtensorMap *maps, const ATile *tiles, unsigned nTiles, bool hasNarrow,
+                              const Rect3 &reg,
                               int tileZ, T dt, T eta, cudaStream_t stream, bool wrapX = false, const void *push = nullptr, unsigned flagMask = 0,
                               unsigned epoch = 0) {
   if (!nTiles) return;
@@ -1091,10 +1094,12 @@ static void launch_region_tma(bool cross, LocalDomain &ld, int fields, const CUt
   P.push = static_cast<const PushParams<T> *>(push);
   P.pushFlagMask = flagMask;
   P.epoch = epoch;
+  /* a table without narrow tiles needs only the wide tile's ring */
+  const int smem = hasNarrow ? tma_smem_bytes<T>() : TmaGeom<T, 32>::smemBytes;
   if (cross)
-    astaroth_tma_kernel<T, true><<<nTiles, kTThreads, tma_smem_bytes<T>(), stream>>>(P);
+    astaroth_tma_kernel<T, true><<<nTiles, kTThreads, smem, stream>>>(P);
   else
-    astaroth_tma_kernel<T, false><<<nTiles, kTThreads, tma_smem_bytes<T>(), stream>>>(P);
+    astaroth_tma_kernel<T, false><<<nTiles, kTThreads, smem, stream>>>(P);
   CUDA_RUNTIME(cudaGetLastError());
 }
 
@@ -1116,10 +1121,10 @@ void AstarothSim::step() {
       const void *pushDev = fused ? impl_->push[di].dev[doms[di].parity()] : nullptr;
       const unsigned pushFlags = fused ? impl_->push[di].flagMask : 0u;
       if (opt_.fp64)
-        launch_region_tma<double>(cross, doms[di], opt_.fields, maps, tiles->dev, tiles->n, reg, opt_.tileZ, opt_.dt, opt_.crossWeight, impl_->streams[di],
+        launch_region_tma<double>(cross, doms[di], opt_.fields, maps, tiles->dev, tiles->n, tiles->hasNarrow, reg, opt_.tileZ, opt_.dt, opt_.crossWeight, impl_->streams[di],
                                   whole && impl_->fusedX, pushDev, pushFlags, impl_->iter);
       else
-        launch_region_tma<float>(cross, doms[di], opt_.fields, maps, tiles->dev, tiles->n, reg, opt_.tileZ, float(opt_.dt), float(opt_.crossWeight),
+        launch_region_tma<float>(cross, doms[di], opt_.fields, maps, tiles->dev, tiles->n, tiles->hasNarrow, reg, opt_.tileZ, float(opt_.dt), float(opt_.crossWeight),
                                  impl_->streams[di], whole && impl_->fusedX, pushDev, pushFlags, impl_->iter);
       ++launches_;
       return;

@@ -100,7 +100,8 @@ struct JacobiParams {
   int lox, loy, loz, hix, hiy, hiz; // cells to update (compute coordinates, half open)
   int tileZ;
   int wrapLoad;       // fused mode, subdomain is its own +-x neighbour: x neighbours across the wrap come from side TMA boxes
-  unsigned debugSkip; // diagnostics only (STENCIL_JACOBI_DEBUG_SKIP): 1 no signal, 2 no x push, 4 no y/z push
+  unsigned debugSkip; // diagnostics only (STENCIL_JACOBI_DEBUG_SKIP): 1 no signal, 2 no x push, 4 no y/z push,
+                      // 8 wide tiles fetch 16 rows per plane instead of 18 (WRONG results: timing bound for halo-row sharing)
   int tmaX0; // index of compute cell x=0 inside a padded row (TMA coordinates count from the row start)
   /* Dirichlet spheres in global coordinates */
   long long ox, oy, oz;   // global coordinate of compute cell (0,0,0)
@@ -468,7 +469,8 @@ __device__ __forceinline__ void tma_tile(unsigned char *smem, const CUtensorMap 
   auto issue = [&](int j) {          // load input plane j (compute plane z0 - 1 + j, raw plane z0 + j)
     const int sj = j % kTmaStages;
     if (j >= kTmaStages) mbar_wait(&empty[sj], ((j / kTmaStages) - 1) & 1);
-    mbar_arrive_expect_tx(&full[sj], G::kPlaneBytes + (sideL ? G::kSideBytes : 0) + (sideR ? G::kSideBytes : 0));
+    const int planeBytes = (LW == 32 && (P.debugSkip & 8u)) ? G::kBoxX * (G::kBoxY - 2) * 4 : G::kPlaneBytes;
+    mbar_arrive_expect_tx(&full[sj], planeBytes + (sideL ? G::kSideBytes : 0) + (sideR ? G::kSideBytes : 0));
     tma_load_3d(smem + sj * G::kStageBytes, tmap, cx, cy, z0 + j, &full[sj]);
     /* side boxes: the tile's rows (raw row cy + 1); left tiles want the aligned group of four cells that holds cell
        sx-1 (a TMA box must start on a 16-byte boundary: an unaligned start is an illegal instruction), right tiles
@@ -484,6 +486,21 @@ __device__ __forceinline__ void tma_tile(unsigned char *smem, const CUtensorMap 
     const int x0 = t.x0 + xl * kVec;
     const int y0 = t.y0 + r0;
     const bool nearSphere = tile_near_sphere(P, t, G::kW, G::kR, z0, z1);
+    /* Inside a tile near a sphere only the vectors that really touch it take the (slow, exact) override path. A cell is
+       inside when dx^2 + dy^2 + dz^2 < r2; per lane and row, r2 - dy^2 and the smallest dx^2 over the lane's four cells
+       and both centres are constants, so each plane costs one multiply and two compares per lane. (The spheres grow with
+       the domain: at 2048 cells they cover half of a 2048 x 256 x 256 box, where calling the override for every vector of
+       every near tile made the kernel 55 % slower.) */
+    long long sphA[2] = {0, 0}, sphMinDx2 = 0;
+    if (nearSphere) {
+      auto gap = [](long long a0, long long a1, long long c) { return c < a0 ? a0 - c : (c > a1 ? c - a1 : 0); };
+      const long long gx0 = P.ox + x0, dh = gap(gx0, gx0 + kVec - 1, P.hcx), dc = gap(gx0, gx0 + kVec - 1, P.ccx);
+      sphMinDx2 = min(dh * dh, dc * dc);
+      for (int r = 0; r < 2; ++r) {
+        const long long dy = P.oy + y0 + r - P.cy;
+        sphA[r] = P.r2 - dy * dy;
+      }
+    }
     /* x wrap by load: which lane's vector holds cell x = sx (patchK = its index there), or is it the last lane's east read? */
     const int patchK = (sideR && x0 <= P.sx && P.sx < x0 + kVec) ? P.sx - x0 : -1;
     const bool eSide = sideR && x0 + kVec == P.sx;
@@ -557,8 +574,9 @@ __device__ __forceinline__ void tma_tile(unsigned char *smem, const CUtensorMap 
         o[1].z = div6((part[1].z + c1.z) + below[1].z);
         o[1].w = div6((part[1].w + c1.w) + below[1].w);
         if (nearSphere) {
-          o[0] = apply_spheres(P, x0, y0, z, o[0]);
-          o[1] = apply_spheres(P, x0, y0 + 1, z, o[1]);
+          const long long dz = P.oz + z - P.cz, dz2 = dz * dz;
+          if (sphMinDx2 < sphA[0] - dz2) o[0] = apply_spheres(P, x0, y0, z, o[0]);
+          if (sphMinDx2 < sphA[1] - dz2) o[1] = apply_spheres(P, x0, y0 + 1, z, o[1]);
         }
 #pragma unroll
         for (int r = 0; r < 2; ++r) {
@@ -694,6 +712,7 @@ struct Jacobi3D::Impl {
     unsigned nAll = 0, nFace[6] = {0, 0, 0, 0, 0, 0};
     Tile *tilesInterior = nullptr;
     unsigned nInterior = 0;
+    bool anyNarrow = false; // some tile table of this subdomain holds narrow tiles: launches ask for the larger ring
     std::vector<std::pair<Tile *, unsigned>> tilesExterior;
     std::vector<Rect3> exterior;
     Rect3 interior;
@@ -952,13 +971,19 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
     const std::vector<Tile> all = make_tiles(Dim3(0, 0, 0), sz, sz, rows, opt_.tileZ, faceMask, d.nFace, narrow, opt_.flaggedFirst, flagMask);
     d.tilesAll = upload(all);
     d.nAll = unsigned(all.size());
+    auto note_narrow = [&d](const std::vector<Tile> &v) {
+      for (const Tile &t : v) d.anyNarrow = d.anyNarrow || t.narrow;
+    };
+    note_narrow(all);
     d.interior = interiors[di];
     d.exterior = exteriors[di];
     const std::vector<Tile> in = make_tiles(d.interior.lo - org, d.interior.hi - org, sz, rows, opt_.tileZ, 0, nullptr, narrow);
+    note_narrow(in);
     d.tilesInterior = upload(in);
     d.nInterior = unsigned(in.size());
     for (const Rect3 &r : d.exterior) {
       const std::vector<Tile> ex = make_tiles(r.lo - org, r.hi - org, sz, rows, opt_.tileZ, 0, nullptr, narrow);
+      note_narrow(ex);
       d.tilesExterior.emplace_back(upload(ex), unsigned(ex.size()));
     }
 
@@ -985,7 +1010,7 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
         P.tmaX0 = int(ld.lead_elems(h_.id())) + 1;
         if (impl_->useTma) {
           char *b = const_cast<char *>(bufStart);
-          d.tmap[parity] = make_plane_map(b, pitch, ld.raw_size(), Wide::kBoxX, Wide::kBoxY);
+          d.tmap[parity] = make_plane_map(b, pitch, ld.raw_size(), Wide::kBoxX, (P.debugSkip & 8u) ? Wide::kBoxY - 2 : Wide::kBoxY);
           d.tmapNarrow[parity] = make_plane_map(b, pitch, ld.raw_size(), Narrow::kBoxX, Narrow::kBoxY);
           d.tmapSide[parity] = make_plane_map(b, pitch, ld.raw_size(), kSideBoxX, Wide::kR);
           d.tmapSideNarrow[parity] = make_plane_map(b, pitch, ld.raw_size(), kSideBoxX, Narrow::kR);
@@ -1103,7 +1128,7 @@ void Jacobi3D::step() {
       auto *k = fused ? (mb == 3 ? &jacobi7_tma_kernel<true, 3> : &jacobi7_tma_kernel<true, 2>)
                       : (mb == 3 ? &jacobi7_tma_kernel<false, 3> : &jacobi7_tma_kernel<false, 2>);
       const int pa = ld.parity();
-      (*k)<<<n, kTmaThreads, kTmaSmemBytes, d.stream>>>(d.tmap[pa], d.tmapNarrow[pa], d.tmapSide[pa], d.tmapSideNarrow[pa], P);
+      (*k)<<<n, kTmaThreads, d.anyNarrow ? kTmaSmemBytes : Wide::kSmemBytes, d.stream>>>(d.tmap[pa], d.tmapNarrow[pa], d.tmapSide[pa], d.tmapSideNarrow[pa], P);
     } else if (fused) {
       jacobi7_kernel<true><<<n, kThreads, 0, d.stream>>>(P);
     } else {

@@ -97,8 +97,6 @@ void LocalDomain::compute_layout() {
       const int64_t interiorStart = int64_t(round_up_multiple(size_t(rmx), size_t(per)));
       l.lead = interiorStart - rmx;
       l.pitchX = int64_t(round_up_multiple(size_t(interiorStart + sz_.x + int64_t(radius_.x(1))), size_t(per)));
-      /* experiments: extra alignment units of row padding (every rank must see the same value) */
-      if (const char *e = std::getenv("STENCIL_ROW_PAD_UNITS")) l.pitchX += per * std::atoll(e);
     } else { // odd element size: dense rows
       l.lead = 0;
       l.pitchX = raw.x;
@@ -108,8 +106,6 @@ void LocalDomain::compute_layout() {
     l.bufBytes = size_t(l.pitchX) * size_t(raw.y) * size_t(raw.z) * es + 32;
     for (int b = 0; b < 2; ++b) {
       off = round_up_multiple(off, slabAlign);
-      if (b == 1)
-        if (const char *e = std::getenv("STENCIL_BUF_SKEW_BYTES")) off += round_up_multiple(size_t(std::atoll(e)), slabAlign);
       l.off[b] = off;
       off += l.bufBytes;
     }
