@@ -189,6 +189,8 @@ public:
     v.rowElems = raw_size().x;
     v.padLoBytes = l.lead * es < 28 ? l.lead * es : 28;
     v.padHiBytes = (l.pitchX - raw_size().x) * es < 28 ? (l.pitchX - raw_size().x) * es : 28;
+    /* aligned layouts only (compute_layout's first branch): buffer starts and row pitches are multiples of 128 bytes */
+    v.windowSafe = (v.pitchY % 16) == 0 && (v.pitchZ % 16) == 0 && ((l.off[0] | l.off[1]) % 16) == 0;
     return v;
   }
 

@@ -66,17 +66,46 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 
 constexpr int kThreads = 256;
 
+/* A thin row of nw <= 4 words that starts `so` words into an aligned 16-byte window which may be read whole
+   (CopySeg::srcWin): the payload arrives with one or two 16-byte requests instead of one per word. */
+__device__ __forceinline__ void load_row_window(const char *__restrict__ a, unsigned so, unsigned nw, unsigned (&p)[4]) {
+  const uint4 *q = reinterpret_cast<const uint4 *>(a - 4 * (long long)so);
+  const uint4 q0 = ld_stream(q);
+  uint4 q1 = make_uint4(0u, 0u, 0u, 0u);
+  if (so + nw > 4) q1 = ld_stream(q + 1);
+  switch (so) { // uniform per segment
+  case 0: p[0] = q0.x, p[1] = q0.y, p[2] = q0.z, p[3] = q0.w; break;
+  case 1: p[0] = q0.y, p[1] = q0.z, p[2] = q0.w, p[3] = q1.x; break;
+  case 2: p[0] = q0.z, p[1] = q0.w, p[2] = q1.x, p[3] = q1.y; break;
+  default: p[0] = q0.w, p[1] = q1.x, p[2] = q1.y, p[3] = q1.z; break;
+  }
+}
+
+/* 32 bytes in one request (sm_100: 256-bit global stores) */
+__device__ __forceinline__ void st_sector(void *p, unsigned a, unsigned b, unsigned c, unsigned d, unsigned e, unsigned f, unsigned g, unsigned h) {
+  asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d), "r"(e), "r"(f), "r"(g), "r"(h) : "memory");
+}
+
 /* one thin row in sector mode: gather the payload words into their place inside 1-2 whole sectors, zero elsewhere */
 __device__ __forceinline__ void copy_row_sectors(const CopySeg &s, const char *__restrict__ a, char *__restrict__ b) {
   const unsigned lo = s.padLoWords, nw = s.rowBytes / 4, total = s.totalWords;
   const unsigned *src = reinterpret_cast<const unsigned *>(a);
   unsigned w[16];
+  if (s.srcWin) {
+    unsigned p[4];
+    load_row_window(a, s.srcWin - 1, nw, p);
 #pragma unroll
-  for (unsigned j = 0; j < 16; ++j) w[j] = (j >= lo && j < lo + nw) ? ld_stream(src + (j - lo)) : 0u;
-  uint4 *dst = reinterpret_cast<uint4 *>(b - 4 * (long long)lo);
+    for (unsigned j = 0; j < 16; ++j) {
+      const unsigned d = j - lo; // wraps to a huge value below lo
+      w[j] = d < nw ? (d == 0 ? p[0] : (d == 1 ? p[1] : (d == 2 ? p[2] : p[3]))) : 0u;
+    }
+  } else {
 #pragma unroll
-  for (unsigned q = 0; q < 4; ++q)
-    if (4 * q < total) dst[q] = make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
+    for (unsigned j = 0; j < 16; ++j) w[j] = (j >= lo && j < lo + nw) ? ld_stream(src + (j - lo)) : 0u;
+  }
+  char *dst = b - 4 * (long long)lo; // 32-byte aligned by construction of sector mode
+  st_sector(dst, w[0], w[1], w[2], w[3], w[4], w[5], w[6], w[7]);
+  if (total > 8) st_sector(dst + 32, w[8], w[9], w[10], w[11], w[12], w[13], w[14], w[15]);
 }
 
 /* Copy `nrows` consecutive rows of one plane with BYTES-wide accesses. sp/dp point at the first row. No integer
@@ -178,9 +207,17 @@ __device__ __forceinline__ void gather_dense(const CopySeg &s, RowSrc rowSrc, ch
     const unsigned n = min(rowsPerPass, rows - r0);
     for (unsigned r = threadIdx.x; r < n; r += kThreads) {
       const unsigned *a = reinterpret_cast<const unsigned *>(rowSrc(r0 + r));
+      if (s.srcWin) {
+        unsigned p[4];
+        load_row_window(reinterpret_cast<const char *>(a), s.srcWin - 1, nw, p);
 #pragma unroll
-      for (unsigned w = 0; w < 16; ++w)
-        if (w < nw) stage[r * nw + w] = ld_stream(a + w);
+        for (unsigned w = 0; w < 4; ++w)
+          if (w < nw) stage[r * nw + w] = p[w];
+      } else {
+#pragma unroll
+        for (unsigned w = 0; w < 16; ++w)
+          if (w < nw) stage[r * nw + w] = ld_stream(a + w);
+      }
     }
     __syncthreads();
     const unsigned words = n * nw;
@@ -387,9 +424,15 @@ CopySeg make_seg(const BoxView &src, const Dim3 &srcPos, const BoxView &dst, con
       s.totalWords = (unsigned short)((lo + s.rowBytes + hi) / 4);
     }
   }
-  /* thin rows into a dense destination: gather through shared memory */
+  /* thin rows (<= 16 bytes) out of a padded array whose aligned windows may be read: same word offset in every row */
+  s.srcWin = 0;
+  if (src.windowSafe && (es % 4) == 0 && s.rowBytes <= 16 && ((src.pitchY | src.pitchZ) & 15) == 0 && (((uintptr_t)s.src[0] | (uintptr_t)s.src[1]) & 3) == 0 &&
+      (((uintptr_t)s.src[0] ^ (uintptr_t)s.src[1]) & 15) == 0)
+    s.srcWin = 1u + unsigned(((uintptr_t)s.src[0] >> 2) & 3u);
+  /* thin rows into a dense destination: gather through shared memory — always when the rows can be fetched by window
+     (the stores then leave as coalesced 16-byte runs instead of one 4-byte store per word), else only across NVLink */
   s.gatherDense = 0;
-  if (dst.acrossLink && s.totalWords == 0 && (es % 4) == 0 && s.rowBytes <= 64 && dst.pitchY == (long long)s.rowBytes &&
+  if ((dst.acrossLink || s.srcWin) && s.totalWords == 0 && (es % 4) == 0 && s.rowBytes <= 64 && dst.pitchY == (long long)s.rowBytes &&
       (s.nz == 1 || dst.pitchZ == (long long)s.rowBytes * s.ny) && ((src.pitchY | src.pitchZ) & 3) == 0) {
     bool ok = true;
     for (int p = 0; p < 2; ++p) ok = ok && (((uintptr_t)s.src[p] | (uintptr_t)s.dst[p]) & 3) == 0;
