@@ -774,6 +774,20 @@ std::vector<ATile> make_atiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, i
         for (const auto &col : cols)
           if (col.second) emit(col.first, y0, narrowY, true);
     }
+  if (const char *e = std::getenv("STENCIL_ASTAROTH_TILE_ORDER")) {
+    /* experiments: 1 = field innermost (the same tile of every field back to back), 2 = z chunk outermost, then field */
+    const int mode = std::atoi(e);
+    if (mode == 1)
+      std::stable_sort(out.begin(), out.end(), [&](const ATile &a, const ATile &b) {
+        if (a.chunk != b.chunk) return a.chunk < b.chunk;
+        if (a.narrow != b.narrow) return a.narrow < b.narrow;
+        if (a.y0 != b.y0) return a.y0 < b.y0;
+        if (a.x0 != b.x0) return a.x0 < b.x0;
+        return a.field < b.field;
+      });
+    else if (mode == 2)
+      std::stable_sort(out.begin(), out.end(), [&](const ATile &a, const ATile &b) { return a.chunk < b.chunk; });
+  }
   if (flaggedFirst && flagMask) {
     const unsigned zbits = (1u << kZM) | (1u << kZP);
     auto prio = [&](const ATile &t) { return (t.dirs & flagMask & zbits) ? 0 : ((t.dirs & flagMask) ? 1 : 2); };
