@@ -38,6 +38,7 @@ public:
                               // Jacobi kernel): all 26 directions stay current with no exchange() left in steady state
     bool narrowTiles = true;  // TMA kernel: cover the remainder of rows that are not a multiple of the tile with 8-lane tiles
     bool flaggedFirst = true; // TMA kernel: schedule the tiles that push to ANOTHER GPU first
+    bool zigzag = true;       // TMA kernel: neighbouring z chunks march in opposite directions (shared planes hit L2)
     double crossWeight = 0.25; // Star19Cross: weight of the cross-derivative terms
     bool useTma = true; // Star19: TMA + mbarrier pipelined kernel for regions wide enough to fill its tiles
     std::vector<int> gpus;

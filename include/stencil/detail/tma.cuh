@@ -39,6 +39,22 @@ __device__ __forceinline__ void load_3d(void *dst, const CUtensorMap *map, int c
 }
 #endif
 
+/* Keep a small, hot table (the per-launch tile table: every CTA starts by reading its entry, and nothing can be issued
+   before it arrives) resident in L2 across iterations that stream gigabytes through it: persisting access-policy window
+   on the stream that runs the kernels. Best effort: failures (e.g. MPS without persisting L2) are ignored. */
+inline void keep_in_l2(cudaStream_t stream, const void *base, size_t bytes) {
+  if (!base || !bytes) return;
+  (void)cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, 4u << 20);
+  cudaStreamAttrValue v;
+  v.accessPolicyWindow.base_ptr = const_cast<void *>(base);
+  v.accessPolicyWindow.num_bytes = bytes;
+  v.accessPolicyWindow.hitRatio = 1.0f;
+  v.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+  v.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+  (void)cudaStreamSetAttribute(stream, cudaStreamAttributeAccessPolicyWindow, &v);
+  (void)cudaGetLastError();
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
                                   const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
                                   CUtensorMapFloatOOBfill);

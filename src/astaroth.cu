@@ -381,7 +381,7 @@ inline unsigned tile_dirs(int ylo, int tr, int z0, int z1, int sy, int sz, unsig
 struct ATile {
   int x0, y0;           // first cell / row of the tile (compute coordinates)
   unsigned short chunk; // z chunk of the region: planes loz + chunk*tileZ ...
-  unsigned char field, dirs, narrow, pad[3];
+  unsigned char field, dirs, narrow, down, pad[2]; // down: march z downwards (neighbouring chunks alternate, see astaroth_tile)
 };
 
 template <typename T> struct TmaParams {
@@ -427,6 +427,11 @@ __device__ __forceinline__ void astaroth_tile(unsigned char *smem, const TmaPara
   if ((dirs & P.pushFlagMask) && threadIdx.x == 0) asm volatile("fence.proxy.async.global;" ::: "memory");
 
   const int nplanes = z1 - z0 + 2 * kR; // input planes z0-3 .. z1+2
+  /* Neighbouring z chunks march in opposite directions, so the six planes both of them read are fetched by both at the
+     same end of their march, at about the same time, and the second fetch hits L2 (marching everything upwards re-read
+     them a whole tile duration apart: a third more DRAM reads than the minimum). The stencil is symmetric in z; only the
+     z-coupled cross terms change sign. */
+  const bool down = t.down != 0;
   const CUtensorMap *map = P.maps + 2 * field + (LW == 32 ? 0 : 1);
   const int cx = P.x0pad + t.x0 - kTMargin; // raw x of smem column 0
   const int cy = t.y0;                      // raw row of compute row y0 - 3 (raw = compute + 3)
@@ -434,7 +439,7 @@ __device__ __forceinline__ void astaroth_tile(unsigned char *smem, const TmaPara
     const int sj = j % kTStages;
     if (j >= kTStages) tma::mbar_wait(&empty[sj], ((j / kTStages) - 1) & 1);
     tma::mbar_arrive_expect_tx(&full[sj], G::planeBytes);
-    tma::load_3d(smem + sj * G::stageBytes, map, cx, cy, z0 + j, &full[sj]);
+    tma::load_3d(smem + sj * G::stageBytes, map, cx, cy, down ? z1 + 2 * kR - 1 - j : z0 + j, &full[sj]);
   };
   if (threadIdx.x == 0)
     for (int j = 0; j < kTStages - kTLag && j < nplanes; ++j) issue(j);
@@ -449,7 +454,7 @@ __device__ __forceinline__ void astaroth_tile(unsigned char *smem, const TmaPara
     const int y = y0 + r;
     const bool in = y >= P.loy && y < P.hiy && x0 < P.hix && x0 + N > P.lox;
     mode[r] = !in ? 0 : ((x0 >= P.lox && x0 + N <= P.hix) ? 1 : 2);
-    dp[r] = P.dst[field] + (long long)z0 * P.pitchXY + (long long)y * P.pitchX + x0;
+    dp[r] = P.dst[field] + (long long)(down ? z1 - 1 : z0) * P.pitchXY + (long long)y * P.pitchX + x0;
   }
   /* Fused x faces (periodic wrap onto this subdomain): the lanes that own cells 0..2 or sx-3..sx-1 store their output
      vector a second time, sx cells further / earlier in the same row — that is where the opposite halo lives. The extra
@@ -468,6 +473,8 @@ __device__ __forceinline__ void astaroth_tile(unsigned char *smem, const TmaPara
   }
   const T c1 = T(1.5), c2 = T(-0.15), c3 = T(1.0 / 90.0), c0x3 = T(3) * T(-49.0 / 18.0);
   const T k1 = P.eta * CrossW<T>::m1(), k2 = P.eta * CrossW<T>::m2(), k3 = P.eta * CrossW<T>::m3();
+  const T zs = down ? T(-1) : T(1), kz1 = zs * k1, kz2 = zs * k2, kz3 = zs * k3; // z-coupled cross terms follow the march
+  const long long outStride = down ? -P.pitchXY : P.pitchXY;
   /* pending sums for the planes 1, 2, 3 behind the newest one, and the centres of those planes */
   T a1[2][N], a2[2][N], a3[2][N], h1[2][N], h2[2][N], h3[2][N];
   /* CROSS: sums collected AHEAD of the planes 1, 2, 3 in front of the newest one (the "below" halves of Dxz, Dyz, Dxyz) */
@@ -589,12 +596,12 @@ __device__ __forceinline__ void astaroth_tile(unsigned char *smem, const TmaPara
       for (int i = 0; i < N; ++i) {
         const T c = col[3 + r][i];
         if (CROSS) {
-          out[i] = h3[r][i] + P.dt * ((a3[r][i] + c3 * c) + k3 * e3[r][i]);
-          a3[r][i] = (a2[r][i] + c2 * c) + k2 * e2[r][i];
-          a2[r][i] = (a1[r][i] + c1 * c) + k1 * e1[r][i];
-          b1[r][i] = b2[r][i] - k1 * e1[r][i];
-          b2[r][i] = b3[r][i] - k2 * e2[r][i];
-          b3[r][i] = -(k3 * e3[r][i]);
+          out[i] = h3[r][i] + P.dt * ((a3[r][i] + c3 * c) + kz3 * e3[r][i]);
+          a3[r][i] = (a2[r][i] + c2 * c) + kz2 * e2[r][i];
+          a2[r][i] = (a1[r][i] + c1 * c) + kz1 * e1[r][i];
+          b1[r][i] = b2[r][i] - kz1 * e1[r][i];
+          b2[r][i] = b3[r][i] - kz2 * e2[r][i];
+          b3[r][i] = -(kz3 * e3[r][i]);
         } else {
           out[i] = h3[r][i] + P.dt * (a3[r][i] + c3 * c);
           a3[r][i] = a2[r][i] + c2 * c;
@@ -605,7 +612,7 @@ __device__ __forceinline__ void astaroth_tile(unsigned char *smem, const TmaPara
         h2[r][i] = h1[r][i];
         h1[r][i] = c;
       }
-      if (j >= 2 * kR) { // output plane z0 + j - 6
+      if (j >= 2 * kR) { // output plane z0 + j - 6 (marching down: z1 - 1 - (j - 6))
         if (mode[r] == 1) {
           V v;
           memcpy(&v, out, sizeof(V));
@@ -628,7 +635,7 @@ __device__ __forceinline__ void astaroth_tile(unsigned char *smem, const TmaPara
               if (qdelta && (x0 + i < kR || x0 + i >= P.wrapX - kR)) dp[r][qdelta + i] = out[i];
             }
         }
-        dp[r] += P.pitchXY;
+        dp[r] += outStride;
       }
     }
   }
@@ -732,7 +739,7 @@ const Dim3 kPushDir[kDirs] = {Dim3(0, -1, 0), Dim3(0, 1, 0), Dim3(0, 0, -1), Dim
    and planes resident together; tiles that push to another GPU come first (z directions, then the others) so that
    every direction is announced early in the kernel — see make_tiles() in src/jacobi.cu for the reasoning. */
 std::vector<ATile> make_atiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int fields, int tileZ, int vecN, unsigned dirMask, unsigned flagMask,
-                               unsigned *nDir, bool narrowOk, bool flaggedFirst) {
+                               unsigned *nDir, bool narrowOk, bool flaggedFirst, bool zigzag) {
   std::vector<ATile> out;
   if (nDir)
     for (int d = 0; d < kDirs; ++d) nDir[d] = 0;
@@ -761,6 +768,7 @@ std::vector<ATile> make_atiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, i
         t.chunk = (unsigned short)c;
         t.field = (unsigned char)f;
         t.narrow = nar ? 1 : 0;
+        t.down = (zigzag && (c & 1)) ? 1 : 0;
         t.dirs = (unsigned char)tile_dirs(int(y0), int(tr), z0, z1, int(sz.y), int(sz.z), dirMask);
         if (nDir)
           for (int d = 0; d < kDirs; ++d)
@@ -861,6 +869,7 @@ AstarothSim::AstarothSim(size_t x, size_t y, size_t z, const Options &opt) : opt
   impl_->exterior = dd_->get_exterior();
   if (std::getenv("STENCIL_ASTAROTH_NO_TMA")) opt_.useTma = false;
   if (std::getenv("STENCIL_ASTAROTH_NO_NARROW")) opt_.narrowTiles = false;
+  if (std::getenv("STENCIL_ASTAROTH_NO_ZIGZAG")) opt_.zigzag = false;
   if (std::getenv("STENCIL_ASTAROTH_NATURAL_ORDER")) opt_.flaggedFirst = false;
   if (const char *e = std::getenv("STENCIL_LAUNCH_THREADS")) impl_->launchThreads = std::atoi(e) != 0;
   for (LocalDomain &ld : dd_->domains()) {
@@ -920,12 +929,13 @@ AstarothSim::AstarothSim(size_t x, size_t y, size_t z, const Options &opt) : opt
       /* tile tables: the whole region carries the push directions (filled in by setup_fused_faces when fused) */
       const Dim3 sz = ld.size(), org = ld.origin();
       if (!impl_->tilesAll[di].dev)
-        impl_->tilesAll[di] = Impl::upload(make_atiles(Dim3(0, 0, 0), sz, sz, opt_.fields, opt_.tileZ, vecN, 0, 0, nullptr, opt_.narrowTiles, false));
+        impl_->tilesAll[di] = Impl::upload(make_atiles(Dim3(0, 0, 0), sz, sz, opt_.fields, opt_.tileZ, vecN, 0, 0, nullptr, opt_.narrowTiles, false, opt_.zigzag));
+      tma::keep_in_l2(impl_->streams[di], impl_->tilesAll[di].dev, size_t(impl_->tilesAll[di].n) * sizeof(ATile));
       impl_->tilesInterior[di] = Impl::upload(make_atiles(impl_->interior[di].lo - org, impl_->interior[di].hi - org, sz, opt_.fields, opt_.tileZ,
-                                                          vecN, 0, 0, nullptr, opt_.narrowTiles, false));
+                                                          vecN, 0, 0, nullptr, opt_.narrowTiles, false, opt_.zigzag));
       for (const Rect3 &r : impl_->exterior[di])
         impl_->tilesExterior[di].push_back(
-            Impl::upload(make_atiles(r.lo - org, r.hi - org, sz, opt_.fields, opt_.tileZ, vecN, 0, 0, nullptr, opt_.narrowTiles, false)));
+            Impl::upload(make_atiles(r.lo - org, r.hi - org, sz, opt_.fields, opt_.tileZ, vecN, 0, 0, nullptr, opt_.narrowTiles, false, opt_.zigzag)));
     }
   }
   init();
@@ -973,7 +983,7 @@ void AstarothSim::setup_fused_faces() {
     /* the tile table of the whole-region launch decides which CTAs take part in which hand-shake */
     const Dim3 sz = ld.size();
     impl_->tilesAll[di] = Impl::upload(make_atiles(Dim3(0, 0, 0), sz, sz, opt_.fields, opt_.tileZ, vecN, p.dirMask, p.flagMask, p.nDir,
-                                                   opt_.narrowTiles, opt_.flaggedFirst));
+                                                   opt_.narrowTiles, opt_.flaggedFirst, opt_.zigzag));
     CUDA_RUNTIME(cudaMalloc(&p.done, kDirs * sizeof(unsigned)));
     CUDA_RUNTIME(cudaMemset(p.done, 0, kDirs * sizeof(unsigned)));
     for (int parity = 0; parity < 2; ++parity)

@@ -7,22 +7,29 @@ O=gpurun_out/exp.txt
 : > $O
 J=./build/bin/jacobi3d
 A=./build/bin/astaroth-sim
-OLD=./build/old_src/bld/bin/astaroth-sim
-run() { echo "## $*" >> $O; timeout 300 "$@" 2>/dev/null | grep -E "device|astaroth|verify|weak|^\[" >> $O; }
-for g in "[pack]" "[translate]" "[packer]" "[exchange]" "[jacobi]" "[tx]"; do
+run() { echo "## $TAG $*" >> $O; timeout 300 "$@" 2>/dev/null | grep -E "device|astaroth|verify|weak|^\[" >> $O; }
+for g in "[jacobi]" "[astaroth]"; do
   timeout 900 ./build/bin/test_cuda "$g" > "gpurun_out/test_$g.log" 2>&1; echo "test $g rc=$? $(tail -1 "gpurun_out/test_$g.log")" >> $O
 done
-for cfg in "512 512 512" "1024 512 256" "2048 256 256"; do
-  run $J $cfg --exact-size -n 30 --tile-z 16 --device-time
+for cfg in "512 512 512" "1024 512 256" "645 645 323"; do
+  TAG=zigzag run $J $cfg --exact-size -n 30 --tile-z 16 --device-time
+  TAG=nozz STENCIL_JACOBI_NO_ZIGZAG=1 run $J $cfg --exact-size -n 30 --tile-z 16 --device-time
 done
-run ./build/bin/bench-pack --iters 30
-run ./baseline/_ref/bin/bench-pack --iters 30
-run ./build/bin/weak 512 512 512 30
-run ./build/bin/weak-exchange 512 512 512 30
-STENCIL_EXCHANGE_TRACE=2 ./build/bin/weak 512 512 512 4 2>&1 | grep "exchange " | tail -2 >> $O
-export STENCIL_ASTAROTH_NO_FUSED_YZ=1
-C="--x 256 --y 256 --z 256 --fields 8 --double --star19 --iters 6"
-ncu --set full --clock-control none --import-source on -k regex:astaroth_tma -s 3 -c 1 -f -o gpurun_out/prof_ast_new $A $C > /dev/null 2>&1
-ncu --set full --clock-control none --import-source on -k regex:astaroth_tma -s 3 -c 1 -f -o gpurun_out/prof_ast_old $OLD $C > /dev/null 2>&1
-unset STENCIL_ASTAROTH_NO_FUSED_YZ
+TAG=zigzag run $J 512 512 512 --exact-size -n 30 --tile-z 16 --device-time --no-overlap
+TAG=nozz STENCIL_JACOBI_NO_ZIGZAG=1 run $J 512 512 512 --exact-size -n 30 --tile-z 16 --device-time --no-overlap
+TAG=zz32 run $J 512 512 512 --exact-size -n 30 --tile-z 32 --device-time
+TAG=zz8 run $J 512 512 512 --exact-size -n 30 --tile-z 8 --device-time
+C="--x 256 --y 256 --z 256 --fields 8 --double --star19 --iters 20"
+TAG=zigzag run $A $C
+TAG=nozz STENCIL_ASTAROTH_NO_ZIGZAG=1 run $A $C
+TAG=order1 STENCIL_ASTAROTH_TILE_ORDER=1 run $A $C
+TAG=order2 STENCIL_ASTAROTH_TILE_ORDER=2 run $A $C
+TAG=order2nozz STENCIL_ASTAROTH_TILE_ORDER=2 STENCIL_ASTAROTH_NO_ZIGZAG=1 run $A $C
+TAG=cross run $A --x 256 --y 256 --z 256 --fields 8 --double --cross --iters 10
+TAG=check run $A --x 100 --y 70 --z 90 --fields 3 --double --cross --iters 6 --check
+M=gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum
+ncu --metrics $M --clock-control none -k regex:jacobi7 -s 4 -c 2 --csv --log-file gpurun_out/ncu_jz.csv $J 512 512 512 --exact-size -n 8 --tile-z 16 > /dev/null 2>&1
+echo "## ncu jacobi zigzag" >> $O; grep jacobi7 gpurun_out/ncu_jz.csv | awk -F'","' '{print $(NF-2), $(NF)}' >> $O
+ncu --metrics $M --clock-control none -k regex:astaroth_tma -s 3 -c 2 --csv --log-file gpurun_out/ncu_az.csv $A --x 256 --y 256 --z 256 --fields 8 --double --star19 --iters 6 > /dev/null 2>&1
+echo "## ncu astaroth zigzag" >> $O; grep astaroth_tma gpurun_out/ncu_az.csv | awk -F'","' '{print $(NF-2), $(NF)}' >> $O
 cat $O; grep -h -B2 -A8 FAIL gpurun_out/test_*.log | head -60
