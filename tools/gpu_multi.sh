@@ -28,6 +28,12 @@ run $TR --master-port 29631 --no-python $B/weak 512 512 512 30
 [ -n "$SKIP_REF" ] || run $ROOT/$R/weak 512 512 512 30 --peer --kernel
 run $B/astaroth-sim --x 256 --y 256 --z 256 --fields 8 --double --star19 --iters 20 --weak
 run $TR --master-port 29641 --no-python $B/astaroth-sim --x 256 --y 256 --z 256 --fields 8 --double --star19 --iters 20 --weak
+# NVLink bytes of the fused kernel (1 process x N GPUs under ncu; kernels are serialised by the profiler, flags refer to the
+# previous iteration, so nothing can wait for ever; bounded by timeout all the same)
+NV=gpu__time_duration.sum,nvltx__bytes.sum,nvlrx__bytes.sum,nvltx__bytes_data_user.sum,nvlrx__bytes_data_user.sum,dram__bytes_read.sum,dram__bytes_write.sum
+( cd /tmp && timeout 300 ncu --metrics $NV --clock-control none -k regex:jacobi7 -s $((4 * N)) -c $((2 * N)) --csv --log-file $ROOT/gpurun_out/ncu_nvlink_n$N.csv \
+    $B/jacobi3d 512 512 512 -n 8 --tile-z 16 > /dev/null 2>&1 ); echo "ncu nvlink rc=$?" >> $O
+grep jacobi7 gpurun_out/ncu_nvlink_n$N.csv 2>/dev/null | awk -F'","' '{print $(NF-2), $(NF)}' >> $O
 echo "## bench.py under torchrun, $N ranks" >> $O
 timeout 900 $TR --master-port 29621 bench.py --gpus $N --steps 30 --warmup 5 > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err; echo "bench rc=$?" >> $O
 echo "## reference, $N GPUs" >> $O

@@ -13,7 +13,9 @@ KEYS = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
         "smsp__sass_inst_executed_op_local_ld.sum", "smsp__sass_inst_executed_op_local_st.sum", "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
         "smsp__pcsamp_warps_issue_stalled_long_scoreboard", "smsp__pcsamp_warps_issue_stalled_barrier", "smsp__pcsamp_warps_issue_stalled_membar",
         "smsp__pcsamp_warps_issue_stalled_wait", "smsp__pcsamp_warps_issue_stalled_not_selected", "smsp__pcsamp_warps_issue_stalled_selected",
-        "smsp__pcsamp_warps_issue_stalled_short_scoreboard", "smsp__pcsamp_warps_issue_stalled_math_pipe_throttle"]
+        "smsp__pcsamp_warps_issue_stalled_short_scoreboard", "smsp__pcsamp_warps_issue_stalled_math_pipe_throttle",
+        # NVLink traffic of kernels that store into a peer GPU (captured with --metrics nvltx__bytes.sum,nvlrx__bytes.sum)
+        "nvltx__bytes.sum", "nvlrx__bytes.sum", "nvltx__bytes_data_user.sum", "nvlrx__bytes_data_user.sum"]
 
 
 def main(rep, out):
