@@ -2,6 +2,8 @@
 /* Thin wrappers over the Blackwell/Hopper asynchronous-copy PTX used by the stencil kernels: mbarrier
    (init / arrive / expect_tx / parity wait) and cp.async.bulk.tensor.3d (TMA tile load into shared memory), plus the
    host-side tensor-map encoder fetched through the runtime so that the library does not link against libcuda. */
+#include <cstdlib>
+
 #include <cuda.h>
 #include <cuda_runtime.h>
 
@@ -43,7 +45,7 @@ __device__ __forceinline__ void load_3d(void *dst, const CUtensorMap *map, int c
    before it arrives) resident in L2 across iterations that stream gigabytes through it: persisting access-policy window
    on the stream that runs the kernels. Best effort: failures (e.g. MPS without persisting L2) are ignored. */
 inline void keep_in_l2(cudaStream_t stream, const void *base, size_t bytes) {
-  if (!base || !bytes) return;
+  if (!base || !bytes || std::getenv("STENCIL_NO_L2_KEEP")) return;
   (void)cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, 4u << 20);
   cudaStreamAttrValue v;
   v.accessPolicyWindow.base_ptr = const_cast<void *>(base);

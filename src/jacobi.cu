@@ -36,7 +36,6 @@
 #include <algorithm>
 #include <cstring>
 #include <set>
-#include <type_traits>
 
 #include <cuda.h>
 
@@ -90,9 +89,8 @@ struct Tile {
   int x0, y0;           // first cell / first row of the tile (compute coordinates)
   unsigned short tz;    // z index in units of tileZ
   unsigned char faces;  // bit f set when the tile owns cells on face f that must be pushed
-  unsigned char narrow; // TMA variant: bit 0: 32 x 64 tile instead of 128 x 16; bit 1: march z downwards (kTileDown)
+  unsigned char narrow; // TMA variant: 1 = 32 x 64 tile, 0 = 128 x 16
 };
-constexpr unsigned char kTileNarrow = 1, kTileDown = 2;
 
 struct JacobiParams {
   const float *src; // interior origin: compute cell (0,0,0) of curr
@@ -466,11 +464,6 @@ __device__ __forceinline__ void tma_tile(unsigned char *smem, const CUtensorMap 
      `empty` barrier is almost always already satisfied. */
   const int cx = P.tmaX0 + t.x0 - 4; // 4 cells of left margin keep the centre 16-byte aligned in smem
   const int cy = t.y0;               // raw row of compute row (y0 - 1)
-  /* Neighbouring z tiles march in opposite directions (make_tiles alternates), so the two planes they both read are
-     fetched by both at the same end of their march — at about the same time, since tiles of adjacent layers start
-     within a fraction of a tile's duration of each other — and the second fetch hits L2 instead of DRAM. Marching
-     everything upwards re-read those planes a whole tile duration apart: 14 % more DRAM reads than the minimum. */
-  const bool down = (t.narrow & kTileDown) != 0;
   /* x wrap by load: does this tile hold the first / the last cell of the rows? */
   const bool sideL = FUSED && P.wrapLoad && t.x0 == 0;
   const bool sideR = FUSED && P.wrapLoad && t.x0 + G::kW >= P.sx;
@@ -479,13 +472,12 @@ __device__ __forceinline__ void tma_tile(unsigned char *smem, const CUtensorMap 
     if (j >= kTmaStages) mbar_wait(&empty[sj], ((j / kTmaStages) - 1) & 1);
     const int planeBytes = (LW == 32 && (P.debugSkip & 8u)) ? G::kBoxX * (G::kBoxY - 2) * 4 : G::kPlaneBytes;
     mbar_arrive_expect_tx(&full[sj], planeBytes + (sideL ? G::kSideBytes : 0) + (sideR ? G::kSideBytes : 0));
-    const int zr = down ? z1 + 1 - j : z0 + j; // raw plane (compute + 1): upwards z0-1 .. z1, downwards z1 .. z0-1
-    tma_load_3d(smem + sj * G::kStageBytes, tmap, cx, cy, zr, &full[sj]);
+    tma_load_3d(smem + sj * G::kStageBytes, tmap, cx, cy, z0 + j, &full[sj]);
     /* side boxes: the tile's rows (raw row cy + 1); left tiles want the aligned group of four cells that holds cell
        sx-1 (a TMA box must start on a 16-byte boundary: an unaligned start is an illegal instruction), right tiles
        cells 0 .. 3 */
-    if (sideL) tma_load_3d(smem + G::kSideOffset + sj * G::kSideBytes, tmapSide, P.tmaX0 + ((P.sx - 1) & ~3), cy + 1, zr, &full[sj]);
-    if (sideR) tma_load_3d(smem + G::kSideOffset + (kTmaStages + sj) * G::kSideBytes, tmapSide, P.tmaX0, cy + 1, zr, &full[sj]);
+    if (sideL) tma_load_3d(smem + G::kSideOffset + sj * G::kSideBytes, tmapSide, P.tmaX0 + ((P.sx - 1) & ~3), cy + 1, z0 + j, &full[sj]);
+    if (sideR) tma_load_3d(smem + G::kSideOffset + (kTmaStages + sj) * G::kSideBytes, tmapSide, P.tmaX0, cy + 1, z0 + j, &full[sj]);
   };
   if (threadIdx.x == 0)
     for (int j = 0; j < kTmaStages - kTmaLag && j < nplanes; ++j) issue(j);
@@ -529,9 +521,9 @@ __device__ __forceinline__ void tma_tile(unsigned char *smem, const CUtensorMap 
       const int y = y0 + r;
       const bool in = y >= P.loy && y < P.hiy && x0 < P.hix && x0 + kVec > P.lox;
       mode[r] = !in ? 0 : ((x0 >= P.lox && x0 + kVec <= P.hix) ? 1 : 2);
-      dp[r] = P.dst + (long long)(down ? z1 - 1 : z0) * P.pitchXY + (long long)y * P.pitchX + x0;
+      dp[r] = P.dst + (long long)z0 * P.pitchXY + (long long)y * P.pitchX + x0;
     }
-    const long long planeStride = down ? -P.pitchXY : P.pitchXY;
+    const long long planeStride = P.pitchXY;
     /* Register plan without copies: the centre of plane i is needed again two planes later (as "below"), so two
        register sets alternate (even / odd planes) and the loop is unrolled by two; the in-plane partial sum is
        overwritten in place once the output that needs it has been formed. */
@@ -539,8 +531,7 @@ __device__ __forceinline__ void tma_tile(unsigned char *smem, const CUtensorMap 
     cmA[0] = cmA[1] = cmB[0] = cmB[1] = part[0] = part[1] = make_float4(0.f, 0.f, 0.f, 0.f);
     int s = 0;
     unsigned phase = 0;
-    auto plane = [&](auto downTag, const int i, float4 (&below)[2]) { // `below` holds plane i-2 on entry and plane i on exit
-      constexpr bool DOWN = decltype(downTag)::value;
+    auto plane = [&](const int i, float4 (&below)[2]) { // `below` holds plane i-2 on entry and plane i on exit
       mbar_wait(&full[s], phase);
       const float *pl = reinterpret_cast<const float *>(smem + s * G::kStageBytes);
       /* smem row j holds compute row t.y0 + j - 1; smem column 4 + k holds compute x = t.x0 + k */
@@ -577,29 +568,16 @@ __device__ __forceinline__ void tma_tile(unsigned char *smem, const CUtensorMap 
         phase ^= 1u;
       }
       if (i >= 2) {
-        /* output plane: the one between this plane and the one two steps back. The reference adds +z before -z: marching
-           up, +z is this plane; marching down, it is the older one */
-        const int z = DOWN ? z1 + 1 - i : z0 + i - 2;
+        const int z = z0 + i - 2; // output plane: above = centre of this plane, below = centre two planes back
         float4 o[2];
-        if (DOWN) {
-          o[0].x = div6((part[0].x + below[0].x) + c0.x);
-          o[0].y = div6((part[0].y + below[0].y) + c0.y);
-          o[0].z = div6((part[0].z + below[0].z) + c0.z);
-          o[0].w = div6((part[0].w + below[0].w) + c0.w);
-          o[1].x = div6((part[1].x + below[1].x) + c1.x);
-          o[1].y = div6((part[1].y + below[1].y) + c1.y);
-          o[1].z = div6((part[1].z + below[1].z) + c1.z);
-          o[1].w = div6((part[1].w + below[1].w) + c1.w);
-        } else {
-          o[0].x = div6((part[0].x + c0.x) + below[0].x);
-          o[0].y = div6((part[0].y + c0.y) + below[0].y);
-          o[0].z = div6((part[0].z + c0.z) + below[0].z);
-          o[0].w = div6((part[0].w + c0.w) + below[0].w);
-          o[1].x = div6((part[1].x + c1.x) + below[1].x);
-          o[1].y = div6((part[1].y + c1.y) + below[1].y);
-          o[1].z = div6((part[1].z + c1.z) + below[1].z);
-          o[1].w = div6((part[1].w + c1.w) + below[1].w);
-        }
+        o[0].x = div6((part[0].x + c0.x) + below[0].x);
+        o[0].y = div6((part[0].y + c0.y) + below[0].y);
+        o[0].z = div6((part[0].z + c0.z) + below[0].z);
+        o[0].w = div6((part[0].w + c0.w) + below[0].w);
+        o[1].x = div6((part[1].x + c1.x) + below[1].x);
+        o[1].y = div6((part[1].y + c1.y) + below[1].y);
+        o[1].z = div6((part[1].z + c1.z) + below[1].z);
+        o[1].w = div6((part[1].w + c1.w) + below[1].w);
         if (sphFast) {
           /* vector wholly inside a sphere: the sphere's temperature; wholly outside both: nothing; else the exact
              per-cell test (cells inside cost 2.7x a normal cell when all of them took that path: a 1024-cell domain
@@ -645,18 +623,12 @@ __device__ __forceinline__ void tma_tile(unsigned char *smem, const CUtensorMap 
       part[1].z = ((c1.w + c1.y) + north.z) + c0.z;
       part[1].w = ((e1 + c1.z) + north.w) + c0.w;
     };
-    auto march = [&](auto downTag) {
-      int i = 0;
-      for (; i + 1 < nplanes; i += 2) {
-        plane(downTag, i, cmA);
-        plane(downTag, i + 1, cmB);
-      }
-      if (i < nplanes) plane(downTag, i, cmA);
-    };
-    if (down)
-      march(std::true_type());
-    else
-      march(std::false_type());
+    int i = 0;
+    for (; i + 1 < nplanes; i += 2) {
+      plane(i, cmA);
+      plane(i + 1, cmB);
+    }
+    if (i < nplanes) plane(i, cmA);
   }
 
   if (FUSED && t.faces) {
@@ -682,7 +654,7 @@ __global__ void __launch_bounds__(kTmaThreads, MINB)
                        const __grid_constant__ JacobiParams P) {
   extern __shared__ __align__(128) unsigned char smem[];
   const Tile t = P.tiles[blockIdx.x];
-  if (t.narrow & kTileNarrow)
+  if (t.narrow)
     tma_tile<FUSED, Narrow>(smem, &tmapNarrow, &tmapSideNarrow, P, t);
   else
     tma_tile<FUSED, Wide>(smem, &tmapWide, &tmapSideWide, P, t);
@@ -813,7 +785,7 @@ namespace {
    GPUs may drift by most of an iteration without anybody spinning. Cost: two planes per z face and one row per y-face
    tile lose their L2 hit (< 1 % of the traffic). */
 std::vector<Tile> make_tiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int rows, int tileZ, unsigned faceMask, unsigned *nFace,
-                             bool narrow, bool flaggedFirst = true, unsigned countMask = 0, bool zigzag = false) {
+                             bool narrow, bool flaggedFirst = true, unsigned countMask = 0) {
   std::vector<Tile> out;
   if (nFace)
     for (int f = 0; f < 6; ++f) nFace[f] = 0;
@@ -843,9 +815,7 @@ std::vector<Tile> make_tiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int
     if (nFace)
       for (int k = 0; k < 6; ++k)
         if ((f & countMask) >> k & 1u) ++nFace[k];
-    /* odd z layers march downwards (TMA kernel only): see tma_tile */
-    const unsigned char flags = (unsigned char)((nar ? kTileNarrow : 0) | ((zigzag && (tz & 1)) ? kTileDown : 0));
-    out.push_back(Tile{int(x0), int(y0), (unsigned short)tz, (unsigned char)f, flags});
+    out.push_back(Tile{int(x0), int(y0), (unsigned short)tz, (unsigned char)f, (unsigned char)(nar ? 1 : 0)});
   };
   for (int64_t tz = lo.z / tileZ; tz * tileZ < hi.z; ++tz) {
     /* wide columns row block by row block, then the narrow columns (their row blocks are four times as tall) */
@@ -922,7 +892,6 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
   if (opt_.useTma && opt_.tileZ > kMaxTileZ) opt_.tileZ = kMaxTileZ;
   if (std::getenv("STENCIL_JACOBI_NATURAL_ORDER")) opt_.flaggedFirst = false;
   if (std::getenv("STENCIL_JACOBI_NO_NARROW")) opt_.narrowTiles = false;
-  if (std::getenv("STENCIL_JACOBI_NO_ZIGZAG")) opt_.zigzag = false;
   if (const char *e = std::getenv("STENCIL_LAUNCH_THREADS")) opt_.launchThreads = std::atoi(e) != 0;
   dd_.reset(comm ? new DistributedDomain(x, y, z, *comm) : new DistributedDomain(x, y, z));
   if (!opt_.gpus.empty()) dd_->set_gpus(opt_.gpus);
@@ -1023,23 +992,24 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
     d.sameDevDeps.assign(deps.begin(), deps.end());
     const int rows = impl_->rows;
     const bool narrow = impl_->useTma && opt_.narrowTiles;
-    const bool zigzag = impl_->useTma && opt_.zigzag;
-    const std::vector<Tile> all = make_tiles(Dim3(0, 0, 0), sz, sz, rows, opt_.tileZ, faceMask, d.nFace, narrow, opt_.flaggedFirst, flagMask, zigzag);
+    const std::vector<Tile> all = make_tiles(Dim3(0, 0, 0), sz, sz, rows, opt_.tileZ, faceMask, d.nFace, narrow, opt_.flaggedFirst, flagMask);
     d.tilesAll = upload(all);
     d.nAll = unsigned(all.size());
     auto note_narrow = [&d](const std::vector<Tile> &v) {
-      for (const Tile &t : v) d.anyNarrow = d.anyNarrow || (t.narrow & kTileNarrow);
+      for (const Tile &t : v) d.anyNarrow = d.anyNarrow || t.narrow;
     };
     note_narrow(all);
+    /* every CTA starts by reading its table entry and nothing can be issued before it arrives: keep the table in L2
+       across iterations that stream a gigabyte through it (measured 1.4 % on 512^3) */
     if (impl_->useTma) tma::keep_in_l2(d.stream, d.tilesAll, all.size() * sizeof(Tile));
     d.interior = interiors[di];
     d.exterior = exteriors[di];
-    const std::vector<Tile> in = make_tiles(d.interior.lo - org, d.interior.hi - org, sz, rows, opt_.tileZ, 0, nullptr, narrow, true, 0, zigzag);
+    const std::vector<Tile> in = make_tiles(d.interior.lo - org, d.interior.hi - org, sz, rows, opt_.tileZ, 0, nullptr, narrow);
     note_narrow(in);
     d.tilesInterior = upload(in);
     d.nInterior = unsigned(in.size());
     for (const Rect3 &r : d.exterior) {
-      const std::vector<Tile> ex = make_tiles(r.lo - org, r.hi - org, sz, rows, opt_.tileZ, 0, nullptr, narrow, true, 0, zigzag);
+      const std::vector<Tile> ex = make_tiles(r.lo - org, r.hi - org, sz, rows, opt_.tileZ, 0, nullptr, narrow);
       note_narrow(ex);
       d.tilesExterior.emplace_back(upload(ex), unsigned(ex.size()));
     }
