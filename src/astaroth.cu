@@ -302,28 +302,54 @@ __device__ __noinline__ void push_tile_dirs(const PushParams<T> &Q, int field, u
     if (ny <= 0 || zb <= za) continue;
     T *nb = Q.nb[d][field];
     const long long npx = Q.nbPitchX[d], npxy = Q.nbPitchXY[d];
-    for (int r = warp; r < rows; r += nwarps) {
-      const int z = za + r / ny, y = ya + r % ny;
-      const T *src = mine + (long long)z * pitchXY + (long long)y * pitchX;
-      T *dst = nb + (long long)z * npxy + (long long)y * npx;
-      const bool vec = ((reinterpret_cast<unsigned long long>(dst + xlo) | reinterpret_cast<unsigned long long>(src + xlo)) & (sizeof(V) - 1)) == 0;
-      if (vec) {
-        for (int x = xlo + lane * N; x < xhi; x += 32 * N) {
-          if (x + N <= xhi) {
-            *reinterpret_cast<V *>(dst + x) = __ldcg(reinterpret_cast<const V *>(src + x));
+    /* two rows per pass, every load of both rows issued before the first store: the loop is bound by the L2 round trip of
+       a row, not by bytes */
+    const int xe = lane < kR ? lane : Q.sx - 2 * kR + lane;          // x-wrap cell this lane may carry (lanes 0..5)
+    const bool ext = lane < 2 * kR && xe >= xlo && xe < xhi;         // ... if this tile owns it
+    const int xeDst = lane < kR ? xe + Q.sx : xe - Q.sx;
+    for (int r = warp; r < rows; r += 2 * nwarps) {
+      const T *src[2];
+      T *dst[2];
+      bool on[2], vec[2];
+      V v[2];
+      T e[2], tail[2][N];
+      const int x = xlo + lane * N;
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const int rr = r + k * nwarps;
+        on[k] = rr < rows;
+        const int z = za + (on[k] ? rr : r) / ny, y = ya + (on[k] ? rr : r) % ny;
+        src[k] = mine + (long long)z * pitchXY + (long long)y * pitchX;
+        dst[k] = nb + (long long)z * npxy + (long long)y * npx;
+        vec[k] = ((reinterpret_cast<unsigned long long>(dst[k] + xlo) | reinterpret_cast<unsigned long long>(src[k] + xlo)) & (sizeof(V) - 1)) == 0;
+        v[k] = V();
+        e[k] = T(0);
+#pragma unroll
+        for (int i = 0; i < N; ++i) tail[k][i] = T(0);
+        if (on[k]) {
+          /* a tile is at most 32 vectors wide: one vector (or its in-range part) per lane */
+          if (vec[k] && x + N <= xhi) {
+            v[k] = __ldcg(reinterpret_cast<const V *>(src[k] + x));
           } else {
-            for (int i = x; i < xhi; ++i) dst[i] = __ldcg(src + i);
+#pragma unroll
+            for (int i = 0; i < N; ++i)
+              if (x + i < xhi) tail[k][i] = __ldcg(src[k] + x + i);
           }
+          if (ext) e[k] = __ldcg(src[k] + xe);
         }
-      } else {
-        for (int x = xlo + lane; x < xhi; x += 32) dst[x] = __ldcg(src + x);
       }
-      /* x wrap of this row (xy / xz edges and corners of the destination): only the cells this tile owns */
-      if (lane < kR) {
-        if (lane >= xlo && lane < xhi) dst[lane + Q.sx] = __ldcg(src + lane);
-      } else if (lane < 2 * kR) {
-        const int x = Q.sx - 2 * kR + lane;
-        if (x >= xlo && x < xhi) dst[x - Q.sx] = __ldcg(src + x);
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        if (!on[k]) continue;
+        if (vec[k] && x + N <= xhi) {
+          *reinterpret_cast<V *>(dst[k] + x) = v[k];
+        } else {
+#pragma unroll
+          for (int i = 0; i < N; ++i)
+            if (x + i < xhi) dst[k][x + i] = tail[k][i];
+        }
+        /* x wrap of this row (xy / xz edges and corners of the destination): only the cells this tile owns */
+        if (ext) dst[k][xeDst] = e[k];
       }
     }
   }
