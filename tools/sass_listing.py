@@ -10,9 +10,11 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "stencil2_b200", "lib", "libstencil_b200.so")
 OUT = os.path.join(ROOT, "profiles", "sass")
-KEEP = ["jacobi7_tma_kernelILb1ELi2", "jacobi7_tma_kernelILb0ELi2", "astaroth_tma_kernelId", "astaroth_tma_kernelIf", "box_copy_kernelILb1", "box_copy_kernelILb0", "box_copy_batch_kernel",
-        "wait_flags_kernel", "signal_flags_kernel", "reduce_sum_f32_kernel", "astaroth_kernelIdLb1", "astaroth_kernelIfLb0", "jacobi7_kernelILb0"]
-INTEREST = ["UTMALDG", "UTMASTG", "UBLKCP", "SYNCS", "MEMBAR", "LDG.E.128", "STG.E.128", "LDG.E.64", "STG.E.64", "LDG.E ", "STG.E ", "LDS.128", "LDS ",
+KEEP = ["jacobi7_tma_kernelILb1ELi2", "jacobi7_tma_kernelILb0ELi2", "astaroth_tma_kernelIdLb0", "astaroth_tma_kernelIdLb1", "astaroth_tma_kernelIfLb0",
+        "astaroth_cross_kernelId", "box_copy_kernelILb1", "box_copy_kernelILb0", "box_copy_batch_kernel",
+        "wait_flags_kernel", "signal_flags_kernel", "reduce_sum_f32_kernel", "astaroth_kernelIdLb1", "astaroth_kernelIfLb0", "jacobi7_kernelILb0",
+        "fingerprint_kernel"]
+INTEREST = ["UTMALDG", "UTMASTG", "UBLKCP", "SYNCS", "MEMBAR", "FENCE", "STG.E.ENL2.256", "LDG.E.ENL2.256", "LDG.E.128", "STG.E.128", "LDG.E.64", "STG.E.64", "LDG.E ", "STG.E ", "LDS.128", "LDS ",
             "SHFL", "ATOMG", "RED", "FFMA", "DFMA", "FADD", "DADD", "LD.E.STRONG.SYS", "ST.E.STRONG.SYS", "ERRBAR", "CCTL", "NANOSLEEP", "LDL", "STL"]
 
 
@@ -31,7 +33,7 @@ def main():
             dem = subprocess.run(["cu++filt", name], stdout=subprocess.PIPE, text=True).stdout.strip()
         except Exception:
             dem = name
-        lines = [l for l in body.splitlines() if re.search(r"/\*[0-9a-f]{4}\*/", l)]
+        lines = [l for l in body.splitlines() if re.search(r"/\*[0-9a-f]{4,6}\*/", l)]
         ops = collections.Counter()
         for l in lines:
             m = re.search(r"\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_.]+)", l)
