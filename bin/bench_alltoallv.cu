@@ -44,8 +44,18 @@ struct Pairwise {
         const size_t k = size_t(i * n + j);
         const int64_t b = bytes.at(i, j);
         if (!b) continue;
-        const Dim3 ext(b / 16, 1, 1);
-        plans[size_t(i)].add(stencil::BoxView::dense(src[k], ext, 16), Dim3(0, 0, 0), stencil::BoxView::dense(dst[k], ext, 16), Dim3(0, 0, 0), ext);
+        /* a message is a box of 64 KiB rows (+ one shorter row for the rest): the plan spreads ROWS over CTAs, so one
+           long row would be copied by a single warp */
+        const int64_t units = b / 16, rowUnits = 4096, rows = units / rowUnits, rest = units % rowUnits;
+        if (rows) {
+          const Dim3 ext(rowUnits, rows, 1);
+          plans[size_t(i)].add(stencil::BoxView::dense(src[k], ext, 16), Dim3(0, 0, 0), stencil::BoxView::dense(dst[k], ext, 16), Dim3(0, 0, 0), ext);
+        }
+        if (rest) {
+          const Dim3 ext(rest, 1, 1);
+          char *so = static_cast<char *>(src[k]) + rows * rowUnits * 16, *dn = static_cast<char *>(dst[k]) + rows * rowUnits * 16;
+          plans[size_t(i)].add(stencil::BoxView::dense(so, ext, 16), Dim3(0, 0, 0), stencil::BoxView::dense(dn, ext, 16), Dim3(0, 0, 0), ext);
+        }
       }
       plans[size_t(i)].finalize(i, 256 * 1024);
     }

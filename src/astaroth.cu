@@ -1240,13 +1240,19 @@ void AstarothSim::step() {
 }
 
 void AstarothSim::sync() {
-  for (size_t di = 0; di < dd_->domains().size(); ++di) {
+  const size_t nd = dd_->domains().size();
+  const unsigned long long timeoutNs = flag_timeout_ns();
+  const std::function<void(size_t)> drain = [&](size_t di) {
     DevGuard g(dd_->domains()[di].gpu());
     /* fused faces: my halos of the last iteration are complete only when every neighbour GPU raised its last flag */
     if (impl_->fusedYZ && impl_->iter > 0 && impl_->xHalosFromKernel)
-      launch_wait_flags(impl_->push[di].finalWait, impl_->iter, impl_->err, flag_timeout_ns(), impl_->streams[di]);
+      launch_wait_flags(impl_->push[di].finalWait, impl_->iter, impl_->err, timeoutNs, impl_->streams[di]);
     CUDA_RUNTIME(cudaStreamSynchronize(impl_->streams[di]));
-  }
+  };
+  if (nd > 1 && impl_->launchThreads)
+    impl_->pool.run(nd, drain);
+  else
+    for (size_t di = 0; di < nd; ++di) drain(di);
   dd_->exchange_wait(); // no-op unless an asynchronous exchange is still in flight
   if (impl_->err && *impl_->err) LOG_FATAL("AstarothSim: timed out waiting for a neighbour GPU (code " << *impl_->err << ", iteration " << impl_->iter << ")");
 }

@@ -1251,14 +1251,20 @@ void Jacobi3D::step_io(const void *paramsPinned, size_t nbytes, float *resultPin
 
 void Jacobi3D::sync() {
   std::vector<LocalDomain> &doms = dd_->domains();
-  for (size_t di = 0; di < doms.size(); ++di) {
+  const unsigned long long timeoutNs = flag_timeout_ns();
+  const std::function<void(size_t)> drain = [&](size_t di) {
     DevGuard g(doms[di].gpu());
     Impl::Dom &d = impl_->doms[di];
     /* fused: my halos of the final iteration are complete only when every neighbour raised its last flag */
-    if (opt_.mode == Mode::Fused && impl_->iter > 0) launch_wait_flags(d.finalWait, impl_->iter, impl_->err, flag_timeout_ns(), d.stream);
+    if (opt_.mode == Mode::Fused && impl_->iter > 0) launch_wait_flags(d.finalWait, impl_->iter, impl_->err, timeoutNs, d.stream);
     CUDA_RUNTIME(cudaStreamSynchronize(d.stream));
     CUDA_RUNTIME(cudaStreamSynchronize(d.ioOut));
-  }
+  };
+  /* several local GPUs: wait for all of them at once, not one after the other */
+  if (doms.size() > 1 && opt_.launchThreads)
+    impl_->pool.run(doms.size(), drain);
+  else
+    for (size_t di = 0; di < doms.size(); ++di) drain(di);
   if (*impl_->err) LOG_FATAL("Jacobi3D: timed out waiting for a neighbour (code " << *impl_->err << ", iteration " << impl_->iter << ")");
 }
 
