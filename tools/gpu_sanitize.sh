@@ -12,7 +12,7 @@ export STENCIL_FLAG_TIMEOUT_MS=600000
 S=gpurun_out/sanitizer/summary.txt
 : > $S
 for tool in memcheck racecheck; do
-  for g in "[pack]" "[exchange]" "[jacobi]" "[astaroth]"; do
+  for g in ${SAN_GROUPS:-"[pack]" "[exchange]" "[jacobi]" "[astaroth]"}; do
     name=$(echo "$g" | tr -d '[]')
     log=gpurun_out/sanitizer/${tool}_${name}.log
     timeout ${SAN_TIMEOUT:-1500} compute-sanitizer --tool $tool --error-exitcode 9 --print-limit 20 ./build/bin/test_cuda "$g" > $log 2>&1
