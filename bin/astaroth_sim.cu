@@ -15,7 +15,7 @@
 
 int main(int argc, char **argv) {
   size_t x = 512, y = 512, z = 512;
-  int iters = 5, fields = 1;
+  int iters = 5, fields = 1, tileZ = 0;
   bool remote = false, cudaAware = false, colocated = false, peer = false, kernel = false, direct = false, trivial = false;
   bool fp64 = false, star = false, cross = false, noOverlap = false, forceOverlap = false, weak = false, check = false;
   std::string file;
@@ -33,6 +33,7 @@ int main(int argc, char **argv) {
   p.add_option(file, "--file", "-f")->help("unused (reference compatibility)");
   p.add_option(iters, "--iters");
   p.add_option(fields, "--fields");
+  p.add_option(tileZ, "--tile-z")->help("planes marched per CTA (default 32)");
   p.add_flag(fp64, "--double");
   p.add_flag(star, "--star");
   p.add_flag(star, "--star19")->help("same as --star (torchrun's parser mistakes --star for an abbreviation of its --start-method)");
@@ -77,6 +78,7 @@ int main(int argc, char **argv) {
     opt.overlap = !noOverlap;
     opt.autoSchedule = !forceOverlap;
     opt.planFile = true;
+    if (tileZ > 0) opt.tileZ = tileZ;
     stencil::AstarothSim sim(x, y, z, opt);
     if (check) {
       /* every rank advances the whole (small) domain on the host from the device's own initial field and compares

@@ -515,8 +515,21 @@ __device__ __forceinline__ void astaroth_tile(unsigned char *smem, const TmaPara
 
   int s = 0;
   unsigned phase = 0;
+  /* a warp none of whose lanes has a cell to update (rows past the end of the subdomain: 323 rows leave 13 of the last
+     block's 16 rows empty) only keeps the ring's protocol going and leaves the fp64 pipe to the warps with work */
+  const bool warpIdle = !__any_sync(0xffffffffu, (mode[0] | mode[1]) != 0);
   for (int j = 0; j < nplanes; ++j) {
     tma::mbar_wait(&full[s], phase);
+    if (warpIdle) {
+      __syncwarp();
+      if (lane == 0) tma::mbar_arrive(&empty[s]);
+      if (threadIdx.x == 0 && j + kTStages - kTLag < nplanes) issue(j + kTStages - kTLag);
+      if (++s == kTStages) {
+        s = 0;
+        phase ^= 1u;
+      }
+      continue;
+    }
     const T *pl = reinterpret_cast<const T *>(smem + s * G::stageBytes);
     /* smem row q holds compute row t.y0 + q - 3; smem column kTMargin + k holds compute x = t.x0 + k */
     const T *base = pl + (r0 + kR) * G::boxX + kTMargin + xl * N;

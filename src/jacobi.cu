@@ -623,12 +623,28 @@ __device__ __forceinline__ void tma_tile(unsigned char *smem, const CUtensorMap 
       part[1].z = ((c1.w + c1.y) + north.z) + c0.z;
       part[1].w = ((e1 + c1.z) + north.w) + c0.w;
     };
-    int i = 0;
-    for (; i + 1 < nplanes; i += 2) {
-      plane(i, cmA);
-      plane(i + 1, cmB);
+    /* A warp none of whose lanes has a cell to update (rows past the last row of the subdomain or outside the region:
+       645 rows leave 11 of the last block's 16 rows empty) only keeps the ring's protocol going — wait, hand the slot
+       back, let thread 0 refill — and leaves the issue slots to the warps that have work. */
+    if (__any_sync(0xffffffffu, (mode[0] | mode[1]) != 0)) {
+      int i = 0;
+      for (; i + 1 < nplanes; i += 2) {
+        plane(i, cmA);
+        plane(i + 1, cmB);
+      }
+      if (i < nplanes) plane(i, cmA);
+    } else {
+      for (int i = 0; i < nplanes; ++i) {
+        mbar_wait(&full[s], phase);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[s]);
+        if (threadIdx.x == 0 && i + kTmaStages - kTmaLag < nplanes) issue(i + kTmaStages - kTmaLag);
+        if (++s == kTmaStages) {
+          s = 0;
+          phase ^= 1u;
+        }
+      }
     }
-    if (i < nplanes) plane(i, cmA);
   }
 
   if (FUSED && t.faces) {
