@@ -515,21 +515,8 @@ __device__ __forceinline__ void astaroth_tile(unsigned char *smem, const TmaPara
 
   int s = 0;
   unsigned phase = 0;
-  /* a warp none of whose lanes has a cell to update (rows past the end of the subdomain: 323 rows leave 13 of the last
-     block's 16 rows empty) only keeps the ring's protocol going and leaves the fp64 pipe to the warps with work */
-  const bool warpIdle = !__any_sync(0xffffffffu, (mode[0] | mode[1]) != 0);
   for (int j = 0; j < nplanes; ++j) {
     tma::mbar_wait(&full[s], phase);
-    if (warpIdle) {
-      __syncwarp();
-      if (lane == 0) tma::mbar_arrive(&empty[s]);
-      if (threadIdx.x == 0 && j + kTStages - kTLag < nplanes) issue(j + kTStages - kTLag);
-      if (++s == kTStages) {
-        s = 0;
-        phase ^= 1u;
-      }
-      continue;
-    }
     const T *pl = reinterpret_cast<const T *>(smem + s * G::stageBytes);
     /* smem row q holds compute row t.y0 + q - 3; smem column kTMargin + k holds compute x = t.x0 + k */
     const T *base = pl + (r0 + kR) * G::boxX + kTMargin + xl * N;
@@ -821,20 +808,6 @@ std::vector<ATile> make_atiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, i
         for (const auto &col : cols)
           if (col.second) emit(col.first, y0, narrowY, true);
     }
-  if (const char *e = std::getenv("STENCIL_ASTAROTH_TILE_ORDER")) {
-    /* experiments: 1 = field innermost (the same tile of every field back to back), 2 = z chunk outermost, then field */
-    const int mode = std::atoi(e);
-    if (mode == 1)
-      std::stable_sort(out.begin(), out.end(), [&](const ATile &a, const ATile &b) {
-        if (a.chunk != b.chunk) return a.chunk < b.chunk;
-        if (a.narrow != b.narrow) return a.narrow < b.narrow;
-        if (a.y0 != b.y0) return a.y0 < b.y0;
-        if (a.x0 != b.x0) return a.x0 < b.x0;
-        return a.field < b.field;
-      });
-    else if (mode == 2)
-      std::stable_sort(out.begin(), out.end(), [&](const ATile &a, const ATile &b) { return a.chunk < b.chunk; });
-  }
   if (flaggedFirst && flagMask) {
     const unsigned zbits = (1u << kZM) | (1u << kZP);
     auto prio = [&](const ATile &t) { return (t.dirs & flagMask & zbits) ? 0 : ((t.dirs & flagMask) ? 1 : 2); };
