@@ -89,10 +89,8 @@ struct Tile {
   int x0, y0;           // first cell / first row of the tile (compute coordinates)
   unsigned short tz;    // z index in units of tileZ
   unsigned char faces;  // bit f set when the tile owns cells on face f that must be pushed
-  unsigned char narrow; // bit 0 (TMA variant): 32 x 64 tile instead of 128 x 16; bit 1: the tile runs to the top of the
-                        // region (a last z layer of less than half a tile is merged into the one below it)
+  unsigned char narrow; // TMA variant: 1 = 32 x 64 tile, 0 = 128 x 16
 };
-constexpr unsigned char kTileNarrow = 1, kTileToTop = 2;
 
 struct JacobiParams {
   const float *src; // interior origin: compute cell (0,0,0) of curr
@@ -231,7 +229,7 @@ template <bool FUSED> __global__ void __launch_bounds__(kThreads) jacobi7_kernel
 
   const int x0 = t.x0 + lane * kVec;
   const int y = t.y0 + row;
-  const int z0 = max(int(t.tz) * P.tileZ, P.loz), z1 = (t.narrow & kTileToTop) ? P.hiz : min(int(t.tz + 1) * P.tileZ, P.hiz);
+  const int z0 = max(int(t.tz) * P.tileZ, P.loz), z1 = min(int(t.tz + 1) * P.tileZ, P.hiz);
   /* a warp is one row, so the row test is warp-uniform; the x test is per lane (partial tiles) */
   const bool rowActive = y >= P.loy && y < P.hiy;
   const bool laneActive = x0 < P.hix && x0 + kVec > P.lox;
@@ -457,7 +455,7 @@ __device__ __forceinline__ void tma_tile(unsigned char *smem, const CUtensorMap 
      the two proxies explicitly. */
   if (FUSED && (t.faces & P.flagMask) && threadIdx.x == 0) asm volatile("fence.proxy.async.global;" ::: "memory");
 
-  const int z0 = max(int(t.tz) * P.tileZ, P.loz), z1 = (t.narrow & kTileToTop) ? P.hiz : min(int(t.tz + 1) * P.tileZ, P.hiz);
+  const int z0 = max(int(t.tz) * P.tileZ, P.loz), z1 = min(int(t.tz + 1) * P.tileZ, P.hiz);
   const int nplanes = z1 > z0 ? z1 - z0 + 2 : 0; // input planes z0-1 .. z1
 
   /* There is no producer warp: a ninth warp would cost a tenth warp's worth of registers (warps are allocated in
@@ -672,7 +670,7 @@ __global__ void __launch_bounds__(kTmaThreads, MINB)
                        const __grid_constant__ JacobiParams P) {
   extern __shared__ __align__(128) unsigned char smem[];
   const Tile t = P.tiles[blockIdx.x];
-  if (t.narrow & kTileNarrow)
+  if (t.narrow)
     tma_tile<FUSED, Narrow>(smem, &tmapNarrow, &tmapSideNarrow, P, t);
   else
     tma_tile<FUSED, Wide>(smem, &tmapWide, &tmapSideWide, P, t);
@@ -821,32 +819,21 @@ std::vector<Tile> make_tiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int
       x += kTileX;
     }
   }
-  /* z layers: a last layer of less than half a tile (323 planes = 20 x 16 + 3) is merged into the one below it: its
-     tiles would pay the pipeline's prologue and the push epilogue for three planes of output */
-  const int64_t tzFirst = lo.z / tileZ;
-  int64_t tzLast = (hi.z - 1) / tileZ;
-  bool mergedTop = false;
-  if (tzLast > tzFirst && hi.z - tzLast * tileZ < (tileZ + 1) / 2) {
-    --tzLast;
-    mergedTop = true;
-  }
   auto emit = [&](int64_t tz, int64_t x0, int64_t y0, int64_t w, int64_t r, bool nar) {
-    const bool toTop = mergedTop && tz == tzLast;
-    const int64_t zhi = toTop ? hi.z : std::min<int64_t>((tz + 1) * tileZ, hi.z);
     unsigned f = 0;
     if (x0 == 0) f |= 1u << XM;
     if (x0 <= sz.x - 1 && sz.x - 1 < x0 + w) f |= 1u << XP;
     if (y0 == 0) f |= 1u << YM;
     if (y0 <= sz.y - 1 && sz.y - 1 < y0 + r) f |= 1u << YP;
     if (tz == 0) f |= 1u << ZM;
-    if (tz * tileZ <= sz.z - 1 && sz.z - 1 < zhi) f |= 1u << ZP;
+    if (tz * tileZ <= sz.z - 1 && sz.z - 1 < (tz + 1) * tileZ) f |= 1u << ZP;
     f &= faceMask;
     if (nFace)
       for (int k = 0; k < 6; ++k)
         if ((f & countMask) >> k & 1u) ++nFace[k];
-    out.push_back(Tile{int(x0), int(y0), (unsigned short)tz, (unsigned char)f, (unsigned char)((nar ? kTileNarrow : 0) | (toTop ? kTileToTop : 0))});
+    out.push_back(Tile{int(x0), int(y0), (unsigned short)tz, (unsigned char)f, (unsigned char)(nar ? 1 : 0)});
   };
-  for (int64_t tz = tzFirst; tz <= tzLast; ++tz) {
+  for (int64_t tz = lo.z / tileZ; tz * tileZ < hi.z; ++tz) {
     /* wide columns row block by row block, then the narrow columns (their row blocks are four times as tall) */
     for (int64_t y0 = lo.y / rows * rows; y0 < hi.y; y0 += rows)
       for (const auto &c : cols)
@@ -1025,7 +1012,7 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
     d.tilesAll = upload(all);
     d.nAll = unsigned(all.size());
     auto note_narrow = [&d](const std::vector<Tile> &v) {
-      for (const Tile &t : v) d.anyNarrow = d.anyNarrow || (t.narrow & kTileNarrow);
+      for (const Tile &t : v) d.anyNarrow = d.anyNarrow || t.narrow;
     };
     note_narrow(all);
     /* every CTA starts by reading its table entry and nothing can be issued before it arrives: keep the table in L2
