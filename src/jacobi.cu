@@ -843,8 +843,18 @@ std::vector<Tile> make_tiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int
         if (c.second) emit(tz, c.first, y0, Narrow::kW, Narrow::kR, true);
   }
   if (flaggedFirst && countMask) {
+    /* ... and the cheap tiles last: a kernel ends with a partial wave of tiles, and what fills it best are tiles that
+       take a fraction of a full one — those whose rows are mostly past the last row of the subdomain (their idle warps
+       skip the arithmetic) and those of a short top layer. In natural order the short top layer played that part; with
+       the z faces moved to the front the tail was all full tiles (2 GPUs, 645 x 645 x 323: 0.2272 against 0.2223 ms). */
     const unsigned zbits = (1u << ZM) | (1u << ZP);
-    auto prio = [&](const Tile &t) { return (t.faces & countMask & zbits) ? 0 : ((t.faces & countMask) ? 1 : 2); };
+    auto cheap = [&](const Tile &t) {
+      const int64_t r = (t.narrow ? Narrow::kR : rows), z0 = std::max<int64_t>(int64_t(t.tz) * tileZ, lo.z),
+                    z1 = std::min<int64_t>(int64_t(t.tz + 1) * tileZ, hi.z);
+      const int64_t activeRows = std::min<int64_t>(t.y0 + r, hi.y) - std::max<int64_t>(t.y0, lo.y);
+      return 2 * activeRows <= r || 2 * (z1 - z0) <= tileZ;
+    };
+    auto prio = [&](const Tile &t) { return (t.faces & countMask & zbits) ? 0 : ((t.faces & countMask) ? 1 : (cheap(t) ? 3 : 2)); };
     std::stable_sort(out.begin(), out.end(), [&](const Tile &a, const Tile &b) { return prio(a) < prio(b); });
   }
   return out;
