@@ -249,7 +249,7 @@ template <typename T> constexpr int tma_smem_bytes() {
    flag and one completion counter PER DIRECTION, exactly as the fused Jacobi kernel does per face (src/jacobi.cu):
    a tile waits for the flags of the directions it touches before reading halos, counts itself done on them after a
    GPU-scope fence, and whoever completes a direction raises that neighbour's flag behind one system-scope fence. */
-constexpr int kDirs = 8;
+constexpr int kDirs = 8, kPushRows = 4;
 enum PushDir { kYM = 0, kYP = 1, kZM = 2, kZP = 3, kYMZM = 4, kYMZP = 5, kYPZM = 6, kYPZP = 7 };
 constexpr int kFusedFlagBase = 64; // word offset of the fused-iteration flags inside a control block (as in jacobi.cu)
 
@@ -302,20 +302,20 @@ __device__ __noinline__ void push_tile_dirs(const PushParams<T> &Q, int field, u
     if (ny <= 0 || zb <= za) continue;
     T *nb = Q.nb[d][field];
     const long long npx = Q.nbPitchX[d], npxy = Q.nbPitchXY[d];
-    /* two rows per pass, every load of both rows issued before the first store: the loop is bound by the L2 round trip of
-       a row, not by bytes */
+    /* kPushRows rows per warp and pass, every load of all of them issued before the first store: the loop is bound by
+       the L2 round trip of a row, not by bytes */
     const int xe = lane < kR ? lane : Q.sx - 2 * kR + lane;          // x-wrap cell this lane may carry (lanes 0..5)
     const bool ext = lane < 2 * kR && xe >= xlo && xe < xhi;         // ... if this tile owns it
     const int xeDst = lane < kR ? xe + Q.sx : xe - Q.sx;
-    for (int r = warp; r < rows; r += 2 * nwarps) {
-      const T *src[2];
-      T *dst[2];
-      bool on[2], vec[2];
-      V v[2];
-      T e[2], tail[2][N];
+    for (int r = warp; r < rows; r += kPushRows * nwarps) {
+      const T *src[kPushRows];
+      T *dst[kPushRows];
+      bool on[kPushRows], vec[kPushRows];
+      V v[kPushRows];
+      T e[kPushRows], tail[kPushRows][N];
       const int x = xlo + lane * N;
 #pragma unroll
-      for (int k = 0; k < 2; ++k) {
+      for (int k = 0; k < kPushRows; ++k) {
         const int rr = r + k * nwarps;
         on[k] = rr < rows;
         const int z = za + (on[k] ? rr : r) / ny, y = ya + (on[k] ? rr : r) % ny;
@@ -339,7 +339,7 @@ __device__ __noinline__ void push_tile_dirs(const PushParams<T> &Q, int field, u
         }
       }
 #pragma unroll
-      for (int k = 0; k < 2; ++k) {
+      for (int k = 0; k < kPushRows; ++k) {
         if (!on[k]) continue;
         if (vec[k] && x + N <= xhi) {
           *reinterpret_cast<V *>(dst[k] + x) = v[k];
@@ -714,9 +714,11 @@ struct AstarothSim::Impl {
     ATile *dev = nullptr;
     unsigned n = 0;
     bool hasNarrow = false; // decides how much shared memory a launch asks for
+    int tileZ = 0;          // planes per z chunk of THIS table (balanced over the region's planes, see balanced_tile_z)
   };
-  static Tiles upload(const std::vector<ATile> &t) {
+  static Tiles upload(const std::vector<ATile> &t, int tileZ) {
     Tiles r;
+    r.tileZ = tileZ;
     r.n = unsigned(t.size());
     for (const ATile &a : t) r.hasNarrow = r.hasNarrow || a.narrow;
     if (t.empty()) return r;
@@ -764,6 +766,16 @@ const Dim3 kPushDir[kDirs] = {Dim3(0, -1, 0), Dim3(0, 1, 0), Dim3(0, 0, -1), Dim
    to such a neighbour in direction d. Order: field-major, then (z, y, x), which keeps the tiles that share halo rows
    and planes resident together; tiles that push to another GPU come first (z directions, then the others) so that
    every direction is announced early in the kernel — see make_tiles() in src/jacobi.cu for the reasoning. */
+/* Planes per z chunk for a region `planes` deep: as many chunks as the requested depth gives, all of (nearly) the same
+   depth. 162 planes at depth 32 are 6 chunks of 27 instead of 5 x 32 + 2: the 2-plane chunk would load 8 planes for 2,
+   and the three planes of the top face would straddle two chunks, which makes BOTH of them hand-shake with the
+   neighbour GPU (half of all tiles instead of a third, each paying the push epilogue). */
+int balanced_tile_z(int64_t planes, int tileZ) {
+  if (planes <= 0) return tileZ;
+  const int64_t chunks = (planes + tileZ - 1) / tileZ;
+  return int(std::max<int64_t>(kR, (planes + chunks - 1) / chunks));
+}
+
 std::vector<ATile> make_atiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int fields, int tileZ, int vecN, unsigned dirMask, unsigned flagMask,
                                unsigned *nDir, bool narrowOk, bool flaggedFirst, bool zigzag) {
   std::vector<ATile> out;
@@ -941,13 +953,21 @@ AstarothSim::AstarothSim(size_t x, size_t y, size_t z, const Options &opt) : opt
       /* tile tables: the whole region carries the push directions (filled in by setup_fused_faces when fused) */
       const Dim3 sz = ld.size(), org = ld.origin();
       if (!impl_->tilesAll[di].dev)
-        impl_->tilesAll[di] = Impl::upload(make_atiles(Dim3(0, 0, 0), sz, sz, opt_.fields, opt_.tileZ, vecN, 0, 0, nullptr, opt_.narrowTiles, false, opt_.zigzag));
+      {
+        const int tz = balanced_tile_z(sz.z, opt_.tileZ);
+        impl_->tilesAll[di] = Impl::upload(make_atiles(Dim3(0, 0, 0), sz, sz, opt_.fields, tz, vecN, 0, 0, nullptr, opt_.narrowTiles, false, opt_.zigzag), tz);
+      }
       tma::keep_in_l2(impl_->streams[di], impl_->tilesAll[di].dev, size_t(impl_->tilesAll[di].n) * sizeof(ATile));
-      impl_->tilesInterior[di] = Impl::upload(make_atiles(impl_->interior[di].lo - org, impl_->interior[di].hi - org, sz, opt_.fields, opt_.tileZ,
-                                                          vecN, 0, 0, nullptr, opt_.narrowTiles, false, opt_.zigzag));
-      for (const Rect3 &r : impl_->exterior[di])
+      {
+        const int tz = balanced_tile_z(impl_->interior[di].extent().z, opt_.tileZ);
+        impl_->tilesInterior[di] = Impl::upload(make_atiles(impl_->interior[di].lo - org, impl_->interior[di].hi - org, sz, opt_.fields, tz, vecN, 0, 0,
+                                                            nullptr, opt_.narrowTiles, false, opt_.zigzag), tz);
+      }
+      for (const Rect3 &r : impl_->exterior[di]) {
+        const int tz = balanced_tile_z(r.extent().z, opt_.tileZ);
         impl_->tilesExterior[di].push_back(
-            Impl::upload(make_atiles(r.lo - org, r.hi - org, sz, opt_.fields, opt_.tileZ, vecN, 0, 0, nullptr, opt_.narrowTiles, false, opt_.zigzag)));
+            Impl::upload(make_atiles(r.lo - org, r.hi - org, sz, opt_.fields, tz, vecN, 0, 0, nullptr, opt_.narrowTiles, false, opt_.zigzag), tz));
+      }
     }
   }
   init();
@@ -994,8 +1014,9 @@ void AstarothSim::setup_fused_faces() {
     p.sameDevDeps.assign(deps.begin(), deps.end());
     /* the tile table of the whole-region launch decides which CTAs take part in which hand-shake */
     const Dim3 sz = ld.size();
-    impl_->tilesAll[di] = Impl::upload(make_atiles(Dim3(0, 0, 0), sz, sz, opt_.fields, opt_.tileZ, vecN, p.dirMask, p.flagMask, p.nDir,
-                                                   opt_.narrowTiles, opt_.flaggedFirst, opt_.zigzag));
+    const int tz = balanced_tile_z(sz.z, opt_.tileZ);
+    impl_->tilesAll[di] = Impl::upload(make_atiles(Dim3(0, 0, 0), sz, sz, opt_.fields, tz, vecN, p.dirMask, p.flagMask, p.nDir, opt_.narrowTiles,
+                                                   opt_.flaggedFirst, opt_.zigzag), tz);
     CUDA_RUNTIME(cudaMalloc(&p.done, kDirs * sizeof(unsigned)));
     CUDA_RUNTIME(cudaMemset(p.done, 0, kDirs * sizeof(unsigned)));
     for (int parity = 0; parity < 2; ++parity)
@@ -1157,10 +1178,10 @@ void AstarothSim::step() {
       const void *pushDev = fused ? impl_->push[di].dev[doms[di].parity()] : nullptr;
       const unsigned pushFlags = fused ? impl_->push[di].flagMask : 0u;
       if (opt_.fp64)
-        launch_region_tma<double>(cross, doms[di], opt_.fields, maps, tiles->dev, tiles->n, tiles->hasNarrow, reg, opt_.tileZ, opt_.dt, opt_.crossWeight, impl_->streams[di],
+        launch_region_tma<double>(cross, doms[di], opt_.fields, maps, tiles->dev, tiles->n, tiles->hasNarrow, reg, tiles->tileZ, opt_.dt, opt_.crossWeight, impl_->streams[di],
                                   whole && impl_->fusedX, pushDev, pushFlags, impl_->iter);
       else
-        launch_region_tma<float>(cross, doms[di], opt_.fields, maps, tiles->dev, tiles->n, tiles->hasNarrow, reg, opt_.tileZ, float(opt_.dt), float(opt_.crossWeight),
+        launch_region_tma<float>(cross, doms[di], opt_.fields, maps, tiles->dev, tiles->n, tiles->hasNarrow, reg, tiles->tileZ, float(opt_.dt), float(opt_.crossWeight),
                                  impl_->streams[di], whole && impl_->fusedX, pushDev, pushFlags, impl_->iter);
       ++launches_;
       return;
