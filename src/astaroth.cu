@@ -820,9 +820,15 @@ std::vector<ATile> make_atiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, i
         for (const auto &col : cols)
           if (col.second) emit(col.first, y0, narrowY, true);
     }
-  if (flaggedFirst && flagMask) {
+  if (flaggedFirst) {
+    /* tiles that push to another GPU first; tiles whose rows are mostly past the last row of the subdomain last (they
+       take a fraction of a full tile and fill the kernel's last partial wave: see make_tiles() in src/jacobi.cu) */
     const unsigned zbits = (1u << kZM) | (1u << kZP);
-    auto prio = [&](const ATile &t) { return (t.dirs & flagMask & zbits) ? 0 : ((t.dirs & flagMask) ? 1 : 2); };
+    auto cheap = [&](const ATile &t) {
+      const int64_t r = t.narrow ? narrowY : kTRows;
+      return 2 * (std::min<int64_t>(t.y0 + r, hi.y) - std::max<int64_t>(t.y0, lo.y)) <= r;
+    };
+    auto prio = [&](const ATile &t) { return (t.dirs & flagMask & zbits) ? 0 : ((t.dirs & flagMask) ? 1 : (cheap(t) ? 3 : 2)); };
     std::stable_sort(out.begin(), out.end(), [&](const ATile &a, const ATile &b) { return prio(a) < prio(b); });
   }
   return out;
@@ -955,7 +961,7 @@ AstarothSim::AstarothSim(size_t x, size_t y, size_t z, const Options &opt) : opt
       if (!impl_->tilesAll[di].dev)
       {
         const int tz = balanced_tile_z(sz.z, opt_.tileZ);
-        impl_->tilesAll[di] = Impl::upload(make_atiles(Dim3(0, 0, 0), sz, sz, opt_.fields, tz, vecN, 0, 0, nullptr, opt_.narrowTiles, false, opt_.zigzag), tz);
+        impl_->tilesAll[di] = Impl::upload(make_atiles(Dim3(0, 0, 0), sz, sz, opt_.fields, tz, vecN, 0, 0, nullptr, opt_.narrowTiles, opt_.flaggedFirst, opt_.zigzag), tz);
       }
       tma::keep_in_l2(impl_->streams[di], impl_->tilesAll[di].dev, size_t(impl_->tilesAll[di].n) * sizeof(ATile));
       {
