@@ -3,19 +3,18 @@
 mkdir -p gpurun_out
 cd /root/repo
 export STENCIL_LOG_LEVEL=1
-O=gpurun_out/exp.txt
+N=${N:-4}
+O=gpurun_out/exp_n$N.txt
 : > $O
-A=./build/bin/astaroth-sim
-run() { echo "## $TAG $*" >> $O; timeout 300 "$@" 2>/dev/null | grep -E "device|astaroth" >> $O; }
-timeout 900 ./build/bin/test_cuda "[astaroth]" > "gpurun_out/test_astaroth.log" 2>&1; echo "test rc=$? $(tail -1 gpurun_out/test_astaroth.log)" >> $O
-C="--fields 8 --double --star19 --iters 20"
-for cfg in "--x 256 --y 256 --z 256" "--x 323 --y 323 --z 162" "--x 406 --y 203 --z 203" "--x 512 --y 256 --z 128"; do
-  TAG=cheaplast run $A $cfg $C
-  TAG=natural STENCIL_ASTAROTH_NATURAL_ORDER=1 run $A $cfg $C
-done
-timeout 900 python bench.py --steps 30 --warmup 5 > gpurun_out/bench1.json 2> gpurun_out/bench1.err; echo "bench rc=$?" >> $O
-timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> $O
-cat $O; tail -3 gpurun_out/pytest_gpu.log; python3 -c "
+B=/root/repo/build/bin
+TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
+run() { echo "## $TAG $*" >> $O; ( cd /tmp && timeout 300 "$@" 2>/dev/null | grep -E "device|jacobi3d,|astaroth|verify" ) >> $O; }
+timeout 600 $B/test_cuda "[multigpu]" > gpurun_out/test_multigpu_n$N.log 2>&1; echo "test_multigpu rc=$? $(tail -1 gpurun_out/test_multigpu_n$N.log)" >> $O
+TAG=1proc run $B/jacobi3d 512 512 512 -n 30 --tile-z 16 --device-time
+TAG=nproc run $TR --master-port 29611 --no-python $B/jacobi3d 512 512 512 -n 30 --tile-z 16 --device-time
+run $TR --master-port 29603 --no-python $B/astaroth-sim --x 96 --y 80 --z 72 --fields 3 --double --cross --iters 9 --check
+timeout 900 $TR --master-port 29621 bench.py --gpus $N --steps 30 --warmup 5 > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err; echo "bench rc=$?" >> $O
+cat $O; python3 -c "
 import json
-d=json.loads(open('gpurun_out/bench1.json').read().strip().splitlines()[-1])
+d=json.loads(open('gpurun_out/bench_n$N.json').read().strip().splitlines()[-1])
 print(d['value'], d['ms_per_step'], d['verified'], d['exchange_us_per_iter'], d['astaroth'], d['e2e']['value'])"
