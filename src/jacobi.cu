@@ -448,6 +448,11 @@ __device__ __forceinline__ void tma_tile(unsigned char *smem, const CUtensorMap 
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
+  /* Programmatic dependent launch (Jacobi3D::Options::pdl): this grid may have been started while the previous
+     iteration's last CTAs were still running — its CTAs take the slots those free, set up their barriers and fetch their
+     table entry meanwhile — and everything that touches the fields waits here for that grid to complete. A no-op in a
+     launch without the attribute. */
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   if (FUSED && (t.faces & P.flagMask)) wait_faces(P, t.faces & P.flagMask);
   __syncthreads();
   /* The halo cells this tile is about to fetch were written by another GPU with ordinary (generic-proxy) stores and
@@ -669,6 +674,7 @@ __global__ void __launch_bounds__(kTmaThreads, MINB)
                        const __grid_constant__ CUtensorMap tmapSideWide, const __grid_constant__ CUtensorMap tmapSideNarrow,
                        const __grid_constant__ JacobiParams P) {
   extern __shared__ __align__(128) unsigned char smem[];
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); // the next iteration may start filling the slots this grid frees
   const Tile t = P.tiles[blockIdx.x];
   if (t.narrow)
     tma_tile<FUSED, Narrow>(smem, &tmapNarrow, &tmapSideNarrow, P, t);
@@ -918,6 +924,7 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
   if (opt_.useTma && opt_.tileZ > kMaxTileZ) opt_.tileZ = kMaxTileZ;
   if (std::getenv("STENCIL_JACOBI_NATURAL_ORDER")) opt_.flaggedFirst = false;
   if (std::getenv("STENCIL_JACOBI_NO_NARROW")) opt_.narrowTiles = false;
+  if (const char *e = std::getenv("STENCIL_JACOBI_PDL")) opt_.pdl = std::atoi(e) != 0;
   if (const char *e = std::getenv("STENCIL_LAUNCH_THREADS")) opt_.launchThreads = std::atoi(e) != 0;
   dd_.reset(comm ? new DistributedDomain(x, y, z, *comm) : new DistributedDomain(x, y, z));
   if (!opt_.gpus.empty()) dd_->set_gpus(opt_.gpus);
@@ -1182,7 +1189,18 @@ void Jacobi3D::step() {
       auto *k = fused ? (mb == 3 ? &jacobi7_tma_kernel<true, 3> : &jacobi7_tma_kernel<true, 2>)
                       : (mb == 3 ? &jacobi7_tma_kernel<false, 3> : &jacobi7_tma_kernel<false, 2>);
       const int pa = ld.parity();
-      (*k)<<<n, kTmaThreads, d.anyNarrow ? kTmaSmemBytes : Wide::kSmemBytes, d.stream>>>(d.tmap[pa], d.tmapNarrow[pa], d.tmapSide[pa], d.tmapSideNarrow[pa], P);
+      cudaLaunchConfig_t cfg;
+      std::memset(&cfg, 0, sizeof(cfg));
+      cfg.gridDim = dim3(n, 1, 1);
+      cfg.blockDim = dim3(kTmaThreads, 1, 1);
+      cfg.dynamicSmemBytes = size_t(d.anyNarrow ? kTmaSmemBytes : Wide::kSmemBytes);
+      cfg.stream = d.stream;
+      cudaLaunchAttribute attr;
+      attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      attr.val.programmaticStreamSerializationAllowed = 1;
+      cfg.attrs = &attr;
+      cfg.numAttrs = opt_.pdl ? 1 : 0;
+      CUDA_RUNTIME(cudaLaunchKernelEx(&cfg, *k, d.tmap[pa], d.tmapNarrow[pa], d.tmapSide[pa], d.tmapSideNarrow[pa], P));
     } else if (fused) {
       jacobi7_kernel<true><<<n, kThreads, 0, d.stream>>>(P);
     } else {

@@ -3,18 +3,21 @@
 mkdir -p gpurun_out
 cd /root/repo
 export STENCIL_LOG_LEVEL=1
-N=${N:-4}
-O=gpurun_out/exp_n$N.txt
+O=gpurun_out/exp.txt
 : > $O
-B=/root/repo/build/bin
-TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
-run() { echo "## $TAG $*" >> $O; ( cd /tmp && timeout 300 "$@" 2>/dev/null | grep -E "device|jacobi3d,|astaroth|verify" ) >> $O; }
-timeout 600 $B/test_cuda "[multigpu]" > gpurun_out/test_multigpu_n$N.log 2>&1; echo "test_multigpu rc=$? $(tail -1 gpurun_out/test_multigpu_n$N.log)" >> $O
-TAG=1proc run $B/jacobi3d 512 512 512 -n 30 --tile-z 16 --device-time
-TAG=nproc run $TR --master-port 29611 --no-python $B/jacobi3d 512 512 512 -n 30 --tile-z 16 --device-time
-run $TR --master-port 29603 --no-python $B/astaroth-sim --x 96 --y 80 --z 72 --fields 3 --double --cross --iters 9 --check
-timeout 900 $TR --master-port 29621 bench.py --gpus $N --steps 30 --warmup 5 > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err; echo "bench rc=$?" >> $O
-cat $O; python3 -c "
-import json
-d=json.loads(open('gpurun_out/bench_n$N.json').read().strip().splitlines()[-1])
-print(d['value'], d['ms_per_step'], d['verified'], d['exchange_us_per_iter'], d['astaroth'], d['e2e']['value'])"
+J=./build/bin/jacobi3d
+run() { echo "## $TAG $*" >> $O; timeout 300 "$@" 2>/dev/null | grep -E "device|verify" >> $O; }
+timeout 900 ./build/bin/test_cuda "[jacobi]" > "gpurun_out/test_jacobi.log" 2>&1; echo "test rc=$? $(tail -1 gpurun_out/test_jacobi.log)" >> $O
+STENCIL_JACOBI_PDL=1 timeout 900 ./build/bin/test_cuda "[jacobi]" > "gpurun_out/test_jacobi_pdl.log" 2>&1; echo "test pdl rc=$? $(tail -1 gpurun_out/test_jacobi_pdl.log)" >> $O
+for rep in 1 2; do
+for cfg in "512 512 512" "645 645 323"; do
+  TAG=nopdl run $J $cfg --exact-size -n 40 --tile-z 16 --device-time
+  TAG=pdl STENCIL_JACOBI_PDL=1 run $J $cfg --exact-size -n 40 --tile-z 16 --device-time
+done
+done
+TAG=pdl STENCIL_JACOBI_PDL=1 run $J 300 200 100 --exact-size --verify 30 --tile-z 16 --delay-us 50
+TAG=pdl-nooverlap STENCIL_JACOBI_PDL=1 run $J 512 512 512 --exact-size -n 30 --tile-z 16 --device-time --no-overlap
+TAG=nopdl-nooverlap run $J 512 512 512 --exact-size -n 30 --tile-z 16 --device-time --no-overlap
+timeout 300 python bench.py --steps 30 --warmup 5 --random-init --skip-exchange --skip-astaroth > gpurun_out/bench1_random.json 2> gpurun_out/bench1_random.err; echo "bench random rc=$?" >> $O
+timeout 120 python -c "import __graft_entry__ as g; g.smoke()" >> $O 2>&1
+cat $O; cut -c1-400 gpurun_out/bench1_random.json; grep -h -B2 -A8 FAIL gpurun_out/test_*.log | head -30
