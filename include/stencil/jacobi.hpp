@@ -35,7 +35,8 @@ public:
     bool useTma = true;    // TMA + mbarrier pipelined kernel (false: plain LDG variant, kept for comparison)
     bool flaggedFirst = true; // schedule the tiles that push to ANOTHER GPU first, so each face is announced early
     bool narrowTiles = true;  // cover the remainder of rows that are not a multiple of 128 cells with 32 x 64 tiles
-    bool pdl = false;         // programmatic dependent launch between consecutive kernels of a stream (STENCIL_JACOBI_PDL)
+    bool pdl = true;          // programmatic dependent launch between consecutive kernels of a stream: the next iteration's
+                              // CTAs take the slots the last wave frees and set up while it drains (STENCIL_JACOBI_PDL=0: off)
     bool planFile = false;
     bool launchThreads = true; // several local GPUs: enqueue each GPU's work from its own host thread (STENCIL_LAUNCH_THREADS=0 turns it off)
   };

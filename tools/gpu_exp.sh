@@ -5,19 +5,19 @@ cd /root/repo
 export STENCIL_LOG_LEVEL=1
 O=gpurun_out/exp.txt
 : > $O
-J=./build/bin/jacobi3d
-run() { echo "## $TAG $*" >> $O; timeout 300 "$@" 2>/dev/null | grep -E "device|verify" >> $O; }
-timeout 900 ./build/bin/test_cuda "[jacobi]" > "gpurun_out/test_jacobi.log" 2>&1; echo "test rc=$? $(tail -1 gpurun_out/test_jacobi.log)" >> $O
-STENCIL_JACOBI_PDL=1 timeout 900 ./build/bin/test_cuda "[jacobi]" > "gpurun_out/test_jacobi_pdl.log" 2>&1; echo "test pdl rc=$? $(tail -1 gpurun_out/test_jacobi_pdl.log)" >> $O
-for rep in 1 2; do
-for cfg in "512 512 512" "645 645 323"; do
-  TAG=nopdl run $J $cfg --exact-size -n 40 --tile-z 16 --device-time
-  TAG=pdl STENCIL_JACOBI_PDL=1 run $J $cfg --exact-size -n 40 --tile-z 16 --device-time
-done
-done
-TAG=pdl STENCIL_JACOBI_PDL=1 run $J 300 200 100 --exact-size --verify 30 --tile-z 16 --delay-us 50
-TAG=pdl-nooverlap STENCIL_JACOBI_PDL=1 run $J 512 512 512 --exact-size -n 30 --tile-z 16 --device-time --no-overlap
-TAG=nopdl-nooverlap run $J 512 512 512 --exact-size -n 30 --tile-z 16 --device-time --no-overlap
-timeout 300 python bench.py --steps 30 --warmup 5 --random-init --skip-exchange --skip-astaroth > gpurun_out/bench1_random.json 2> gpurun_out/bench1_random.err; echo "bench random rc=$?" >> $O
-timeout 120 python -c "import __graft_entry__ as g; g.smoke()" >> $O 2>&1
-cat $O; cut -c1-400 gpurun_out/bench1_random.json; grep -h -B2 -A8 FAIL gpurun_out/test_*.log | head -30
+N=2
+B=/root/repo/build/bin
+TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
+run() { echo "## $TAG $*" >> $O; ( cd /tmp && timeout 300 "$@" 2>/dev/null | grep -E "device|astaroth|verify" ) >> $O; }
+timeout 600 $B/test_cuda "[multigpu]" > gpurun_out/test_multigpu_n2.log 2>&1; echo "test_multigpu rc=$? $(tail -1 gpurun_out/test_multigpu_n2.log)" >> $O
+run $TR --master-port 29601 --no-python $B/jacobi3d 512 512 512 --verify 50 --tile-z 16 --delay-us 300
+run $B/jacobi3d 512 512 512 --verify 50 --tile-z 16 --delay-us 300
+TAG=pdl run $TR --master-port 29611 --no-python $B/jacobi3d 512 512 512 -n 40 --tile-z 16 --device-time
+TAG=nopdl STENCIL_JACOBI_PDL=0 run $TR --master-port 29612 --no-python $B/jacobi3d 512 512 512 -n 40 --tile-z 16 --device-time
+TAG=pdl run $TR --master-port 29613 --no-python $B/jacobi3d 512 512 512 -n 40 --tile-z 16 --device-time
+CUDA_VISIBLE_DEVICES=0 timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$? $(tail -1 gpurun_out/pytest_gpu.log)" >> $O
+timeout 900 $TR --master-port 29621 bench.py --gpus $N --steps 30 --warmup 5 > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err; echo "bench rc=$?" >> $O
+cat $O; python3 -c "
+import json
+d=json.loads(open('gpurun_out/bench_n2.json').read().strip().splitlines()[-1])
+print(d['value'], d['ms_per_step'], d['verified'], d['exchange_us_per_iter'], d['astaroth']['ms_per_step_device'])"
