@@ -98,6 +98,7 @@ class CopyPlan {
   unsigned *dDone_ = nullptr; // CTA completion counter used by the signalling variant
   int dev_ = -1;
   std::vector<unsigned char> optional_; // per segment
+  std::vector<unsigned char> remote_;   // per segment: the destination is on another GPU
   unsigned nRequiredChunks_ = 0;
 
   void upload();

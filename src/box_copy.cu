@@ -372,6 +372,7 @@ void CopyPlan::swap(CopyPlan &o) noexcept {
   std::swap(dDone_, o.dDone_);
   std::swap(dev_, o.dev_);
   optional_.swap(o.optional_);
+  remote_.swap(o.remote_);
   std::swap(nRequiredChunks_, o.nRequiredChunks_);
 }
 
@@ -446,6 +447,7 @@ void CopyPlan::add(const BoxView &src, const Dim3 &srcPos, const BoxView &dst, c
   const CopySeg s = make_seg(src, srcPos, dst, dstPos, ext);
   segs_.push_back(s);
   optional_.push_back(0);
+  remote_.push_back(dst.acrossLink ? 1 : 0);
   bytes_ += size_t(s.rowBytes) * s.ny * s.nz;
 }
 
@@ -467,19 +469,35 @@ void CopyPlan::build_chunks(size_t chunkBytes) {
   /* chunks of the optional segments go last, so that leaving them out is a shorter chunk table */
   for (int pass = 0; pass < 2; ++pass) {
   if (pass == 1) nRequiredChunks_ = unsigned(chunks_.size());
+  /* Chunks whose destination is another GPU are spread evenly among the local ones: a launch walks the table front to
+     back, and the two kinds are bound by different things — NVLink for the first, the DRAM's page-open rate for thin
+     local rows — so each should be in flight during the whole launch instead of one after the other. */
+  std::vector<CopyChunk> link, local;
   for (size_t si = 0; si < segs_.size(); ++si) {
     if (int(optional_[si]) != pass) continue;
     const CopySeg &s = segs_[si];
+    std::vector<CopyChunk> &out = remote_[si] ? link : local;
     /* thin rows cost a sector each way whatever their length: count at least 32 bytes per row when sizing chunks */
     const unsigned per = unsigned(std::min<size_t>(32768, std::max<size_t>(1, chunkBytes / std::max(32u, s.rowBytes))));
     if (s.ny >= per) {
       for (unsigned z = 0; z < s.nz; ++z)
         for (unsigned y = 0; y < s.ny; y += per)
-          chunks_.push_back(CopyChunk{unsigned(si), z, y, (unsigned short)std::min(per, s.ny - y), (unsigned short)1});
+          out.push_back(CopyChunk{unsigned(si), z, y, (unsigned short)std::min(per, s.ny - y), (unsigned short)1});
     } else { // few rows per plane (edges, corners): a chunk takes several whole planes
       const unsigned planesPer = std::max(1u, per / s.ny);
       for (unsigned z = 0; z < s.nz; z += planesPer)
-        chunks_.push_back(CopyChunk{unsigned(si), z, 0, (unsigned short)s.ny, (unsigned short)std::min(planesPer, s.nz - z)});
+        out.push_back(CopyChunk{unsigned(si), z, 0, (unsigned short)s.ny, (unsigned short)std::min(planesPer, s.nz - z)});
+    }
+  }
+  {
+    size_t a = 0, b = 0;
+    const size_t na = link.size(), nb = local.size();
+    while (a < na || b < nb) {
+      /* the kind that is further behind its share goes next */
+      if (b >= nb || (a < na && a * nb <= b * na))
+        chunks_.push_back(link[a++]);
+      else
+        chunks_.push_back(local[b++]);
     }
   }
   }

@@ -222,9 +222,15 @@ class Exchanger {
 
   /* view of quantity qi of subdomain `w` as seen from device myDev */
   BoxView view_of(const Where &w, size_t qi, int myDev) {
-    if (w.rank == dd_.rank_) return dd_.domains_[size_t(w.dom)].view(qi);
-    RemoteSlab &rs = map_remote(myDev, w);
-    return rs.shadow->view_at(qi, static_cast<char *>(rs.ptr));
+    BoxView v;
+    if (w.rank == dd_.rank_) {
+      v = dd_.domains_[size_t(w.dom)].view(qi);
+    } else {
+      RemoteSlab &rs = map_remote(myDev, w);
+      v = rs.shadow->view_at(qi, static_cast<char *>(rs.ptr));
+    }
+    v.acrossLink = w.dev != myDev; // lets the plan spread the NVLink chunks over the whole launch
+    return v;
   }
 
   /* dense landing box for the halo on side `side` of quantity qi of subdomain w, as addressed from device myDev */

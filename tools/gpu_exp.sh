@@ -8,16 +8,11 @@ O=gpurun_out/exp.txt
 N=2
 B=/root/repo/build/bin
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
-run() { echo "## $TAG $*" >> $O; ( cd /tmp && timeout 300 "$@" 2>/dev/null | grep -E "device|astaroth|verify" ) >> $O; }
+run() { echo "## $TAG $*" >> $O; ( cd /tmp && timeout 300 "$@" 2>/dev/null | grep -E "device|weak" ) >> $O; }
+timeout 600 $B/test_cuda "[exchange]" > gpurun_out/test_exchange_n2.log 2>&1; echo "test_exchange rc=$? $(tail -1 gpurun_out/test_exchange_n2.log)" >> $O
 timeout 600 $B/test_cuda "[multigpu]" > gpurun_out/test_multigpu_n2.log 2>&1; echo "test_multigpu rc=$? $(tail -1 gpurun_out/test_multigpu_n2.log)" >> $O
-run $TR --master-port 29601 --no-python $B/jacobi3d 512 512 512 --verify 50 --tile-z 16 --delay-us 300
-run $B/jacobi3d 512 512 512 --verify 50 --tile-z 16 --delay-us 300
-TAG=pdl run $TR --master-port 29611 --no-python $B/jacobi3d 512 512 512 -n 40 --tile-z 16 --device-time
-TAG=nopdl STENCIL_JACOBI_PDL=0 run $TR --master-port 29612 --no-python $B/jacobi3d 512 512 512 -n 40 --tile-z 16 --device-time
-TAG=pdl run $TR --master-port 29613 --no-python $B/jacobi3d 512 512 512 -n 40 --tile-z 16 --device-time
-CUDA_VISIBLE_DEVICES=0 timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$? $(tail -1 gpurun_out/pytest_gpu.log)" >> $O
-timeout 900 $TR --master-port 29621 bench.py --gpus $N --steps 30 --warmup 5 > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err; echo "bench rc=$?" >> $O
-cat $O; python3 -c "
-import json
-d=json.loads(open('gpurun_out/bench_n2.json').read().strip().splitlines()[-1])
-print(d['value'], d['ms_per_step'], d['verified'], d['exchange_us_per_iter'], d['astaroth']['ms_per_step_device'])"
+run $B/weak-exchange 512 512 512 30
+run $TR --master-port 29631 --no-python $B/weak-exchange 512 512 512 30
+CUDA_VISIBLE_DEVICES=0 run $B/weak-exchange 512 512 512 30
+STENCIL_EXCHANGE_TRACE=3 $B/weak 512 512 512 4 2>&1 | grep "exchange " | tail -4 >> $O
+cat $O
