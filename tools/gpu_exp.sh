@@ -3,15 +3,17 @@
 mkdir -p gpurun_out
 cd /root/repo
 export STENCIL_LOG_LEVEL=1
-O=gpurun_out/exp.txt
+N=${N:-4}
+O=gpurun_out/exp_n$N.txt
 : > $O
-timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$? $(tail -1 gpurun_out/pytest_gpu.log)" >> $O
-timeout 120 python -c "import __graft_entry__ as g; g.smoke()" >> $O 2>&1
-timeout 900 python bench.py --steps 30 --warmup 5 > gpurun_out/bench1.json 2> gpurun_out/bench1.err; echo "bench rc=$?" >> $O
-timeout 900 python bench.py --impl reference --steps 30 --warmup 5 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "bench ref rc=$?" >> $O
-timeout 900 python bench.py > gpurun_out/bench_default.json 2> gpurun_out/bench_default.err; echo "bench default-args rc=$?" >> $O
+B=/root/repo/build/bin
+TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
+run() { echo "## $TAG $*" >> $O; ( cd /tmp && timeout 300 "$@" 2>/dev/null | grep -E "device|jacobi3d,|astaroth|verify|weak" ) >> $O; }
+timeout 600 $B/test_cuda "[multigpu]" > gpurun_out/test_multigpu_n$N.log 2>&1; echo "test_multigpu rc=$? $(tail -1 gpurun_out/test_multigpu_n$N.log)" >> $O
+run $TR --master-port 29601 --no-python $B/jacobi3d 512 512 512 --verify 50 --tile-z 16 --delay-us 300
+TAG=1proc run $B/weak-exchange 512 512 512 30
+timeout 900 $TR --master-port 29621 bench.py --gpus $N --steps 30 --warmup 5 > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err; echo "bench rc=$?" >> $O
 cat $O; python3 -c "
 import json
-for f in ['bench1','bench_ref','bench_default']:
-    d=json.loads(open('gpurun_out/'+f+'.json').read().strip().splitlines()[-1])
-    print(f, d['value'], d['ms_per_step'], d.get('verified'), d['exchange_us_per_iter'], (d.get('astaroth') or {}).get('ms_per_step_device'), d['e2e']['value'], d['clocks'])"
+d=json.loads(open('gpurun_out/bench_n$N.json').read().strip().splitlines()[-1])
+print(d['value'], d['ms_per_step'], d['verified'], d['exchange_us_per_iter'], d['astaroth']['ms_per_step_device'], d['e2e']['value'])"
