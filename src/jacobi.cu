@@ -50,12 +50,10 @@ namespace {
 constexpr int kLanes = 32, kRows = 8, kThreads = kLanes * kRows, kVec = 4, kTileX = kLanes * kVec;
 /* TMA variant geometry. Two tile shapes share one kernel, picked per tile (uniform per CTA):
      wide   128 cells x 16 rows: a warp is one pair of rows, a lane owns 4 cells of each;
-     narrow  32 cells x 64 rows: a warp is four pairs of rows, 8 lanes per row;
-     slim    16 cells x 128 rows: a warp is eight pairs of rows, 4 lanes per row. Same 2048 cells per plane, same loop.
+     narrow  32 cells x 64 rows: a warp is four pairs of rows, 8 lanes per row. Same 2048 cells per plane, same loop.
    Narrow tiles cover what is left of a row after the last full 128-cell tile: the weak-scaling rule produces rows of
    645 and 813 cells, and a wide tile on the remaining 5 / 45 cells costs as much as one on 128 (the kernel is as much
-   issue bound as DRAM bound). 645 -> 5 wide + 1 slim column = 5.125 tile columns instead of 6; 813 -> 6 wide + 1 narrow
-   + 1 slim = 6.375 instead of 7. */
+   issue bound as DRAM bound). 645 -> 5 wide + 1 narrow column = 5.25 tile columns instead of 6. */
 constexpr int kTmaRows = 16, kTmaStages = 6;
 constexpr int kTmaConsumerWarps = kTmaRows / 2, kTmaThreads = kTmaConsumerWarps * 32;
 constexpr int kMaxTileZ = 64; // bound on Options::tileZ for the TMA variant (keeps enough tiles in flight on small domains)
@@ -80,12 +78,8 @@ template <int LW> struct Geo { // LW = lanes per row: 32 (wide) or 8 (narrow)
 };
 using Wide = Geo<32>;
 using Narrow = Geo<8>;
-using Slim = Geo<4>;
-constexpr unsigned char kShapeWide = 0, kShapeNarrow = 1, kShapeSlim = 2; // Tile::narrow
 constexpr int kNarrowMaxRemainder = 96; // a remainder wider than this is cheaper as one wide tile than as four narrow ones
-constexpr int kShapeSmemBytes[3] = {Wide::kSmemBytes, Narrow::kSmemBytes, Slim::kSmemBytes};
-constexpr int kTmaSmemBytes = Slim::kSmemBytes > Narrow::kSmemBytes ? (Slim::kSmemBytes > Wide::kSmemBytes ? Slim::kSmemBytes : Wide::kSmemBytes)
-                                                                    : (Narrow::kSmemBytes > Wide::kSmemBytes ? Narrow::kSmemBytes : Wide::kSmemBytes);
+constexpr int kTmaSmemBytes = Narrow::kSmemBytes > Wide::kSmemBytes ? Narrow::kSmemBytes : Wide::kSmemBytes;
 constexpr size_t kDynBytes = Jacobi3D::kParamBytes;
 constexpr int kFusedFlagBase = 64; // word offset of the fused-iteration flags inside a control block
 
@@ -95,7 +89,7 @@ struct Tile {
   int x0, y0;           // first cell / first row of the tile (compute coordinates)
   unsigned short tz;    // z index in units of tileZ
   unsigned char faces;  // bit f set when the tile owns cells on face f that must be pushed
-  unsigned char narrow; // TMA variant: tile shape, kShapeWide (128 x 16) / kShapeNarrow (32 x 64) / kShapeSlim (16 x 128)
+  unsigned char narrow; // TMA variant: 1 = 32 x 64 tile, 0 = 128 x 16
 };
 
 struct JacobiParams {
@@ -438,7 +432,7 @@ __device__ __noinline__ void store_partial(const JacobiParams &P, float *dp, int
     if (x0 + k >= P.lox && x0 + k < P.hix) dp[k] = ov[k];
 }
 
-/* one tile of the TMA kernel; G = Wide, Narrow or Slim (uniform per CTA) */
+/* one tile of the TMA kernel; G = Wide or Narrow (uniform per CTA) */
 template <bool FUSED, class G>
 __device__ __forceinline__ void tma_tile(unsigned char *smem, const CUtensorMap *tmap, const CUtensorMap *tmapSide, const JacobiParams &P, const Tile &t) {
   constexpr int LW = 32 / G::kSub;
@@ -677,15 +671,12 @@ __device__ __forceinline__ void tma_tile(unsigned char *smem, const CUtensorMap 
 template <bool FUSED, int MINB>
 __global__ void __launch_bounds__(kTmaThreads, MINB)
     jacobi7_tma_kernel(const __grid_constant__ CUtensorMap tmapWide, const __grid_constant__ CUtensorMap tmapNarrow,
-                       const __grid_constant__ CUtensorMap tmapSlim, const __grid_constant__ CUtensorMap tmapSideWide,
-                       const __grid_constant__ CUtensorMap tmapSideNarrow, const __grid_constant__ CUtensorMap tmapSideSlim,
+                       const __grid_constant__ CUtensorMap tmapSideWide, const __grid_constant__ CUtensorMap tmapSideNarrow,
                        const __grid_constant__ JacobiParams P) {
   extern __shared__ __align__(128) unsigned char smem[];
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); // the next iteration may start filling the slots this grid frees
   const Tile t = P.tiles[blockIdx.x];
-  if (t.narrow == kShapeSlim)
-    tma_tile<FUSED, Slim>(smem, &tmapSlim, &tmapSideSlim, P, t);
-  else if (t.narrow == kShapeNarrow)
+  if (t.narrow)
     tma_tile<FUSED, Narrow>(smem, &tmapNarrow, &tmapSideNarrow, P, t);
   else
     tma_tile<FUSED, Wide>(smem, &tmapWide, &tmapSideWide, P, t);
@@ -767,7 +758,7 @@ struct Jacobi3D::Impl {
     unsigned nAll = 0, nFace[6] = {0, 0, 0, 0, 0, 0};
     Tile *tilesInterior = nullptr;
     unsigned nInterior = 0;
-    int smemBytes = Wide::kSmemBytes; // the largest ring any tile shape in this subdomain's tables needs
+    bool anyNarrow = false; // some tile table of this subdomain holds narrow tiles: launches ask for the larger ring
     std::vector<std::pair<Tile *, unsigned>> tilesExterior;
     std::vector<Rect3> exterior;
     Rect3 interior;
@@ -784,7 +775,7 @@ struct Jacobi3D::Impl {
     JacobiParams base[2]; // per parity: src = buffer[parity]
     /* per parity: the curr buffer as a 3-D tensor (padded row, rows, planes) with the box of a wide tile, of a narrow
        tile, and the 4-cell-wide boxes at the other end of the rows (x wrap by load) for both shapes */
-    CUtensorMap tmap[2], tmapNarrow[2], tmapSlim[2], tmapSide[2], tmapSideNarrow[2], tmapSideSlim[2];
+    CUtensorMap tmap[2], tmapNarrow[2], tmapSide[2], tmapSideNarrow[2];
     bool wrapLoad = false;
     std::vector<int> sameDevDeps;
     WaitSet finalWait;
@@ -805,8 +796,7 @@ namespace {
 /* Tiles covering region [lo,hi) (compute coordinates) of a subdomain of size sz. faceMask selects which subdomain
    faces push (0 for non-fused launches); countMask the faces whose neighbour is another GPU, nFace[f] receives the
    number of tiles that push through face f to such a neighbour. With `narrow` (TMA variant) the part of a row that is
-   left after the last full 128-cell tile is covered by 32 x 64 tiles, and a last piece of at most 16 cells by a 16 x 128
-   tile, when it is at most kNarrowMaxRemainder cells.
+   left after the last full 128-cell tile is covered by 32 x 64 tiles when it is at most kNarrowMaxRemainder cells.
 
    Order. Natural (z, y, x) order keeps tiles that share halo rows / planes / margins resident together, so those
    re-reads hit L2 (putting ALL pushing tiles first, x faces included, measured +160 MB of DRAM reads per 512^3
@@ -822,23 +812,20 @@ std::vector<Tile> make_tiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int
   if (nFace)
     for (int f = 0; f < 6; ++f) nFace[f] = 0;
   if (hi.x <= lo.x || hi.y <= lo.y || hi.z <= lo.z) return out;
-  /* columns of tiles: (x0, shape) */
-  std::vector<std::pair<int64_t, unsigned char>> cols;
+  /* columns of tiles: (x0, narrow?) */
+  std::vector<std::pair<int64_t, bool>> cols;
   for (int64_t x = lo.x / kTileX * kTileX; x < hi.x;) {
     const int64_t left = std::min<int64_t>(hi.x, sz.x) - x;
-    if (narrow && left <= Slim::kW) {
-      if (x + Slim::kW > lo.x) cols.emplace_back(x, kShapeSlim);
-      x += Slim::kW;
-    } else if (narrow && left <= kNarrowMaxRemainder) {
-      /* skip columns that lie wholly before lo.x (regions that start inside a tile) */
-      if (x + Narrow::kW > lo.x) cols.emplace_back(x, kShapeNarrow);
+    if (narrow && left <= kNarrowMaxRemainder) {
+      /* skip 32-cell columns that lie wholly before lo.x (regions that start inside a tile) */
+      if (x + Narrow::kW > lo.x) cols.emplace_back(x, true);
       x += Narrow::kW;
     } else {
-      cols.emplace_back(x, kShapeWide);
+      cols.emplace_back(x, false);
       x += kTileX;
     }
   }
-  auto emit = [&](int64_t tz, int64_t x0, int64_t y0, int64_t w, int64_t r, unsigned char shape) {
+  auto emit = [&](int64_t tz, int64_t x0, int64_t y0, int64_t w, int64_t r, bool nar) {
     unsigned f = 0;
     if (x0 == 0) f |= 1u << XM;
     if (x0 <= sz.x - 1 && sz.x - 1 < x0 + w) f |= 1u << XP;
@@ -850,19 +837,16 @@ std::vector<Tile> make_tiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int
     if (nFace)
       for (int k = 0; k < 6; ++k)
         if ((f & countMask) >> k & 1u) ++nFace[k];
-    out.push_back(Tile{int(x0), int(y0), (unsigned short)tz, (unsigned char)f, shape});
+    out.push_back(Tile{int(x0), int(y0), (unsigned short)tz, (unsigned char)f, (unsigned char)(nar ? 1 : 0)});
   };
   for (int64_t tz = lo.z / tileZ; tz * tileZ < hi.z; ++tz) {
-    /* wide columns row block by row block, then the narrow and the slim columns (row blocks 4 and 8 times as tall) */
+    /* wide columns row block by row block, then the narrow columns (their row blocks are four times as tall) */
     for (int64_t y0 = lo.y / rows * rows; y0 < hi.y; y0 += rows)
       for (const auto &c : cols)
-        if (c.second == kShapeWide) emit(tz, c.first, y0, kTileX, rows, kShapeWide);
+        if (!c.second) emit(tz, c.first, y0, kTileX, rows, false);
     for (int64_t y0 = lo.y / Narrow::kR * Narrow::kR; y0 < hi.y; y0 += Narrow::kR)
       for (const auto &c : cols)
-        if (c.second == kShapeNarrow) emit(tz, c.first, y0, Narrow::kW, Narrow::kR, kShapeNarrow);
-    for (int64_t y0 = lo.y / Slim::kR * Slim::kR; y0 < hi.y; y0 += Slim::kR)
-      for (const auto &c : cols)
-        if (c.second == kShapeSlim) emit(tz, c.first, y0, Slim::kW, Slim::kR, kShapeSlim);
+        if (c.second) emit(tz, c.first, y0, Narrow::kW, Narrow::kR, true);
   }
   if (flaggedFirst && countMask) {
     /* ... and the cheap tiles last: a kernel ends with a partial wave of tiles, and what fills it best are tiles that
@@ -871,7 +855,7 @@ std::vector<Tile> make_tiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int
        the z faces moved to the front the tail was all full tiles (2 GPUs, 645 x 645 x 323: 0.2272 against 0.2223 ms). */
     const unsigned zbits = (1u << ZM) | (1u << ZP);
     auto cheap = [&](const Tile &t) {
-      const int64_t r = (t.narrow == kShapeSlim ? Slim::kR : (t.narrow == kShapeNarrow ? Narrow::kR : rows)), z0 = std::max<int64_t>(int64_t(t.tz) * tileZ, lo.z),
+      const int64_t r = (t.narrow ? Narrow::kR : rows), z0 = std::max<int64_t>(int64_t(t.tz) * tileZ, lo.z),
                     z1 = std::min<int64_t>(int64_t(t.tz + 1) * tileZ, hi.z);
       const int64_t activeRows = std::min<int64_t>(t.y0 + r, hi.y) - std::max<int64_t>(t.y0, lo.y);
       return 2 * activeRows <= r || 2 * (z1 - z0) <= tileZ;
@@ -1045,7 +1029,7 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
     d.tilesAll = upload(all);
     d.nAll = unsigned(all.size());
     auto note_narrow = [&d](const std::vector<Tile> &v) {
-      for (const Tile &t : v) d.smemBytes = std::max(d.smemBytes, kShapeSmemBytes[t.narrow]);
+      for (const Tile &t : v) d.anyNarrow = d.anyNarrow || t.narrow;
     };
     note_narrow(all);
     /* every CTA starts by reading its table entry and nothing can be issued before it arrives: keep the table in L2
@@ -1090,8 +1074,6 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
           d.tmapNarrow[parity] = make_plane_map(b, pitch, ld.raw_size(), Narrow::kBoxX, Narrow::kBoxY);
           d.tmapSide[parity] = make_plane_map(b, pitch, ld.raw_size(), kSideBoxX, Wide::kR);
           d.tmapSideNarrow[parity] = make_plane_map(b, pitch, ld.raw_size(), kSideBoxX, Narrow::kR);
-          d.tmapSlim[parity] = make_plane_map(b, pitch, ld.raw_size(), Slim::kBoxX, Slim::kBoxY);
-          d.tmapSideSlim[parity] = make_plane_map(b, pitch, ld.raw_size(), kSideBoxX, Slim::kR);
         }
         P.wrapLoad = d.wrapLoad ? 1 : 0;
       }
@@ -1211,14 +1193,14 @@ void Jacobi3D::step() {
       std::memset(&cfg, 0, sizeof(cfg));
       cfg.gridDim = dim3(n, 1, 1);
       cfg.blockDim = dim3(kTmaThreads, 1, 1);
-      cfg.dynamicSmemBytes = size_t(d.smemBytes);
+      cfg.dynamicSmemBytes = size_t(d.anyNarrow ? kTmaSmemBytes : Wide::kSmemBytes);
       cfg.stream = d.stream;
       cudaLaunchAttribute attr;
       attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
       attr.val.programmaticStreamSerializationAllowed = 1;
       cfg.attrs = &attr;
       cfg.numAttrs = opt_.pdl ? 1 : 0;
-      CUDA_RUNTIME(cudaLaunchKernelEx(&cfg, *k, d.tmap[pa], d.tmapNarrow[pa], d.tmapSlim[pa], d.tmapSide[pa], d.tmapSideNarrow[pa], d.tmapSideSlim[pa], P));
+      CUDA_RUNTIME(cudaLaunchKernelEx(&cfg, *k, d.tmap[pa], d.tmapNarrow[pa], d.tmapSide[pa], d.tmapSideNarrow[pa], P));
     } else if (fused) {
       jacobi7_kernel<true><<<n, kThreads, 0, d.stream>>>(P);
     } else {

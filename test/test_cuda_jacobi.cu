@@ -110,18 +110,14 @@ TEST_CASE("jacobi: one subdomain, all schedules, bit exact", "[cuda][jacobi]") {
   }
 }
 
-TEST_CASE("jacobi: rows that are not a multiple of the 128-cell tile use 32 x 64 and 16 x 128 remainder tiles", "[cuda][jacobi][narrow]") {
+TEST_CASE("jacobi: rows that are not a multiple of the 128-cell tile use 32 x 64 remainder tiles", "[cuda][jacobi][narrow]") {
   using M = stencil::Jacobi3D::Mode;
   for (M m : {M::Fused, M::Overlap, M::NoOverlap}) {
-    REQUIRE(mismatches(Dim3(133, 70, 20), m, {0}, 4, 8) == 0);    // one wide column + one slim column (remainder 5)
-    REQUIRE(mismatches(Dim3(150, 70, 20), m, {0}, 4, 8) == 0);    // one wide column + one narrow column, two narrow row blocks
+    REQUIRE(mismatches(Dim3(133, 70, 20), m, {0}, 4, 8) == 0);    // one wide column + one narrow column, two narrow row blocks
     REQUIRE(mismatches(Dim3(70, 130, 12), m, {0}, 4, 4) == 0);    // narrow columns only (0, 32, 64), three row blocks
     REQUIRE(mismatches(Dim3(200, 65, 10), m, {0, 0}, 4, 8) == 0); // remainder 72: three narrow columns; y cut across subdomains
     REQUIRE(mismatches(Dim3(230, 20, 18), m, {0}, 3, 8) == 0);    // remainder 102 > 96: a second wide column instead
     REQUIRE(mismatches(Dim3(132, 64, 9), m, {0}, 3, 4) == 0);     // remainder is exactly one vector
-    REQUIRE(mismatches(Dim3(170, 140, 9), m, {0}, 3, 4) == 0);    // remainder 42: one narrow + one slim column, two slim row blocks
-    REQUIRE(mismatches(Dim3(145, 30, 11), m, {0, 0}, 3, 4) == 0); // remainder 17: one narrow column, no slim one
-    REQUIRE(mismatches(Dim3(16, 130, 10), m, {0}, 3, 4) == 0);    // a slim column only
   }
   /* same sizes with the remainder tiles switched off agree as well */
   REQUIRE(mismatches(Dim3(133, 70, 20), M::Fused, {0}, 4, 8, MethodFlags::All, false) == 0);
