@@ -668,19 +668,15 @@ __device__ __forceinline__ void tma_tile(unsigned char *smem, const CUtensorMap 
   }
 }
 
-/* NARROW = false: the instantiation for tile tables that hold wide tiles only (every row a multiple of 128 cells: the
-   512^3 and 1024 x 512 x 256 subdomains of 1 and 8 GPUs) — half the code, nothing else different. ~100 registers are
-   needed either way: at 3 CTAs/SM (80 registers) the loop spills, and with the shared-memory-heavy carve-out those
-   spills miss L1 (measured 4x slower), so the kernels are built for 2 CTAs/SM. */
-template <bool FUSED, bool NARROW>
-__global__ void __launch_bounds__(kTmaThreads, 2)
+template <bool FUSED, int MINB>
+__global__ void __launch_bounds__(kTmaThreads, MINB)
     jacobi7_tma_kernel(const __grid_constant__ CUtensorMap tmapWide, const __grid_constant__ CUtensorMap tmapNarrow,
                        const __grid_constant__ CUtensorMap tmapSideWide, const __grid_constant__ CUtensorMap tmapSideNarrow,
                        const __grid_constant__ JacobiParams P) {
   extern __shared__ __align__(128) unsigned char smem[];
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); // the next iteration may start filling the slots this grid frees
   const Tile t = P.tiles[blockIdx.x];
-  if (NARROW && t.narrow)
+  if (t.narrow)
     tma_tile<FUSED, Narrow>(smem, &tmapNarrow, &tmapSideNarrow, P, t);
   else
     tma_tile<FUSED, Wide>(smem, &tmapWide, &tmapSideWide, P, t);
@@ -790,6 +786,8 @@ struct Jacobi3D::Impl {
   unsigned *err = nullptr;
   bool fusedOk = true;
   bool useTma = true;
+  int minBlocks = 3; // resident CTAs per SM the TMA kernel is compiled for (when forced through the environment)
+  bool minBlocksForced = false;
   int rows = kTmaRows; // tile rows of the selected kernel variant
 };
 
@@ -942,6 +940,10 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
   impl_.reset(new Impl);
   impl_->useTma = opt_.useTma;
   impl_->rows = opt_.useTma ? kTmaRows : kRows;
+  if (const char *e = std::getenv("STENCIL_JACOBI_MINB")) {
+    impl_->minBlocks = std::atoi(e) == 2 ? 2 : 3;
+    impl_->minBlocksForced = true;
+  }
   CUDA_RUNTIME(cudaHostAlloc(&impl_->err, sizeof(unsigned), cudaHostAllocMapped | cudaHostAllocPortable));
   *impl_->err = 0;
 
@@ -973,13 +975,13 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
     DevGuard g(ld.gpu());
     d.stream = RcStream(ld.gpu());
     if (opt_.useTma) { // function attributes are per device
-      for (auto *k : {&jacobi7_tma_kernel<true, true>, &jacobi7_tma_kernel<false, true>, &jacobi7_tma_kernel<true, false>, &jacobi7_tma_kernel<false, false>})
+      for (auto *k : {&jacobi7_tma_kernel<true, 2>, &jacobi7_tma_kernel<false, 2>, &jacobi7_tma_kernel<true, 3>, &jacobi7_tma_kernel<false, 3>})
         CUDA_RUNTIME(cudaFuncSetAttribute(*k, cudaFuncAttributeMaxDynamicSharedMemorySize, kTmaSmemBytes));
       /* three 59 KB rings per SM fit the driver's default carve-out; forcing the maximum carve-out measured no better */
       int carve = -1;
       if (const char *e = std::getenv("STENCIL_JACOBI_CARVEOUT")) carve = std::atoi(e); // percent of the unified array; -1 = driver default
       if (carve >= 0)
-        for (auto *k : {&jacobi7_tma_kernel<true, true>, &jacobi7_tma_kernel<false, true>, &jacobi7_tma_kernel<true, false>, &jacobi7_tma_kernel<false, false>})
+        for (auto *k : {&jacobi7_tma_kernel<true, 2>, &jacobi7_tma_kernel<false, 2>, &jacobi7_tma_kernel<true, 3>, &jacobi7_tma_kernel<false, 3>})
           CUDA_RUNTIME(cudaFuncSetAttribute(*k, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
     }
     CUDA_RUNTIME(cudaEventCreateWithFlags(&d.done, cudaEventDisableTiming));
@@ -1181,9 +1183,11 @@ void Jacobi3D::step() {
     P.epoch = impl_->iter;
     P.dyn = d.dynNow;
     if (impl_->useTma) {
-      const bool lean = !d.anyNarrow && !std::getenv("STENCIL_JACOBI_FAT_KERNEL");
-      auto *k = fused ? (lean ? &jacobi7_tma_kernel<true, false> : &jacobi7_tma_kernel<true, true>)
-                      : (lean ? &jacobi7_tma_kernel<false, false> : &jacobi7_tma_kernel<false, true>);
+      /* the fused variant needs ~100 registers: at 3 CTAs/SM (80 registers) it spills inside the plane loop, and with
+         the shared-memory-heavy carve-out those spills miss L1 (measured 4x slower); the plain variant fits in 80 */
+      const int mb = impl_->minBlocksForced ? impl_->minBlocks : 2;
+      auto *k = fused ? (mb == 3 ? &jacobi7_tma_kernel<true, 3> : &jacobi7_tma_kernel<true, 2>)
+                      : (mb == 3 ? &jacobi7_tma_kernel<false, 3> : &jacobi7_tma_kernel<false, 2>);
       const int pa = ld.parity();
       cudaLaunchConfig_t cfg;
       std::memset(&cfg, 0, sizeof(cfg));

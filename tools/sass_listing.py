@@ -10,7 +10,7 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "stencil2_b200", "lib", "libstencil_b200.so")
 OUT = os.path.join(ROOT, "profiles", "sass")
-KEEP = ["jacobi7_tma_kernelILb1ELb1", "jacobi7_tma_kernelILb0ELb1", "jacobi7_tma_kernelILb1ELb0", "jacobi7_tma_kernelILb0ELb0", "astaroth_tma_kernelIdLb0", "astaroth_tma_kernelIdLb1", "astaroth_tma_kernelIfLb0",
+KEEP = ["jacobi7_tma_kernelILb1ELi2", "jacobi7_tma_kernelILb0ELi2", "astaroth_tma_kernelIdLb0", "astaroth_tma_kernelIdLb1", "astaroth_tma_kernelIfLb0",
         "astaroth_cross_kernelId", "box_copy_kernelILb1", "box_copy_kernelILb0", "box_copy_batch_kernel",
         "wait_flags_kernel", "signal_flags_kernel", "reduce_sum_f32_kernel", "astaroth_kernelIdLb1", "astaroth_kernelIfLb0", "jacobi7_kernelILb0",
         "fingerprint_kernel"]
@@ -39,7 +39,7 @@ def main():
             m = re.search(r"\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_.]+)", l)
             if m:
                 ops[m.group(1)] += 1
-        path = os.path.join(OUT, short.replace("ILb", "_").replace("ELi", "_").replace("ELb", "_") + ".sass")
+        path = os.path.join(OUT, short.replace("ILb", "_").replace("ELi", "_") + ".sass")
         with open(path, "w") as f:
             f.write("// " + dem + "\n// extracted with cuobjdump -sass from libstencil_b200.so (sm_100a)\n")
             f.write("\n".join(re.sub(r"\s*/\* 0x[0-9a-f]{16} \*/", "", l) for l in body.splitlines() if l.strip() and "0x" in l and "/*" in l))
