@@ -12,6 +12,7 @@
 #include <memory>
 #include <vector>
 
+#include "stencil/jacobi.hpp"
 #include "stencil/stencil.hpp"
 
 namespace stencil {
@@ -73,6 +74,13 @@ private:
   std::unique_ptr<Impl> impl_;
   std::atomic<unsigned long long> launches_{0};
 };
+
+namespace detail {
+/* test hook (host only, no GPU): the tile table of the Astaroth TMA kernel for region [lo,hi) of a subdomain of size sz,
+   in launch order; vecN = cells per 16-byte vector (4 fp32, 2 fp64); TileBox as in stencil/jacobi.hpp */
+std::vector<TileBox> astaroth_tile_table(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int fields, int tileZ, int vecN, unsigned dirMask,
+                                                unsigned flagMask, bool narrow, bool flaggedFirst, unsigned nDir[8], int *tileZUsed);
+} // namespace detail
 
 /* host reference: one step of one field on a dense periodic array (same arithmetic order as the kernel) */
 void astaroth_host_step(std::vector<double> &next, const std::vector<double> &curr, const Dim3 &size, AstarothSim::Stencil st, bool fp64,

@@ -95,6 +95,21 @@ private:
   std::atomic<unsigned long long> launches_{0};
 };
 
+namespace detail {
+/* One entry of a kernel's tile table as a box of cells (compute coordinates of the subdomain, clipped to the region the
+   table covers). faces / dirs: the subdomain faces (Jacobi: bit 0..5 = -x +x -y +y -z +z) or push directions (Astaroth:
+   bit 0..7 = -y +y -z +z and the four yz diagonals) the tile pushes through. shape: 0 wide, 1 narrow. */
+struct TileBox {
+  Dim3 lo, hi;
+  unsigned faces;
+  int shape, field;
+};
+/* test hooks (host only, no GPU): the table the Jacobi TMA kernel walks for region [lo,hi) of a subdomain of size sz —
+   in launch order — and the number of tiles counted per face of countMask */
+std::vector<TileBox> jacobi_tile_table(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int tileZ, unsigned faceMask, unsigned countMask, bool narrow,
+                                       bool flaggedFirst, unsigned nFace[6]);
+} // namespace detail
+
 /* test hook: how many of `values` does the kernel's 3-instruction x/6 round differently from IEEE division (expect 0) */
 unsigned jacobi_div6_mismatches(const std::vector<float> &values);
 

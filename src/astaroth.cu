@@ -883,6 +883,26 @@ void *build_push(DistributedDomain &dd, size_t di, int parity, int fields, const
 
 static bool is_star(AstarothSim::Stencil st) { return st != AstarothSim::Stencil::Average7; }
 
+namespace detail {
+std::vector<TileBox> astaroth_tile_table(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int fields, int tileZ, int vecN, unsigned dirMask,
+                                         unsigned flagMask, bool narrow, bool flaggedFirst, unsigned nDir[8], int *tileZUsed) {
+  const int tz = balanced_tile_z(hi.z - lo.z, tileZ);
+  if (tileZUsed) *tileZUsed = tz;
+  std::vector<TileBox> out;
+  for (const ATile &t : make_atiles(lo, hi, sz, fields, tz, vecN, dirMask, flagMask, nDir, narrow, flaggedFirst, true)) {
+    const int64_t w = (t.narrow ? 8 : 32) * vecN, r = t.narrow ? 4 * kTRows : kTRows, z0 = lo.z + int64_t(t.chunk) * tz;
+    TileBox b;
+    b.lo = Dim3(std::max<int64_t>(t.x0, lo.x), std::max<int64_t>(t.y0, lo.y), z0);
+    b.hi = Dim3(std::min<int64_t>(t.x0 + w, hi.x), std::min<int64_t>(t.y0 + r, hi.y), std::min<int64_t>(z0 + tz, hi.z));
+    b.faces = t.dirs;
+    b.shape = t.narrow;
+    b.field = t.field;
+    out.push_back(b);
+  }
+  return out;
+}
+} // namespace detail
+
 AstarothSim::AstarothSim(size_t x, size_t y, size_t z, const Options &opt) : opt_(opt) {
   if (opt_.fields < 1 || opt_.fields > kMaxFields) LOG_FATAL("AstarothSim supports 1.." << kMaxFields << " fields");
   dd_.reset(new DistributedDomain(x, y, z));

@@ -866,6 +866,28 @@ std::vector<Tile> make_tiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int
   return out;
 }
 
+} // namespace
+
+namespace detail {
+std::vector<TileBox> jacobi_tile_table(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int tileZ, unsigned faceMask, unsigned countMask, bool narrow,
+                                       bool flaggedFirst, unsigned nFace[6]) {
+  std::vector<TileBox> out;
+  for (const Tile &t : make_tiles(lo, hi, sz, kTmaRows, tileZ, faceMask, nFace, narrow, flaggedFirst, countMask)) {
+    const int64_t w = t.narrow ? Narrow::kW : Wide::kW, r = t.narrow ? Narrow::kR : Wide::kR;
+    TileBox b;
+    b.lo = Dim3(std::max<int64_t>(t.x0, lo.x), std::max<int64_t>(t.y0, lo.y), std::max<int64_t>(int64_t(t.tz) * tileZ, lo.z));
+    b.hi = Dim3(std::min<int64_t>(t.x0 + w, hi.x), std::min<int64_t>(t.y0 + r, hi.y), std::min<int64_t>(int64_t(t.tz + 1) * tileZ, hi.z));
+    b.faces = t.faces;
+    b.shape = t.narrow;
+    b.field = 0;
+    out.push_back(b);
+  }
+  return out;
+}
+} // namespace detail
+
+namespace {
+
 Tile *upload(const std::vector<Tile> &t) {
   if (t.empty()) return nullptr;
   Tile *d = nullptr;

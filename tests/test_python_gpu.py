@@ -47,6 +47,69 @@ def test_astaroth_engine_against_host(built):
             sim.close()
 
 
+def test_jacobi_random_field_fingerprint_and_cross_stencil(built):
+    """What bench.py's verification relies on: a random initial field that is a function of the global coordinate, and a
+    field fingerprint that does not depend on partition or schedule; and the cross-derivative Astaroth stencil (reads
+    edge and corner halos) against the host reference, with every halo coming from the kernels' pushes after step 1."""
+    from stencil2_b200._lib import lib
+    from stencil2_b200.models import Jacobi3D, AstarothSim, astaroth_host_step, jacobi_host_step
+    size = (133, 40, 30)
+    ref = np.empty((size[2], size[1], size[0]), dtype=np.float32)
+    L = lib()
+    for z in range(0, size[2], 7):
+        for y in range(0, size[1], 5):
+            for x in range(0, size[0], 11):
+                ref[z, y, x] = L.stencil_jacobi_random_value(7, x, y, z, *size)
+    prints = []
+    fields = []
+    for mode, gpus in ((Jacobi3D.FUSED, [0]), (Jacobi3D.NO_OVERLAP, [0, 0]), (Jacobi3D.FUSED, [0, 0, 0, 0])):
+        j = Jacobi3D(*size, gpus=gpus, mode=mode, tile_z=8)
+        j.init_random(7)
+        got = j.gather()
+        assert all(got[z, y, x] == ref[z, y, x] for z in range(0, size[2], 7) for y in range(0, size[1], 5) for x in range(0, size[0], 11))
+        assert 0.0 <= got.min() and got.max() < 1.0 and got.std() > 0.2
+        for _ in range(6):
+            j.step()
+        prints.append(j.fingerprint())
+        fields.append(j.gather())
+        j.close()
+    assert prints[0] == prints[1] == prints[2] and prints[0] != 0
+    assert np.array_equal(fields[0], fields[1]) and np.array_equal(fields[0], fields[2])
+    host = got
+    for _ in range(6):
+        host = jacobi_host_step(host)
+    assert np.array_equal(host, fields[0])
+
+    sim = AstarothSim(70, 44, 50, fields=2, fp64=True, stencil=AstarothSim.STAR19_CROSS, overlap=False, gpus=[0, 0, 0, 0])
+    sim.init()
+    ref = sim.gather(0)
+    for _ in range(7):
+        sim.step()
+        ref = astaroth_host_step(ref, stencil=2, fp64=True, dt=sim.dt)
+    sim.sync()
+    assert np.abs(sim.gather(0) - ref).max() < 1e-12
+    t, ex, dev = sim.run_timed(3)
+    assert t > 0 and dev > 0 and dev <= t * 1.5
+    sim.close()
+
+
+def test_domain_grid_and_timed_exchange(built):
+    from stencil2_b200.models import DistributedDomain, Method
+    dd = DistributedDomain(40, 30, 20)
+    dd.set_radius(2)
+    dd.add_data(np.float32, "a")
+    dd.add_data(np.float64, "b")
+    dd.set_methods(Method.ALL)
+    dd.set_gpus([0, 0, 0, 0])
+    dd.set_plan_file(False)
+    dd.realize()
+    gx, gy, gz = dd.grid
+    assert gx * gy * gz == 4 and gx == 1  # x is the expensive axis: cut last
+    host_s, dev_s = dd.time_exchange(5)
+    assert host_s > 0 and dev_s > 0 and dev_s <= host_s * 1.5
+    dd.close()
+
+
 def test_exchange_async_chained_to_a_torch_stream(built):
     """DistributedDomain.exchange_async(): halos of a periodic 2-subdomain field are filled while the host never waits
     for the exchange; a torch stream is chained to it through the raw CUDA events in both directions."""
