@@ -1,19 +1,17 @@
 #!/bin/bash
-# Scratch script for one-off GPU experiments (edited per experiment, run through gpurun).
+# scratch: A/B of the narrow tile shape (build = 8 lanes: 32 x 64 cells, build_exp4 = 4 lanes: 16 x 128 cells)
 mkdir -p gpurun_out
-cd /root/repo
-export STENCIL_LOG_LEVEL=1
-O=gpurun_out/exp.txt
-: > $O
-J=./build/bin/jacobi3d
-run() { echo "## $TAG $*" >> $O; timeout 300 "$@" 2>/dev/null | grep -E "device|verify" >> $O; }
-timeout 900 ./build/bin/test_cuda "[jacobi]" > "gpurun_out/test_jacobi.log" 2>&1; echo "test rc=$? $(tail -1 gpurun_out/test_jacobi.log)" >> $O
-for rep in 1 2; do
-for cfg in "512 512 512" "1024 512 256"; do
-  TAG=lean run $J $cfg --exact-size -n 40 --tile-z 16 --device-time
-  TAG=fat STENCIL_JACOBI_FAT_KERNEL=1 run $J $cfg --exact-size -n 40 --tile-z 16 --device-time
-done
-done
-TAG=lean run $J 512 512 512 --exact-size -n 40 --tile-z 16 --device-time --no-overlap
-TAG=fat STENCIL_JACOBI_FAT_KERNEL=1 run $J 512 512 512 --exact-size -n 40 --tile-z 16 --device-time --no-overlap
-cat $O; grep -h -B2 -A8 FAIL gpurun_out/test_*.log | head -30
+{
+  for b in build build_exp4; do
+    echo "## $b test [jacobi]"; timeout 200 ./$b/bin/test_cuda "[jacobi]" 2>&1 | tail -2
+  done
+  for rep in 1 2; do
+    for sz in "645 645 323" "813 407 407" "512 512 512" "333 300 200"; do
+      for b in build build_exp4; do
+        echo "## $b $sz"; timeout 100 ./$b/bin/jacobi3d $sz --exact-size -n 40 --device-time 2>&1 | grep "jacobi3d-device"
+      done
+    done
+  done
+  echo "## verify exp4"; timeout 200 ./build_exp4/bin/jacobi3d 645 645 323 --exact-size --verify 20 2>&1 | tail -2
+} > gpurun_out/exp.txt 2>&1
+cat gpurun_out/exp.txt
