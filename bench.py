@@ -246,7 +246,7 @@ def main():
     ap.add_argument("--impl", default="own", choices=["own", "reference"])
     ap.add_argument("--size", type=int, default=512, help="cells per axis per GPU")
     ap.add_argument("--astaroth-size", type=int, default=256, help="cells per axis per GPU of the Astaroth config")
-    ap.add_argument("--tile-z", type=int, default=16)
+    ap.add_argument("--tile-z", type=int, default=0, help="planes per tile; 0 = the library's own choice")
     ap.add_argument("--verify-iters", type=int, default=20, help="0 skips the fused-vs-plain verification")
     ap.add_argument("--random-init", action="store_true", help="time on a random initial field instead of the reference app's 0.5")
     ap.add_argument("--skip-exchange", action="store_true")

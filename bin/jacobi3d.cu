@@ -21,7 +21,7 @@ int main(int argc, char **argv) {
   double delayUs = 0;
   size_t x = 512, y = 512, z = 512;
   std::string prefix;
-  int iters = 30, period = -1, tileZ = 32;
+  int iters = 30, period = -1, tileZ = 0;
 
   argparse::Parser parser("7-point Jacobi on a periodic box with a hot and a cold sphere");
   methodArgs.add_to(parser);
@@ -40,7 +40,7 @@ int main(int argc, char **argv) {
   parser.add_flag(paraview, "--paraview")->help("dump paraview files");
   parser.add_option(iters, "--iters", "-n")->help("number of iterations");
   parser.add_option(period, "--period", "-q")->help("iterations between checkpoints");
-  parser.add_option(tileZ, "--tile-z")->help("planes marched per CTA");
+  parser.add_option(tileZ, "--tile-z")->help("planes marched per CTA (default: chosen from the subdomain size)");
   parser.add_positional(x)->required();
   parser.add_positional(y)->required();
   parser.add_positional(z)->required();

@@ -31,7 +31,9 @@ public:
     PlacementStrategy placement = PlacementStrategy::NodeAware;
     Mode mode = Mode::Fused;
     std::vector<int> gpus; // empty: the rank's default devices
-    int tileZ = 32;        // z-extent of a tile (planes marched per CTA)
+    int tileZ = 0;         // z-extent of a tile (planes marched per CTA); 0: 48 on large subdomains, down to 16 on small ones
+    int tailPlanes = 48;   // the top tailPlanes planes of a subdomain are cut into layers of tailDepth planes instead: thin
+    int tailDepth = 8;     // tiles at the end of the table fill the kernel's ragged last wave (STENCIL_JACOBI_TAIL_PLANES / _DEPTH)
     bool useTma = true;    // TMA + mbarrier pipelined kernel (false: plain LDG variant, kept for comparison)
     bool flaggedFirst = true; // schedule the tiles that push to ANOTHER GPU first, so each face is announced early
     bool narrowTiles = true;  // cover the remainder of rows that are not a multiple of 128 cells with 32 x 64 tiles
@@ -107,7 +109,7 @@ struct TileBox {
 /* test hooks (host only, no GPU): the table the Jacobi TMA kernel walks for region [lo,hi) of a subdomain of size sz —
    in launch order — and the number of tiles counted per face of countMask */
 std::vector<TileBox> jacobi_tile_table(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int tileZ, unsigned faceMask, unsigned countMask, bool narrow,
-                                       bool flaggedFirst, unsigned nFace[6]);
+                                       bool flaggedFirst, unsigned nFace[6], int tailPlanes = 0, int tailDepth = 8);
 } // namespace detail
 
 /* test hook: how many of `values` does the kernel's 3-instruction x/6 round differently from IEEE division (expect 0) */

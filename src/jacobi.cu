@@ -56,6 +56,7 @@ constexpr int kLanes = 32, kRows = 8, kThreads = kLanes * kRows, kVec = 4, kTile
    issue bound as DRAM bound). 645 -> 5 wide + 1 narrow column = 5.25 tile columns instead of 6. */
 constexpr int kTmaRows = 16, kTmaStages = 6;
 constexpr int kTmaConsumerWarps = kTmaRows / 2, kTmaThreads = kTmaConsumerWarps * 32;
+constexpr int kAutoTileZ = 48; // layer depth chosen for large subdomains when Options::tileZ is 0 (measured: profiles/README.md)
 constexpr int kMaxTileZ = 64; // bound on Options::tileZ for the TMA variant (keeps enough tiles in flight on small domains)
 constexpr int kTmaLag = 2; // the producer refills the slot that was consumed kTmaLag planes ago
 /* Subdomains that wrap onto themselves in x (always, with the default partition) do not keep x halo cells at all in
@@ -86,11 +87,12 @@ constexpr int kFusedFlagBase = 64; // word offset of the fused-iteration flags i
 enum Face { XM = 0, XP = 1, YM = 2, YP = 3, ZM = 4, ZP = 5 };
 
 struct Tile {
-  int x0, y0;           // first cell / first row of the tile (compute coordinates)
-  unsigned short tz;    // z index in units of tileZ
+  int x0, y0, z0;       // first cell / first row / first plane of the tile (compute coordinates)
+  unsigned short nz;    // planes the tile marches (layers differ in depth: see z_layers)
   unsigned char faces;  // bit f set when the tile owns cells on face f that must be pushed
   unsigned char narrow; // TMA variant: 1 = 32 x 64 tile, 0 = 128 x 16
 };
+static_assert(sizeof(Tile) == 16, "one 16-byte load per CTA");
 
 struct JacobiParams {
   const float *src; // interior origin: compute cell (0,0,0) of curr
@@ -98,7 +100,6 @@ struct JacobiParams {
   long long pitchX, pitchXY; // elements: row pitch, plane pitch
   int sx, sy, sz;            // compute-region size
   int lox, loy, loz, hix, hiy, hiz; // cells to update (compute coordinates, half open)
-  int tileZ;
   int wrapLoad;       // fused mode, subdomain is its own +-x neighbour: x neighbours across the wrap come from side TMA boxes
   unsigned debugSkip; // diagnostics only (STENCIL_JACOBI_DEBUG_SKIP): 1 no signal, 2 no x push, 4 no y/z push,
                       // 8 wide tiles fetch 16 rows per plane instead of 18 (WRONG results: timing bound for halo-row sharing)
@@ -229,7 +230,7 @@ template <bool FUSED> __global__ void __launch_bounds__(kThreads) jacobi7_kernel
 
   const int x0 = t.x0 + lane * kVec;
   const int y = t.y0 + row;
-  const int z0 = max(int(t.tz) * P.tileZ, P.loz), z1 = min(int(t.tz + 1) * P.tileZ, P.hiz);
+  const int z0 = max(t.z0, P.loz), z1 = min(t.z0 + int(t.nz), P.hiz);
   /* a warp is one row, so the row test is warp-uniform; the x test is per lane (partial tiles) */
   const bool rowActive = y >= P.loy && y < P.hiy;
   const bool laneActive = x0 < P.hix && x0 + kVec > P.lox;
@@ -460,7 +461,7 @@ __device__ __forceinline__ void tma_tile(unsigned char *smem, const CUtensorMap 
      the two proxies explicitly. */
   if (FUSED && (t.faces & P.flagMask) && threadIdx.x == 0) asm volatile("fence.proxy.async.global;" ::: "memory");
 
-  const int z0 = max(int(t.tz) * P.tileZ, P.loz), z1 = min(int(t.tz + 1) * P.tileZ, P.hiz);
+  const int z0 = max(t.z0, P.loz), z1 = min(t.z0 + int(t.nz), P.hiz);
   const int nplanes = z1 > z0 ? z1 - z0 + 2 : 0; // input planes z0-1 .. z1
 
   /* There is no producer warp: a ninth warp would cost a tenth warp's worth of registers (warps are allocated in
@@ -806,8 +807,42 @@ namespace {
    kernel — whose first tiles are exactly the ones that need that face — never waits for the END of this one, and the
    GPUs may drift by most of an iteration without anybody spinning. Cost: two planes per z face and one row per y-face
    tile lose their L2 hit (< 1 % of the traffic). */
-std::vector<Tile> make_tiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int rows, int tileZ, unsigned faceMask, unsigned *nFace,
+/* The z layers of planes [lo, hi). The bulk is cut into layers of (about) tileZ planes: deep tiles amortise the two
+   halo planes and the pipeline fill of a tile. The top `tailPlanes` planes are cut into layers of tailDepth instead:
+   a kernel ends when its slowest CTA does, and with 296 resident tiles of equal depth the last of them retire over
+   most of a tile's duration, during which the SMs that finished first have nothing left to take; thin tiles at the
+   end of the table fill that gap in small pieces (the same reasoning as for the cheap tiles in make_tiles). Depths
+   are even wherever the plane count allows (the plane loop is unrolled by two). */
+struct ZPlan {
+  int tileZ = 32, tailPlanes = 0, tailDepth = 8;
+};
+std::vector<std::pair<int64_t, int64_t>> z_layers(int64_t lo, int64_t hi, const ZPlan &zp) {
+  std::vector<std::pair<int64_t, int64_t>> out;
+  const int64_t planes = hi - lo;
+  if (planes <= 0) return out;
+  const int64_t tileZ = std::max(1, zp.tileZ), tailDepth = std::max(1, std::min(zp.tailDepth, zp.tileZ));
+  /* no thin tail on regions that are not at least two full layers deeper than it */
+  int64_t tail = (zp.tailPlanes > 0 && planes >= zp.tailPlanes + 2 * tileZ) ? zp.tailPlanes : 0;
+  const int64_t bulk = planes - tail;
+  int64_t z = lo;
+  if (tail == 0) {
+    for (; z < hi; z += tileZ) out.emplace_back(z, std::min(z + tileZ, hi));
+    return out;
+  }
+  /* the bulk in equal (even) layers, so that no short layer ends up in the middle of the table */
+  const int64_t n = (bulk + tileZ - 1) / tileZ;
+  int64_t d = (bulk + n - 1) / n;
+  d += d & 1;
+  d = std::min(d, tileZ);
+  const int64_t end = lo + bulk;
+  for (; z < end; z += d) out.emplace_back(z, std::min(z + d, end));
+  for (z = end; z < hi; z += tailDepth) out.emplace_back(z, std::min(z + tailDepth, hi));
+  return out;
+}
+
+std::vector<Tile> make_tiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int rows, const ZPlan &zp, unsigned faceMask, unsigned *nFace,
                              bool narrow, bool flaggedFirst = true, unsigned countMask = 0) {
+  const int tileZ = zp.tileZ;
   std::vector<Tile> out;
   if (nFace)
     for (int f = 0; f < 6; ++f) nFace[f] = 0;
@@ -825,21 +860,21 @@ std::vector<Tile> make_tiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int
       x += kTileX;
     }
   }
-  auto emit = [&](int64_t tz, int64_t x0, int64_t y0, int64_t w, int64_t r, bool nar) {
+  auto emit = [&](const std::pair<int64_t, int64_t> &zl, int64_t x0, int64_t y0, int64_t w, int64_t r, bool nar) {
     unsigned f = 0;
     if (x0 == 0) f |= 1u << XM;
     if (x0 <= sz.x - 1 && sz.x - 1 < x0 + w) f |= 1u << XP;
     if (y0 == 0) f |= 1u << YM;
     if (y0 <= sz.y - 1 && sz.y - 1 < y0 + r) f |= 1u << YP;
-    if (tz == 0) f |= 1u << ZM;
-    if (tz * tileZ <= sz.z - 1 && sz.z - 1 < (tz + 1) * tileZ) f |= 1u << ZP;
+    if (zl.first == 0) f |= 1u << ZM;
+    if (zl.first <= sz.z - 1 && sz.z - 1 < zl.second) f |= 1u << ZP;
     f &= faceMask;
     if (nFace)
       for (int k = 0; k < 6; ++k)
         if ((f & countMask) >> k & 1u) ++nFace[k];
-    out.push_back(Tile{int(x0), int(y0), (unsigned short)tz, (unsigned char)f, (unsigned char)(nar ? 1 : 0)});
+    out.push_back(Tile{int(x0), int(y0), int(zl.first), (unsigned short)(zl.second - zl.first), (unsigned char)f, (unsigned char)(nar ? 1 : 0)});
   };
-  for (int64_t tz = lo.z / tileZ; tz * tileZ < hi.z; ++tz) {
+  for (const auto &tz : z_layers(lo.z, hi.z, zp)) {
     /* wide columns row block by row block, then the narrow columns (their row blocks are four times as tall) */
     for (int64_t y0 = lo.y / rows * rows; y0 < hi.y; y0 += rows)
       for (const auto &c : cols)
@@ -855,10 +890,9 @@ std::vector<Tile> make_tiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int
        the z faces moved to the front the tail was all full tiles (2 GPUs, 645 x 645 x 323: 0.2272 against 0.2223 ms). */
     const unsigned zbits = (1u << ZM) | (1u << ZP);
     auto cheap = [&](const Tile &t) {
-      const int64_t r = (t.narrow ? Narrow::kR : rows), z0 = std::max<int64_t>(int64_t(t.tz) * tileZ, lo.z),
-                    z1 = std::min<int64_t>(int64_t(t.tz + 1) * tileZ, hi.z);
+      const int64_t r = (t.narrow ? Narrow::kR : rows);
       const int64_t activeRows = std::min<int64_t>(t.y0 + r, hi.y) - std::max<int64_t>(t.y0, lo.y);
-      return 2 * activeRows <= r || 2 * (z1 - z0) <= tileZ;
+      return 2 * activeRows <= r || 2 * int64_t(t.nz) <= tileZ;
     };
     auto prio = [&](const Tile &t) { return (t.faces & countMask & zbits) ? 0 : ((t.faces & countMask) ? 1 : (cheap(t) ? 3 : 2)); };
     std::stable_sort(out.begin(), out.end(), [&](const Tile &a, const Tile &b) { return prio(a) < prio(b); });
@@ -870,13 +904,17 @@ std::vector<Tile> make_tiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int
 
 namespace detail {
 std::vector<TileBox> jacobi_tile_table(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int tileZ, unsigned faceMask, unsigned countMask, bool narrow,
-                                       bool flaggedFirst, unsigned nFace[6]) {
+                                       bool flaggedFirst, unsigned nFace[6], int tailPlanes, int tailDepth) {
   std::vector<TileBox> out;
-  for (const Tile &t : make_tiles(lo, hi, sz, kTmaRows, tileZ, faceMask, nFace, narrow, flaggedFirst, countMask)) {
+  ZPlan zp;
+  zp.tileZ = tileZ;
+  zp.tailPlanes = tailPlanes;
+  zp.tailDepth = tailDepth;
+  for (const Tile &t : make_tiles(lo, hi, sz, kTmaRows, zp, faceMask, nFace, narrow, flaggedFirst, countMask)) {
     const int64_t w = t.narrow ? Narrow::kW : Wide::kW, r = t.narrow ? Narrow::kR : Wide::kR;
     TileBox b;
-    b.lo = Dim3(std::max<int64_t>(t.x0, lo.x), std::max<int64_t>(t.y0, lo.y), std::max<int64_t>(int64_t(t.tz) * tileZ, lo.z));
-    b.hi = Dim3(std::min<int64_t>(t.x0 + w, hi.x), std::min<int64_t>(t.y0 + r, hi.y), std::min<int64_t>(int64_t(t.tz + 1) * tileZ, hi.z));
+    b.lo = Dim3(std::max<int64_t>(t.x0, lo.x), std::max<int64_t>(t.y0, lo.y), t.z0);
+    b.hi = Dim3(std::min<int64_t>(t.x0 + w, hi.x), std::min<int64_t>(t.y0 + r, hi.y), t.z0 + int64_t(t.nz));
     b.faces = t.faces;
     b.shape = t.narrow;
     b.field = 0;
@@ -942,8 +980,10 @@ Jacobi3D::~Jacobi3D() {
 }
 
 void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
-  if (opt_.tileZ < 1) opt_.tileZ = 32;
+  if (opt_.tileZ < 0) opt_.tileZ = 0; // 0: chosen per subdomain below
   if (opt_.useTma && opt_.tileZ > kMaxTileZ) opt_.tileZ = kMaxTileZ;
+  if (const char *e = std::getenv("STENCIL_JACOBI_TAIL_PLANES")) opt_.tailPlanes = std::atoi(e);
+  if (const char *e = std::getenv("STENCIL_JACOBI_TAIL_DEPTH")) opt_.tailDepth = std::atoi(e);
   if (std::getenv("STENCIL_JACOBI_NATURAL_ORDER")) opt_.flaggedFirst = false;
   if (std::getenv("STENCIL_JACOBI_NO_NARROW")) opt_.narrowTiles = false;
   if (const char *e = std::getenv("STENCIL_JACOBI_PDL")) opt_.pdl = std::atoi(e) != 0;
@@ -1047,7 +1087,21 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
     d.sameDevDeps.assign(deps.begin(), deps.end());
     const int rows = impl_->rows;
     const bool narrow = impl_->useTma && opt_.narrowTiles;
-    const std::vector<Tile> all = make_tiles(Dim3(0, 0, 0), sz, sz, rows, opt_.tileZ, faceMask, d.nFace, narrow, opt_.flaggedFirst, flagMask);
+    ZPlan zp;
+    zp.tileZ = opt_.tileZ;
+    if (zp.tileZ < 1) {
+      /* automatic depth: deep layers (kAutoTileZ planes) where the subdomain still gives at least four waves of resident
+         tiles, shallower ones — down to 16 planes — on small subdomains, which need the tile count more */
+      int sms = 148;
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ld.gpu());
+      const int64_t perLayer = ((sz.x + kTileX - 1) / kTileX) * ((sz.y + rows - 1) / rows);
+      int64_t depth = sz.z * perLayer / (4 * 2 * int64_t(sms));
+      depth -= depth & 1;
+      zp.tileZ = int(std::min<int64_t>(kAutoTileZ, std::max<int64_t>(16, depth)));
+    }
+    zp.tailPlanes = impl_->useTma ? opt_.tailPlanes : 0;
+    zp.tailDepth = opt_.tailDepth;
+    const std::vector<Tile> all = make_tiles(Dim3(0, 0, 0), sz, sz, rows, zp, faceMask, d.nFace, narrow, opt_.flaggedFirst, flagMask);
     d.tilesAll = upload(all);
     d.nAll = unsigned(all.size());
     auto note_narrow = [&d](const std::vector<Tile> &v) {
@@ -1059,12 +1113,12 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
     if (impl_->useTma) tma::keep_in_l2(d.stream, d.tilesAll, all.size() * sizeof(Tile));
     d.interior = interiors[di];
     d.exterior = exteriors[di];
-    const std::vector<Tile> in = make_tiles(d.interior.lo - org, d.interior.hi - org, sz, rows, opt_.tileZ, 0, nullptr, narrow);
+    const std::vector<Tile> in = make_tiles(d.interior.lo - org, d.interior.hi - org, sz, rows, zp, 0, nullptr, narrow);
     note_narrow(in);
     d.tilesInterior = upload(in);
     d.nInterior = unsigned(in.size());
     for (const Rect3 &r : d.exterior) {
-      const std::vector<Tile> ex = make_tiles(r.lo - org, r.hi - org, sz, rows, opt_.tileZ, 0, nullptr, narrow);
+      const std::vector<Tile> ex = make_tiles(r.lo - org, r.hi - org, sz, rows, zp, 0, nullptr, narrow);
       note_narrow(ex);
       d.tilesExterior.emplace_back(upload(ex), unsigned(ex.size()));
     }
@@ -1084,7 +1138,6 @@ void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
       P.hix = P.sx;
       P.hiy = P.sy;
       P.hiz = P.sz;
-      P.tileZ = opt_.tileZ;
       if (const char *e = std::getenv("STENCIL_JACOBI_DEBUG_SKIP")) P.debugSkip = unsigned(std::atoi(e));
       {
         /* logical element (0,0,0) sits `lead` elements into the padded row; compute x=0 is one radius further */

@@ -10,7 +10,7 @@ from .domain import DistributedDomain, Method, Placement
 class Jacobi3D:
     FUSED, OVERLAP, NO_OVERLAP = 0, 1, 2
 
-    def __init__(self, x, y, z, methods=Method.ALL, placement=Placement.NODE_AWARE, mode=0, gpus=None, tile_z=32):
+    def __init__(self, x, y, z, methods=Method.ALL, placement=Placement.NODE_AWARE, mode=0, gpus=None, tile_z=0):
         arr = (C.c_int * len(gpus))(*gpus) if gpus else None
         self._h = lib().stencil_jacobi_create(x, y, z, int(methods), int(placement), int(mode), arr, len(gpus) if gpus else 0, tile_z)
         self.size = (x, y, z)

@@ -190,3 +190,33 @@ TEST_CASE("astaroth tile table: sub-regions", "[tiles][astaroth]") {
         for (int f = 0; f < 2; ++f) REQUIRE(coverage_faults(t, los[i], his[i], f) == 0);
       }
 }
+
+TEST_CASE("jacobi tile table: thin layers at the top of the subdomain close the table", "[tiles][jacobi]") {
+  const Dim3 sz(300, 40, 323), lo(0, 0, 0);
+  for (unsigned countMask : {0x00u, 0x30u, 0x3Cu}) {
+    unsigned nFace[6];
+    const auto t = stencil::detail::jacobi_tile_table(lo, sz, sz, 32, 0x3F, countMask, true, true, nFace, 48, 8);
+    REQUIRE(coverage_faults(t, lo, sz, 0) == 0);
+    int64_t deepest = 0, thinPlanes = 0;
+    for (const TileBox &b : t) {
+      const int64_t d = b.hi.z - b.lo.z;
+      deepest = std::max(deepest, d);
+      REQUIRE(d <= 32);
+      if (b.lo.z >= 323 - 48) REQUIRE(d <= 8);        // the top 48 planes: 8-plane layers
+      if (b.lo.z < 323 - 48) REQUIRE(b.hi.z <= 323 - 48); // no layer straddles the boundary
+      if (b.lo.z < 323 - 48) REQUIRE(d >= 18);        // the bulk (275 planes) in 9 even layers of 32 with one odd rest
+      if (b.lo.x == 0 && b.lo.y == 0 && d <= 8) thinPlanes += d;
+    }
+    REQUIRE(deepest == 32);
+    REQUIRE(thinPlanes == 48);
+    /* the table ends with thin tiles (those that push to another GPU excepted: they go first) */
+    const TileBox &last = t.back();
+    REQUIRE(last.hi.z - last.lo.z <= 8);
+    REQUIRE((last.faces & countMask) == 0u);
+  }
+  /* a region too shallow for bulk + tail keeps uniform layers */
+  unsigned nFace[6];
+  const Dim3 small(128, 16, 60);
+  for (const TileBox &b : stencil::detail::jacobi_tile_table(lo, small, small, 32, 0, 0, true, true, nFace, 48, 8))
+    REQUIRE((b.hi.z - b.lo.z == 32 || b.hi.z == 60));
+}

@@ -129,6 +129,16 @@ TEST_CASE("jacobi: rows that are not a multiple of the 128-cell tile use 32 x 64
   REQUIRE(bad == 0);
 }
 
+TEST_CASE("jacobi: thin layers at the top of a deep subdomain, automatic layer depth", "[cuda][jacobi][tail]") {
+  using M = stencil::Jacobi3D::Mode;
+  for (M m : {M::Fused, M::Overlap, M::NoOverlap}) {
+    REQUIRE(mismatches(Dim3(140, 20, 70), m, {0}, 4, 8) == 0);       // 70 planes: 22 in three layers, 48 in six thin ones
+    REQUIRE(mismatches(Dim3(140, 20, 140), m, {0, 0}, 4, 8) == 0);   // the same per subdomain, z faces pushed by a thin and a deep layer
+    REQUIRE(mismatches(Dim3(133, 30, 81), m, {0}, 3, 16) == 0);      // odd plane count, narrow column
+    REQUIRE(mismatches(Dim3(96, 40, 50), m, {0, 0}, 3, 0) == 0);     // depth chosen by the library
+  }
+}
+
 TEST_CASE("jacobi: 2, 3, 4 and 8 subdomains on GPU 0", "[cuda][jacobi]") {
   using M = stencil::Jacobi3D::Mode;
   for (M m : {M::Fused, M::Overlap, M::NoOverlap}) {

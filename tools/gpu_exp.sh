@@ -1,17 +1,14 @@
 #!/bin/bash
-# scratch: A/B of the narrow tile shape (build = 8 lanes: 32 x 64 cells, build_exp4 = 4 lanes: 16 x 128 cells)
+# scratch: new layer plan on N GPUs: tests, protocol check with a delayed GPU, bench line
+N=${1:-2}
 mkdir -p gpurun_out
 {
-  for b in build build_exp4; do
-    echo "## $b test [jacobi]"; timeout 200 ./$b/bin/test_cuda "[jacobi]" 2>&1 | tail -2
-  done
-  for rep in 1 2; do
-    for sz in "645 645 323" "813 407 407" "512 512 512" "333 300 200"; do
-      for b in build build_exp4; do
-        echo "## $b $sz"; timeout 100 ./$b/bin/jacobi3d $sz --exact-size -n 40 --device-time 2>&1 | grep "jacobi3d-device"
-      done
-    done
-  done
-  echo "## verify exp4"; timeout 200 ./build_exp4/bin/jacobi3d 645 645 323 --exact-size --verify 20 2>&1 | tail -2
+  timeout 300 ./build/bin/test_cuda "[jacobi]" 2>&1 | tail -3
+  echo "## verify with a delayed GPU, 1 process x $N GPUs"
+  timeout 200 ./build/bin/jacobi3d 512 512 512 --verify 50 --delay-us 300 2>&1 | grep "jacobi3d-verify"
+  echo "## verify with a delayed GPU, $N processes"
+  timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29711 --no-python ./build/bin/jacobi3d 512 512 512 --verify 50 --delay-us 300 2>&1 | grep "jacobi3d-verify"
+  echo "## bench"
+  timeout 400 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29712 bench.py --gpus $N --skip-exchange --skip-astaroth 2>gpurun_out/exp_bench.err | tee gpurun_out/exp_bench_n$N.json | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print(d['ms_per_step'], d['ms_per_step_repeats'], d['value'], d['verified'], d['e2e']['value'])"
 } > gpurun_out/exp.txt 2>&1
 cat gpurun_out/exp.txt
