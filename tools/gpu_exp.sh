@@ -1,11 +1,8 @@
 #!/bin/bash
-# scratch: new layer plan on N GPUs: tests, protocol check with a delayed GPU, bench line
+# scratch: new layer plan on N GPUs: protocol check with a delayed GPU, bench line
 N=${1:-2}
 mkdir -p gpurun_out
 {
-  timeout 300 ./build/bin/test_cuda "[jacobi]" 2>&1 | tail -3
-  echo "## verify with a delayed GPU, 1 process x $N GPUs"
-  timeout 200 ./build/bin/jacobi3d 512 512 512 --verify 50 --delay-us 300 2>&1 | grep "jacobi3d-verify"
   echo "## verify with a delayed GPU, $N processes"
   timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29711 --no-python ./build/bin/jacobi3d 512 512 512 --verify 50 --delay-us 300 2>&1 | grep "jacobi3d-verify"
   echo "## bench"
