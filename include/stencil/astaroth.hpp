@@ -46,6 +46,8 @@ public:
     double period = 10;
     double dt = 0.01;
     int tileZ = 48; // planes per z chunk asked for (chunks are balanced: 256 planes -> 6 x 43); measured 1 - 2 % over 32 on the weak-scaling shapes
+    int tailPlanes = 0; // TMA kernel: the top tailPlanes planes of a subdomain in chunks of tailDepth planes, scheduled last
+    int tailDepth = 8;  // (STENCIL_ASTAROTH_TAIL_PLANES / _DEPTH)
     bool planFile = false;
   };
 
@@ -79,7 +81,7 @@ namespace detail {
 /* test hook (host only, no GPU): the tile table of the Astaroth TMA kernel for region [lo,hi) of a subdomain of size sz,
    in launch order; vecN = cells per 16-byte vector (4 fp32, 2 fp64); TileBox as in stencil/jacobi.hpp */
 std::vector<TileBox> astaroth_tile_table(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int fields, int tileZ, int vecN, unsigned dirMask,
-                                                unsigned flagMask, bool narrow, bool flaggedFirst, unsigned nDir[8], int *tileZUsed);
+                                                unsigned flagMask, bool narrow, bool flaggedFirst, unsigned nDir[8], int *tileZUsed, int tailPlanes = 0, int tailDepth = 8);
 } // namespace detail
 
 /* host reference: one step of one field on a dense periodic array (same arithmetic order as the kernel) */

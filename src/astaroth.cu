@@ -406,8 +406,10 @@ inline unsigned tile_dirs(int ylo, int tr, int z0, int z1, int sy, int sz, unsig
 
 struct ATile {
   int x0, y0;           // first cell / row of the tile (compute coordinates)
-  unsigned short chunk; // z chunk of the region: planes loz + chunk*tileZ ...
-  unsigned char field, dirs, narrow, down, pad[2]; // down: march z downwards (neighbouring chunks alternate, see astaroth_tile)
+  int z0;               // first plane of the tile's z chunk
+  unsigned short nz;    // planes of the chunk (chunks differ in depth: see astaroth_layers)
+  unsigned char field, dirs, narrow, down; // down: march z downwards (neighbouring chunks alternate, see astaroth_tile)
+  unsigned char pad[2];
 };
 
 template <typename T> struct TmaParams {
@@ -443,7 +445,7 @@ __device__ __forceinline__ void astaroth_tile(unsigned char *smem, const TmaPara
     }
     tma::mbar_fence_init();
   }
-  const int z0 = P.loz + int(t.chunk) * P.tileZ, z1 = min(z0 + P.tileZ, P.hiz);
+  const int z0 = t.z0, z1 = min(t.z0 + int(t.nz), P.hiz);
   /* tiles that exchange with another GPU first wait for that GPU's flags of the previous iteration (they are the only
      tiles that read halo cells it wrote); the TMA reads that follow are async-proxy accesses, ordered after the
      acquire by an explicit proxy fence of the issuing thread */
@@ -776,7 +778,29 @@ int balanced_tile_z(int64_t planes, int tileZ) {
   return int(std::max<int64_t>(kR, (planes + chunks - 1) / chunks));
 }
 
-std::vector<ATile> make_atiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int fields, int tileZ, int vecN, unsigned dirMask, unsigned flagMask,
+/* The z chunks of planes [lo, hi): balanced chunks of at most tileZ planes; with tailPlanes > 0 the top tailPlanes planes
+   are cut into chunks of tailDepth instead — thin tiles that go to the end of the table and fill the kernel's ragged
+   last wave in small pieces (same reasoning and measurements as z_layers() in src/jacobi.cu). */
+struct ZChunks {
+  std::vector<std::pair<int64_t, int64_t>> chunk;
+  int depth = 0; // depth of the balanced chunks
+};
+ZChunks astaroth_layers(int64_t lo, int64_t hi, int tileZ, int tailPlanes = 0, int tailDepth = 8) {
+  ZChunks r;
+  const int64_t planes = hi - lo;
+  r.depth = balanced_tile_z(planes, tileZ);
+  if (planes <= 0) return r;
+  tailDepth = std::max(kR, std::min(tailDepth, tileZ));
+  int64_t tail = tailPlanes > 0 ? int64_t(tailPlanes) / tailDepth * tailDepth : 0;
+  if (planes < tail + 2 * int64_t(tileZ)) tail = 0;
+  const int64_t end = hi - tail;
+  if (tail) r.depth = balanced_tile_z(end - lo, tileZ);
+  for (int64_t z = lo; z < end; z += r.depth) r.chunk.emplace_back(z, std::min<int64_t>(z + r.depth, end));
+  for (int64_t z = end; z < hi; z += tailDepth) r.chunk.emplace_back(z, std::min<int64_t>(z + tailDepth, hi));
+  return r;
+}
+
+std::vector<ATile> make_atiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int fields, const ZChunks &zc, int vecN, unsigned dirMask, unsigned flagMask,
                                unsigned *nDir, bool narrowOk, bool flaggedFirst, bool zigzag) {
   std::vector<ATile> out;
   if (nDir)
@@ -794,16 +818,17 @@ std::vector<ATile> make_atiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, i
       x += wideX;
     }
   }
-  const int64_t nChunks = (hi.z - lo.z + tileZ - 1) / tileZ;
+  const int64_t nChunks = int64_t(zc.chunk.size());
   for (int f = 0; f < fields; ++f)
     for (int64_t c = 0; c < nChunks; ++c) {
-      const int z0 = int(lo.z + c * tileZ), z1 = int(std::min<int64_t>(z0 + tileZ, hi.z));
+      const int z0 = int(zc.chunk[size_t(c)].first), z1 = int(zc.chunk[size_t(c)].second);
       auto emit = [&](int64_t x0, int64_t y0, int64_t tr, bool nar) {
         ATile t;
         std::memset(&t, 0, sizeof(t));
         t.x0 = int(x0);
         t.y0 = int(y0);
-        t.chunk = (unsigned short)c;
+        t.z0 = z0;
+        t.nz = (unsigned short)(z1 - z0);
         t.field = (unsigned char)f;
         t.narrow = nar ? 1 : 0;
         t.down = (zigzag && (c & 1)) ? 1 : 0;
@@ -826,7 +851,7 @@ std::vector<ATile> make_atiles(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, i
     const unsigned zbits = (1u << kZM) | (1u << kZP);
     auto cheap = [&](const ATile &t) {
       const int64_t r = t.narrow ? narrowY : kTRows;
-      return 2 * (std::min<int64_t>(t.y0 + r, hi.y) - std::max<int64_t>(t.y0, lo.y)) <= r;
+      return 2 * (std::min<int64_t>(t.y0 + r, hi.y) - std::max<int64_t>(t.y0, lo.y)) <= r || 2 * int64_t(t.nz) <= zc.depth;
     };
     auto prio = [&](const ATile &t) { return (t.dirs & flagMask & zbits) ? 0 : ((t.dirs & flagMask) ? 1 : (cheap(t) ? 3 : 2)); };
     std::stable_sort(out.begin(), out.end(), [&](const ATile &a, const ATile &b) { return prio(a) < prio(b); });
@@ -885,15 +910,15 @@ static bool is_star(AstarothSim::Stencil st) { return st != AstarothSim::Stencil
 
 namespace detail {
 std::vector<TileBox> astaroth_tile_table(const Dim3 &lo, const Dim3 &hi, const Dim3 &sz, int fields, int tileZ, int vecN, unsigned dirMask,
-                                         unsigned flagMask, bool narrow, bool flaggedFirst, unsigned nDir[8], int *tileZUsed) {
-  const int tz = balanced_tile_z(hi.z - lo.z, tileZ);
-  if (tileZUsed) *tileZUsed = tz;
+                                         unsigned flagMask, bool narrow, bool flaggedFirst, unsigned nDir[8], int *tileZUsed, int tailPlanes, int tailDepth) {
+  const ZChunks zc = astaroth_layers(lo.z, hi.z, tileZ, tailPlanes, tailDepth);
+  if (tileZUsed) *tileZUsed = zc.depth;
   std::vector<TileBox> out;
-  for (const ATile &t : make_atiles(lo, hi, sz, fields, tz, vecN, dirMask, flagMask, nDir, narrow, flaggedFirst, true)) {
-    const int64_t w = (t.narrow ? 8 : 32) * vecN, r = t.narrow ? 4 * kTRows : kTRows, z0 = lo.z + int64_t(t.chunk) * tz;
+  for (const ATile &t : make_atiles(lo, hi, sz, fields, zc, vecN, dirMask, flagMask, nDir, narrow, flaggedFirst, true)) {
+    const int64_t w = (t.narrow ? 8 : 32) * vecN, r = t.narrow ? 4 * kTRows : kTRows;
     TileBox b;
-    b.lo = Dim3(std::max<int64_t>(t.x0, lo.x), std::max<int64_t>(t.y0, lo.y), z0);
-    b.hi = Dim3(std::min<int64_t>(t.x0 + w, hi.x), std::min<int64_t>(t.y0 + r, hi.y), std::min<int64_t>(z0 + tz, hi.z));
+    b.lo = Dim3(std::max<int64_t>(t.x0, lo.x), std::max<int64_t>(t.y0, lo.y), t.z0);
+    b.hi = Dim3(std::min<int64_t>(t.x0 + w, hi.x), std::min<int64_t>(t.y0 + r, hi.y), t.z0 + int64_t(t.nz));
     b.faces = t.dirs;
     b.shape = t.narrow;
     b.field = t.field;
@@ -921,6 +946,8 @@ AstarothSim::AstarothSim(size_t x, size_t y, size_t z, const Options &opt) : opt
   if (std::getenv("STENCIL_ASTAROTH_NO_NARROW")) opt_.narrowTiles = false;
   if (std::getenv("STENCIL_ASTAROTH_NO_ZIGZAG")) opt_.zigzag = false;
   if (std::getenv("STENCIL_ASTAROTH_NATURAL_ORDER")) opt_.flaggedFirst = false;
+  if (const char *e = std::getenv("STENCIL_ASTAROTH_TAIL_PLANES")) opt_.tailPlanes = std::atoi(e);
+  if (const char *e = std::getenv("STENCIL_ASTAROTH_TAIL_DEPTH")) opt_.tailDepth = std::atoi(e);
   if (const char *e = std::getenv("STENCIL_LAUNCH_THREADS")) impl_->launchThreads = std::atoi(e) != 0;
   for (LocalDomain &ld : dd_->domains()) {
     DevGuard g(ld.gpu());
@@ -980,19 +1007,19 @@ AstarothSim::AstarothSim(size_t x, size_t y, size_t z, const Options &opt) : opt
       const Dim3 sz = ld.size(), org = ld.origin();
       if (!impl_->tilesAll[di].dev)
       {
-        const int tz = balanced_tile_z(sz.z, opt_.tileZ);
-        impl_->tilesAll[di] = Impl::upload(make_atiles(Dim3(0, 0, 0), sz, sz, opt_.fields, tz, vecN, 0, 0, nullptr, opt_.narrowTiles, opt_.flaggedFirst, opt_.zigzag), tz);
+        const ZChunks zc = astaroth_layers(0, sz.z, opt_.tileZ, opt_.tailPlanes, opt_.tailDepth);
+        impl_->tilesAll[di] = Impl::upload(make_atiles(Dim3(0, 0, 0), sz, sz, opt_.fields, zc, vecN, 0, 0, nullptr, opt_.narrowTiles, opt_.flaggedFirst, opt_.zigzag), zc.depth);
       }
       tma::keep_in_l2(impl_->streams[di], impl_->tilesAll[di].dev, size_t(impl_->tilesAll[di].n) * sizeof(ATile));
       {
-        const int tz = balanced_tile_z(impl_->interior[di].extent().z, opt_.tileZ);
-        impl_->tilesInterior[di] = Impl::upload(make_atiles(impl_->interior[di].lo - org, impl_->interior[di].hi - org, sz, opt_.fields, tz, vecN, 0, 0,
-                                                            nullptr, opt_.narrowTiles, false, opt_.zigzag), tz);
+        const ZChunks zc = astaroth_layers((impl_->interior[di].lo - org).z, (impl_->interior[di].hi - org).z, opt_.tileZ);
+        impl_->tilesInterior[di] = Impl::upload(make_atiles(impl_->interior[di].lo - org, impl_->interior[di].hi - org, sz, opt_.fields, zc, vecN, 0, 0,
+                                                            nullptr, opt_.narrowTiles, false, opt_.zigzag), zc.depth);
       }
       for (const Rect3 &r : impl_->exterior[di]) {
-        const int tz = balanced_tile_z(r.extent().z, opt_.tileZ);
+        const ZChunks zc = astaroth_layers((r.lo - org).z, (r.hi - org).z, opt_.tileZ);
         impl_->tilesExterior[di].push_back(
-            Impl::upload(make_atiles(r.lo - org, r.hi - org, sz, opt_.fields, tz, vecN, 0, 0, nullptr, opt_.narrowTiles, false, opt_.zigzag), tz));
+            Impl::upload(make_atiles(r.lo - org, r.hi - org, sz, opt_.fields, zc, vecN, 0, 0, nullptr, opt_.narrowTiles, false, opt_.zigzag), zc.depth));
       }
     }
   }
@@ -1040,9 +1067,9 @@ void AstarothSim::setup_fused_faces() {
     p.sameDevDeps.assign(deps.begin(), deps.end());
     /* the tile table of the whole-region launch decides which CTAs take part in which hand-shake */
     const Dim3 sz = ld.size();
-    const int tz = balanced_tile_z(sz.z, opt_.tileZ);
-    impl_->tilesAll[di] = Impl::upload(make_atiles(Dim3(0, 0, 0), sz, sz, opt_.fields, tz, vecN, p.dirMask, p.flagMask, p.nDir, opt_.narrowTiles,
-                                                   opt_.flaggedFirst, opt_.zigzag), tz);
+    const ZChunks zc = astaroth_layers(0, sz.z, opt_.tileZ, opt_.tailPlanes, opt_.tailDepth);
+    impl_->tilesAll[di] = Impl::upload(make_atiles(Dim3(0, 0, 0), sz, sz, opt_.fields, zc, vecN, p.dirMask, p.flagMask, p.nDir, opt_.narrowTiles,
+                                                   opt_.flaggedFirst, opt_.zigzag), zc.depth);
     CUDA_RUNTIME(cudaMalloc(&p.done, kDirs * sizeof(unsigned)));
     CUDA_RUNTIME(cudaMemset(p.done, 0, kDirs * sizeof(unsigned)));
     for (int parity = 0; parity < 2; ++parity)

@@ -165,7 +165,7 @@ TEST_CASE("astaroth tile table: coverage per field, direction bits, counts, orde
         REQUIRE(p >= stage);
         stage = std::max(stage, p);
         if (p == 2) {
-          const bool cheap = 2 * (b.hi.y - b.lo.y) <= (b.shape ? 64 : 16);
+          const bool cheap = 2 * (b.hi.y - b.lo.y) <= (b.shape ? 64 : 16) || 2 * (b.hi.z - b.lo.z) <= tz;
           if (cheapSeen) REQUIRE(cheap);
           cheapSeen |= cheap;
         }
@@ -219,4 +219,28 @@ TEST_CASE("jacobi tile table: thin layers at the top of the subdomain close the 
   const Dim3 small(128, 16, 60);
   for (const TileBox &b : stencil::detail::jacobi_tile_table(lo, small, small, 32, 0, 0, true, true, nFace, 48, 8))
     REQUIRE((b.hi.z - b.lo.z == 32 || b.hi.z == 60));
+}
+
+TEST_CASE("astaroth tile table: thin chunks at the top of the subdomain close the table", "[tiles][astaroth]") {
+  const Dim3 sz(130, 40, 256), lo(0, 0, 0);
+  for (unsigned flagMask : {0x00u, 0x0Cu, 0xFFu}) {
+    unsigned nDir[8];
+    int tz = 0;
+    const auto t = stencil::detail::astaroth_tile_table(lo, sz, sz, 3, 48, 2, 0xFF, flagMask, true, true, nDir, &tz, 16, 8);
+    REQUIRE(tz == 48); // 240 planes of bulk in 5 chunks
+    for (int f = 0; f < 3; ++f) REQUIRE(coverage_faults(t, lo, sz, f) == 0);
+    for (const TileBox &b : t) {
+      const int64_t d = b.hi.z - b.lo.z;
+      if (b.lo.z >= 240) REQUIRE(d == 8);
+      if (b.lo.z < 240) REQUIRE(d == 48);
+    }
+    REQUIRE(t.back().hi.z - t.back().lo.z == 8);
+    REQUIRE((t.back().faces & flagMask) == 0u);
+  }
+  /* too shallow for bulk + tail: balanced chunks only */
+  unsigned nDir[8];
+  int tz = 0;
+  const Dim3 small(64, 16, 100);
+  for (const TileBox &b : stencil::detail::astaroth_tile_table(lo, small, small, 1, 48, 2, 0, 0, true, true, nDir, &tz, 16, 8)) REQUIRE(b.hi.z - b.lo.z >= 32);
+  REQUIRE(tz == 34);
 }

@@ -8,7 +8,7 @@
 
 namespace {
 double max_abs_err(const Dim3 &size, stencil::AstarothSim::Stencil st, bool fp64, int fields, const std::vector<int> &gpus, bool overlap, int iters,
-                   MethodFlags methods = MethodFlags::All, bool useTma = true, bool narrowTiles = true) {
+                   MethodFlags methods = MethodFlags::All, bool useTma = true, bool narrowTiles = true, int tailPlanes = 0) {
   stencil::AstarothSim::Options opt;
   opt.stencil = st;
   opt.fp64 = fp64;
@@ -20,6 +20,8 @@ double max_abs_err(const Dim3 &size, stencil::AstarothSim::Stencil st, bool fp64
   opt.methods = methods;
   opt.useTma = useTma;
   opt.narrowTiles = narrowTiles;
+  opt.tailPlanes = tailPlanes;
+  opt.tailDepth = 4;
   stencil::AstarothSim sim(size_t(size.x), size_t(size.y), size_t(size.z), opt);
   /* start from the device's own initial field: the device and host sin() differ in the last bits of a double */
   std::vector<double> ref = sim.gather(0), tmp;
@@ -90,6 +92,15 @@ TEST_CASE("astaroth: rows that are not a multiple of the tile use narrow remaind
   REQUIRE(max_abs_err(Dim3(200, 70, 14), S::Star19, false, 2, {0}, false, 5) < 2e-5);    // 128 + 72: three narrow fp32 columns
   REQUIRE(max_abs_err(Dim3(150, 37, 21), S::Star19, true, 2, {0, 0}, true, 3) < 1e-13);  // overlap schedule: interior / exterior tile tables
   REQUIRE(max_abs_err(Dim3(70, 70, 20), S::Star19, true, 2, {0}, false, 5, MethodFlags::All, true, false) < 1e-13); // remainder tiles off
+}
+
+TEST_CASE("astaroth: thin z chunks at the top of the subdomain", "[cuda][astaroth][tail]") {
+  using S = stencil::AstarothSim::Stencil;
+  /* chunk depth 8, tail 8 planes in chunks of 4: needs 24 planes per subdomain */
+  REQUIRE(max_abs_err(Dim3(150, 37, 30), S::Star19, true, 2, {0}, false, 4, MethodFlags::All, true, true, 8) < 1e-13);
+  REQUIRE(max_abs_err(Dim3(150, 37, 56), S::Star19, true, 2, {0, 0}, false, 5, MethodFlags::All, true, true, 8) < 1e-13); // z pushes by a thin and a deep chunk
+  REQUIRE(max_abs_err(Dim3(133, 40, 27), S::Star19, false, 3, {0}, false, 4, MethodFlags::All, true, true, 8) < 2e-5);
+  REQUIRE(max_abs_err(Dim3(140, 36, 30), S::Star19Cross, true, 2, {0}, false, 4, MethodFlags::All, true, true, 8) < 1e-12);
 }
 
 TEST_CASE("astaroth: cross-derivative stencil reads edge and corner halos", "[cuda][astaroth][cross]") {

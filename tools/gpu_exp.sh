@@ -1,11 +1,15 @@
 #!/bin/bash
-# scratch: new layer plan on N GPUs: protocol check with a delayed GPU, bench line
-N=${1:-2}
+# scratch: Astaroth thin z chunks at the end of the table, one GPU
 mkdir -p gpurun_out
+A="./build/bin/astaroth-sim --fields 8 --double --star19 --iters 20"
 {
-  echo "## verify with a delayed GPU, $N processes"
-  timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29711 --no-python ./build/bin/jacobi3d 512 512 512 --verify 50 --delay-us 300 2>&1 | grep "jacobi3d-verify"
-  echo "## bench"
-  timeout 400 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29712 bench.py --gpus $N --skip-exchange --skip-astaroth 2>gpurun_out/exp_bench.err | tee gpurun_out/exp_bench_n$N.json | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print(d['ms_per_step'], d['ms_per_step_repeats'], d['value'], d['verified'], d['e2e']['value'])"
+  timeout 60 ./build/bin/test_cuda "[tail]" 2>&1 | tail -3
+  for sz in "256 256 256" "323 323 162" "512 256 128"; do
+    set -- $sz
+    for c in "0 8" "16 8" "32 8" "24 12" "48 8"; do
+      r=$(STENCIL_ASTAROTH_TAIL_PLANES=${c% *} STENCIL_ASTAROTH_TAIL_DEPTH=${c#* } timeout 30 $A --x $1 --y $2 --z $3 2>&1 | grep "^astaroth-sim" | awk -F, '{print $12*1e3}')
+      echo "$sz tail $c : $r"
+    done
+  done
 } > gpurun_out/exp.txt 2>&1
 cat gpurun_out/exp.txt
