@@ -929,6 +929,7 @@ std::vector<TileBox> astaroth_tile_table(const Dim3 &lo, const Dim3 &hi, const D
 } // namespace detail
 
 AstarothSim::AstarothSim(size_t x, size_t y, size_t z, const Options &opt) : opt_(opt) {
+  if (opt_.tileZ > 32768) opt_.tileZ = 32768; // ATile::nz is 16 bits wide
   if (opt_.fields < 1 || opt_.fields > kMaxFields) LOG_FATAL("AstarothSim supports 1.." << kMaxFields << " fields");
   dd_.reset(new DistributedDomain(x, y, z));
   if (!opt_.gpus.empty()) dd_->set_gpus(opt_.gpus);

@@ -982,6 +982,7 @@ Jacobi3D::~Jacobi3D() {
 void Jacobi3D::build(size_t x, size_t y, size_t z, Comm *comm) {
   if (opt_.tileZ < 0) opt_.tileZ = 0; // 0: chosen per subdomain below
   if (opt_.useTma && opt_.tileZ > kMaxTileZ) opt_.tileZ = kMaxTileZ;
+  if (opt_.tileZ > 32768) opt_.tileZ = 32768; // Tile::nz is 16 bits wide
   if (const char *e = std::getenv("STENCIL_JACOBI_TAIL_PLANES")) opt_.tailPlanes = std::atoi(e);
   if (const char *e = std::getenv("STENCIL_JACOBI_TAIL_DEPTH")) opt_.tailDepth = std::atoi(e);
   if (std::getenv("STENCIL_JACOBI_NATURAL_ORDER")) opt_.flaggedFirst = false;
