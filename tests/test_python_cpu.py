@@ -206,3 +206,33 @@ def test_c_abi_header_library_and_binding_agree(built):
     unknown = sorted(b for b in bound if b not in declared)
     assert not unknown, f"bound in _lib.py but not in stencil_c.h: {unknown}"
     assert len(bound) > 40
+
+
+def test_bench_line_contract_and_weak_rule():
+    """The JSON line bench.py printed on the GPU box (kept under profiles/) has every key the driver reads, and the
+    weak-scaling rule gives the reference's domain sizes (645^3, 813^3, 1024^3)."""
+    import importlib.util
+    import json
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("bench_module", os.path.join(root, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    assert [bench.weak_size(512, n) for n in (1, 2, 4, 8)] == [512, 645, 813, 1024]
+    assert [bench.weak_size(256, n) for n in (2, 4, 8)] == [323, 406, 512]
+    cfg = bench.shared_config(512, 8)
+    assert cfg["global_batch"] == "1024x1024x1024 cells" and cfg["parallelism"] == "dd8"
+    line_file = os.path.join(root, "profiles", "runs", "r2", "bench_n1.json")
+    if not os.path.exists(line_file):
+        return
+    line = json.loads(open(line_file).read().strip().splitlines()[-1])
+    for key in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "vs_baseline",
+                "dtype", "data", "config", "clocks", "e2e", "gpu_launches"):
+        assert key in line, key
+    assert line["metric"] == bench.METRIC and line["higher_is_better"] is True and line["scaling"] == "weak"
+    assert line["warmup"] >= 3 and line["gpu_launches"] >= line["steps"]
+    for key in ("value", "unit", "h2d_bytes_per_step", "d2h_bytes_per_step"):
+        assert key in line["e2e"], key
+    assert line["config"] == bench.shared_config(512, 1)
+    assert line["verified"] is True
+    # cells per second from the time per step, as printed
+    assert abs(line["value"] - 512.0 ** 3 / (line["ms_per_step"] * 1e-3) / 1e9) < 0.01 * line["value"]
