@@ -1265,13 +1265,12 @@ void Jacobi3D::step() {
       auto *k = fused ? (mb == 3 ? &jacobi7_tma_kernel<true, 3> : &jacobi7_tma_kernel<true, 2>)
                       : (mb == 3 ? &jacobi7_tma_kernel<false, 3> : &jacobi7_tma_kernel<false, 2>);
       const int pa = ld.parity();
-      cudaLaunchConfig_t cfg;
-      std::memset(&cfg, 0, sizeof(cfg));
+      cudaLaunchConfig_t cfg = {};
       cfg.gridDim = dim3(n, 1, 1);
       cfg.blockDim = dim3(kTmaThreads, 1, 1);
       cfg.dynamicSmemBytes = size_t(d.anyNarrow ? kTmaSmemBytes : Wide::kSmemBytes);
       cfg.stream = d.stream;
-      cudaLaunchAttribute attr;
+      cudaLaunchAttribute attr = {};
       attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
       attr.val.programmaticStreamSerializationAllowed = 1;
       cfg.attrs = &attr;
